@@ -1,0 +1,137 @@
+/*
+ * superdsm_b200 -- C ABI of the B200-native DSM candidate solver.
+ *
+ * This is the drop-in boundary for SuperDSM's per-candidate convex fit.  The reference has no FFI for this path (it
+ * is pure Python on top of cvxopt + MKL via ctypes); the seam this library sits behind is
+ *
+ *     superdsm/objects.py:270-284   _compute_objects(objects, y, atoms, x_map, lock, dsm_cfg, log_root_dir)
+ *     superdsm/objects.py:361-412   cvxprog(region, scale, epsilon, alpha, smooth_amount, ...)
+ *
+ * and the entry points below are what a ctypes binding of that seam calls (INTEGRATION.md shows the stub).
+ * One call of sdsm_solve_batch() does, for every candidate of the batch, what objects.py:177-212 (_compute_object)
+ * does for one: region extraction, smooth-matrix construction, elliptical initialisation (objects.py:321-358), the
+ * DSM solve (dsm.py:431-490 -> cvxopt.solvers.cp), status/fallback logic (objects.py:394-410) and the rasterisation
+ * of the result (objects.py:198-211).
+ *
+ * Conventions: plain C types only; every pointer is caller-owned; d_* pointers are DEVICE pointers on the context's
+ * device (e.g. torch tensors' data_ptr()), h_* pointers are host pointers.  The library allocates no per-batch device
+ * memory: the caller provides the workspace sdsm_plan_batch() asked for.  All work is enqueued on the caller's
+ * stream; nothing synchronises.  Errors are integer codes (0 = ok), solver trouble is per-candidate data
+ * (status word), never a C++ exception.  One context per device; a context is not thread-safe.
+ */
+#ifndef SUPERDSM_B200_H
+#define SUPERDSM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SDSM_ABI_VERSION 1
+
+/* return codes */
+#define SDSM_OK              0
+#define SDSM_E_ARG           1   /* bad argument */
+#define SDSM_E_CUDA          2   /* CUDA runtime error, see sdsm_last_error() */
+#define SDSM_E_UNSUPPORTED   3   /* configuration outside what the kernels implement, see sdsm_last_error() */
+#define SDSM_E_WORKSPACE     4   /* workspace too small */
+
+/* per-candidate status word (out.status) */
+#define SDSM_ST_OPTIMAL      0   /* objects.cvxprog status 'optimal' (objects.py:401-403) */
+#define SDSM_ST_FALLBACK     1   /* status 'fallback': DSM solve failed, initialisation returned (objects.py:399-410) */
+#define SDSM_ST_SKIPPED      2   /* exactly one foreground pixel: not fitted (objects.py:184-191) */
+#define SDSM_ST_ERROR        3   /* CvxprogError: both elliptical passes failed (objects.py:351-353), or an empty region */
+#define SDSM_ST_BADREGION    4   /* pixel count differs from the host's, or a zero row in G~ (dsm.py:194 assertion) */
+
+/* hyper-parameters: the dsm_cfg dictionary of dsmcfg.py:6-21 after host-side preparation */
+typedef struct sdsm_params {
+    double alpha;            /* dsm/alpha */
+    double epsilon;          /* dsm/epsilon */
+    double scale;            /* dsm/scale; the solver minimises scale / n * psi (objects.py:380) */
+    double sparsity_tol;     /* dsm/sparsity_tol (dsm.py:346,363) */
+    int32_t subsample;       /* dsm/smooth_subsample; also the edge of the pixel cells */
+    int32_t radius;          /* R = kernel box // 2 (dsm.py:139,187); ignored if !has_smooth */
+    int32_t has_smooth;      /* 0: smooth_amount = inf, no deformation parameters (c2freganal.py:126) */
+    int32_t init_elliptical; /* 1: dsm/init == 'elliptical'; 0: zeros (objects.py:387-392) */
+    const float* h_psf;      /* HOST pointer, (radius+1)^2 floats: psf32[|dr|][|dc|], the float32 Gaussian kernel of
+                                dsm.py:137-142,226 (quarter of the symmetric box); may be NULL if !has_smooth */
+    int32_t maxiters;        /* cvxopt default 100 */
+    int32_t reserved;
+    double abstol, reltol, feastol;   /* cvxopt defaults 1e-7, 1e-6, 1e-7 */
+} sdsm_params;
+
+/* one candidate region.  The caller fills the first 8 fields; sdsm_plan_batch() fills the offsets. */
+typedef struct sdsm_cand {
+    int32_t r0, c0, h, w;    /* bounding box (image coordinates) of the usable pixels of the footprint's atoms */
+    int32_t fp_off, fp_len;  /* footprint = footprints[fp_off : fp_off + fp_len] (atom labels) */
+    int32_t n;               /* number of pixels of the region (sum of the atoms' usable-pixel counts) */
+    int32_t cell_cap;        /* out: upper bound of the number of pixel cells */
+    int64_t pix_off;         /* out: offset into the per-pixel workspace arrays */
+    int64_t cell_off;        /* out: offset into the per-cell workspace arrays */
+    int64_t tab_off;         /* out: offset into the per-row/column tables */
+    int64_t par_off;         /* out: offset into out.params (6 + cell_cap doubles reserved) */
+    int64_t fg_off;          /* out: offset into out.fgmask (h * w bytes, row-major over the bounding box) */
+} sdsm_cand;
+
+typedef struct sdsm_plan {
+    size_t workspace_bytes;  /* device workspace sdsm_solve_batch() needs */
+    int64_t params_len;      /* doubles in out.params */
+    int64_t fgmask_len;      /* bytes in out.fgmask */
+    int32_t n_max;           /* largest 6 + cell_cap of the batch */
+    int32_t cells_max;       /* largest cell_cap of the batch */
+    int32_t solver_ctas;     /* grid size of the persistent solver kernel */
+    int32_t reserved;
+} sdsm_plan;
+
+/* device output arrays of one batch, all caller-owned */
+typedef struct sdsm_out {
+    double*  d_energy;       /* [n_cand]   psi at the result, unscaled (objects.py:208) */
+    int32_t* d_status;       /* [n_cand]   SDSM_ST_* */
+    int32_t* d_info;         /* [n_cand*8] m, iterations (elliptical pass 1, pass 2, DSM), #fg pixels, cvxopt status
+                                           bits, compacted box h', w' */
+    double*  d_params;       /* [params_len] (theta, xi) of candidate c at cands[c].par_off, 6 + m values */
+    int32_t* d_fgbox;        /* [n_cand*4] rmin, rmax, cmin, cmax of the foreground inside the bounding box, -1 if none */
+    uint8_t* d_onboundary;   /* [n_cand]   objects.py:209 */
+    uint8_t* d_fgmask;       /* [fgmask_len] (S > 0) AND omega over the candidate's bounding box (objects.py:200-204) */
+} sdsm_out;
+
+typedef struct sdsm_ctx sdsm_ctx;
+
+int         sdsm_abi_version(void);
+int         sdsm_create(sdsm_ctx** ctx, int device);
+void        sdsm_destroy(sdsm_ctx* ctx);
+const char* sdsm_last_error(const sdsm_ctx* ctx);
+
+/* y: float64 HxW offset image (Image.model); atoms: int32 HxW atom labels with every pixel outside
+ * y_mask AND (EDT(y <= 0) <= background_margin) set to 0 (objects.py:126-127, candidate-independent part). */
+int sdsm_set_image(sdsm_ctx* ctx, const double* d_y, const int32_t* d_atoms, int32_t H, int32_t W);
+int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* params);
+
+/* fills the offset fields of h_cands[0..n_cand) and the plan; host-only, no CUDA call */
+int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* h_cands, int32_t n_cand, sdsm_plan* plan);
+
+/* d_cands / d_footprints / d_order: device copies of the planned candidates, the footprint labels and the processing
+ * order (a permutation of 0..n_cand-1, most expensive first).  stream is a cudaStream_t. */
+int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t n_cand,
+                     const int32_t* d_footprints, const int32_t* d_order,
+                     void* d_workspace, size_t workspace_bytes, const sdsm_out* out, void* stream);
+
+/* Diagnostics for the parity tests: evaluates psi, grad psi and the lower triangle of the Hessian of candidate c of the
+ * LAST solved batch (same workspace, still intact) at the given parameters; d_H is N x N row-major, N = 6 + m. */
+int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, const double* d_x,
+                        double* d_value, double* d_grad, double* d_H, void* d_workspace, void* stream);
+
+/* Diagnostics: exports the smooth matrix G~ of candidate c of the last batch as dense rows in the solver's pixel order:
+ * d_rc[n] = compacted (row | col << 16), d_cols[n * 25] grid index or -1, d_vals[n * 25]; d_grid[m] = (row | col << 16). */
+int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, uint32_t* d_rc,
+                       int32_t* d_cols, float* d_vals, uint32_t* d_grid, void* d_workspace, void* stream);
+
+/* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
+int64_t sdsm_launch_count(const sdsm_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

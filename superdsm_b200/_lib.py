@@ -1,0 +1,73 @@
+"""ctypes binding of ``include/superdsm_b200.h``.  There is no fallback: if the CUDA library is missing the import of
+the solver fails loudly."""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, 'libsuperdsm_b200.so')
+
+SDSM_OK = 0
+ST_OPTIMAL, ST_FALLBACK, ST_SKIPPED, ST_ERROR, ST_BADREGION = range(5)
+
+#: numpy mirror of ``struct sdsm_cand``
+CAND_DTYPE = np.dtype([('r0', '<i4'), ('c0', '<i4'), ('h', '<i4'), ('w', '<i4'), ('fp_off', '<i4'), ('fp_len', '<i4'),
+                       ('n', '<i4'), ('cell_cap', '<i4'), ('pix_off', '<i8'), ('cell_off', '<i8'), ('tab_off', '<i8'),
+                       ('par_off', '<i8'), ('fg_off', '<i8')], align=True)
+assert CAND_DTYPE.itemsize == 72
+
+
+class Params(ctypes.Structure):
+    _fields_ = [('alpha', ctypes.c_double), ('epsilon', ctypes.c_double), ('scale', ctypes.c_double),
+                ('sparsity_tol', ctypes.c_double), ('subsample', ctypes.c_int32), ('radius', ctypes.c_int32),
+                ('has_smooth', ctypes.c_int32), ('init_elliptical', ctypes.c_int32), ('h_psf', ctypes.c_void_p),
+                ('maxiters', ctypes.c_int32), ('reserved', ctypes.c_int32), ('abstol', ctypes.c_double),
+                ('reltol', ctypes.c_double), ('feastol', ctypes.c_double)]
+
+
+class Plan(ctypes.Structure):
+    _fields_ = [('workspace_bytes', ctypes.c_size_t), ('params_len', ctypes.c_int64), ('fgmask_len', ctypes.c_int64),
+                ('n_max', ctypes.c_int32), ('cells_max', ctypes.c_int32), ('solver_ctas', ctypes.c_int32),
+                ('reserved', ctypes.c_int32)]
+
+
+class Out(ctypes.Structure):
+    _fields_ = [('d_energy', ctypes.c_void_p), ('d_status', ctypes.c_void_p), ('d_info', ctypes.c_void_p),
+                ('d_params', ctypes.c_void_p), ('d_fgbox', ctypes.c_void_p), ('d_onboundary', ctypes.c_void_p),
+                ('d_fgmask', ctypes.c_void_p)]
+
+
+EXPORTS = ('sdsm_abi_version', 'sdsm_create', 'sdsm_destroy', 'sdsm_last_error', 'sdsm_set_image', 'sdsm_set_params',
+           'sdsm_plan_batch', 'sdsm_solve_batch', 'sdsm_eval_candidate', 'sdsm_export_smooth', 'sdsm_launch_count')
+
+_lib = None
+
+
+def load():
+    """Loads the shared library (once).  Raises if it has not been built: there is no CPU path."""
+    global _lib
+    if _lib is not None: return _lib
+    if not os.path.isfile(LIB_PATH):
+        raise ImportError(f'{LIB_PATH} is missing: build it with `python -m superdsm_b200.build` (needs nvcc); '
+                          'superdsm_b200 has no CPU fallback')
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, i32, i64 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64
+    lib.sdsm_abi_version.restype = ctypes.c_int
+    lib.sdsm_create.argtypes = [ctypes.POINTER(vp), ctypes.c_int]
+    lib.sdsm_destroy.argtypes = [vp]
+    lib.sdsm_destroy.restype = None
+    lib.sdsm_last_error.argtypes = [vp]
+    lib.sdsm_last_error.restype = ctypes.c_char_p
+    lib.sdsm_set_image.argtypes = [vp, vp, vp, i32, i32]
+    lib.sdsm_set_params.argtypes = [vp, ctypes.POINTER(Params)]
+    lib.sdsm_plan_batch.argtypes = [vp, vp, i32, ctypes.POINTER(Plan)]
+    lib.sdsm_solve_batch.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, ctypes.c_size_t, ctypes.POINTER(Out), vp]
+    lib.sdsm_eval_candidate.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.sdsm_export_smooth.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.sdsm_launch_count.argtypes = [vp]
+    lib.sdsm_launch_count.restype = i64
+    if lib.sdsm_abi_version() != 1:
+        raise ImportError('libsuperdsm_b200.so: ABI version mismatch')
+    _lib = lib
+    return lib

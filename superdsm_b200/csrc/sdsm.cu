@@ -1,0 +1,226 @@
+// C ABI of the superdsm_b200 library (see include/superdsm_b200.h).  Host side: argument checks, workspace layout,
+// kernel launches on the caller's stream.  No per-batch allocation, no synchronisation.
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "common.cuh"
+#include "pack.cuh"
+#include "grid.cuh"
+#include "solver.cuh"
+
+using namespace sdsm;
+
+struct sdsm_ctx {
+    int device = 0;
+    int sm_count = 148;
+    Img img{nullptr, nullptr, 0, 0};
+    Par par{};
+    bool have_par = false;
+    float* d_psf = nullptr;
+    size_t psf_cap = 0;
+    int64_t launches = 0;
+    // totals of the last plan (the layout is a pure function of these)
+    int64_t P = 0, C = 0, T = 0;
+    int32_t n_cand = 0;
+    std::string err;
+};
+
+#define CUDA_TRY(ctx, expr)                                                                      \
+    do {                                                                                         \
+        cudaError_t e_ = (expr);                                                                 \
+        if (e_ != cudaSuccess) {                                                                 \
+            (ctx)->err = std::string(#expr) + ": " + cudaGetErrorString(e_);                     \
+            return SDSM_E_CUDA;                                                                  \
+        }                                                                                        \
+    } while (0)
+
+extern "C" int sdsm_abi_version(void) { return SDSM_ABI_VERSION; }
+
+extern "C" int sdsm_create(sdsm_ctx** out, int device)
+{
+    if (!out) return SDSM_E_ARG;
+    sdsm_ctx* ctx = new (std::nothrow) sdsm_ctx();
+    if (!ctx) return SDSM_E_ARG;
+    ctx->device = device;
+    *out = ctx;
+    CUDA_TRY(ctx, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    if (prop.major < 10) { ctx->err = "superdsm_b200 is built for sm_100a (B200) only"; return SDSM_E_UNSUPPORTED; }
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
+    return SDSM_OK;
+}
+
+extern "C" void sdsm_destroy(sdsm_ctx* ctx)
+{
+    if (!ctx) return;
+    if (ctx->d_psf) { cudaSetDevice(ctx->device); cudaFree(ctx->d_psf); }
+    delete ctx;
+}
+
+extern "C" const char* sdsm_last_error(const sdsm_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+extern "C" int64_t sdsm_launch_count(const sdsm_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int sdsm_set_image(sdsm_ctx* ctx, const double* d_y, const int32_t* d_atoms, int32_t H, int32_t W)
+{
+    if (!ctx || !d_y || !d_atoms || H < 2 || W < 2) return SDSM_E_ARG;
+    if (H > 65535 || W > 65535) { ctx->err = "image larger than 65535 pixels in a dimension"; return SDSM_E_UNSUPPORTED; }
+    ctx->img = Img{d_y, d_atoms, H, W};
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* p)
+{
+    if (!ctx || !p) return SDSM_E_ARG;
+    if (!(p->epsilon > 0) || !(p->alpha >= 0) || !(p->scale > 0) || p->subsample < 1 || !(p->sparsity_tol >= 0)) {
+        ctx->err = "bad hyper-parameters (epsilon > 0, alpha >= 0, scale > 0, smooth_subsample >= 1, sparsity_tol >= 0)";
+        return SDSM_E_ARG;
+    }
+    Par par{};
+    par.alpha = p->alpha; par.epsilon = p->epsilon; par.scale = p->scale; par.sparsity_tol = p->sparsity_tol;
+    par.abstol = p->abstol; par.reltol = p->reltol; par.feastol = p->feastol;
+    par.sub = p->subsample; par.R = p->radius; par.has_smooth = p->has_smooth; par.init_elliptical = p->init_elliptical;
+    par.maxiters = p->maxiters;
+    par.psf = nullptr;
+    if (p->has_smooth) {
+        if (!p->h_psf || p->radius < 1) return SDSM_E_ARG;
+        // a pixel only searches the 5 x 5 cells around its own for grid points: needs ceil(R / subsample) <= 2;
+        // subsample <= R + 1 is what keeps every row of G~ non-empty in the reference (dsm.py:194)
+        if ((p->radius + p->subsample - 1) / p->subsample > NC) {
+            ctx->err = "kernel radius larger than 2 * smooth_subsample is not implemented";
+            return SDSM_E_UNSUPPORTED;
+        }
+        if (p->radius > 255) { ctx->err = "kernel radius > 255 is not implemented"; return SDSM_E_UNSUPPORTED; }
+        const size_t bytes = sizeof(float) * (size_t)(p->radius + 1) * (p->radius + 1);
+        CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+        if (bytes > ctx->psf_cap) {
+            if (ctx->d_psf) CUDA_TRY(ctx, cudaFree(ctx->d_psf));
+            ctx->d_psf = nullptr; ctx->psf_cap = 0;
+            CUDA_TRY(ctx, cudaMalloc(&ctx->d_psf, bytes));
+            ctx->psf_cap = bytes;
+        }
+        CUDA_TRY(ctx, cudaMemcpy(ctx->d_psf, p->h_psf, bytes, cudaMemcpyHostToDevice));
+        par.psf = ctx->d_psf;
+    } else {
+        // the cells only organise the pixels when there is no smooth matrix
+        if (par.sub < 4) par.sub = 16;
+    }
+    ctx->par = par;
+    ctx->have_par = true;
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, sdsm_plan* plan)
+{
+    if (!ctx || !cands || !plan || n_cand < 1) return SDSM_E_ARG;
+    if (!ctx->have_par || !ctx->img.y) { ctx->err = "sdsm_set_image / sdsm_set_params must precede sdsm_plan_batch"; return SDSM_E_ARG; }
+    const int sub = ctx->par.sub;
+    int64_t P = 0, C = 0, T = 0, PAR = 0, FG = 0;
+    int32_t n_max = 6, cells_max = 1;
+    for (int32_t i = 0; i < n_cand; ++i) {
+        sdsm_cand& c = cands[i];
+        if (c.h < 1 || c.w < 1 || c.n < 1 || c.r0 < 0 || c.c0 < 0 || c.r0 + c.h > ctx->img.H || c.c0 + c.w > ctx->img.W || c.fp_len < 1) {
+            ctx->err = "candidate " + std::to_string(i) + ": empty region or bounding box outside the image";
+            return SDSM_E_ARG;
+        }
+        const int32_t cap = ((c.h + sub - 1) / sub) * ((c.w + sub - 1) / sub);
+        c.cell_cap = cap;
+        c.pix_off = P;  P += (c.n + 31) / 32 * 32;
+        c.cell_off = C; C += cap + 1;
+        c.tab_off = T;  T += (c.h + c.w + 3) / 4 * 4;
+        c.par_off = PAR; PAR += 6 + (ctx->par.has_smooth ? cap : 0);
+        c.fg_off = FG;  FG += (int64_t)c.h * c.w;
+        const int32_t nmax_c = 6 + (ctx->par.has_smooth ? cap : 0);
+        if (nmax_c > n_max) n_max = nmax_c;
+        if (cap > cells_max) cells_max = cap;
+    }
+    // persistent solver grid: two CTAs per SM, fewer if the per-CTA workspace of this batch is large
+    int ctas = 2 * ctx->sm_count;
+    if (ctas > n_cand) ctas = n_cand;
+    Layout L = make_layout(P, C, T, n_cand, n_max, cells_max, 1);
+    const size_t budget = (size_t)12 << 30;
+    if (L.cta_bytes * (size_t)ctas > budget) {
+        ctas = (int)(budget / L.cta_bytes);
+        if (ctas < 1) ctas = 1;
+    }
+    L = make_layout(P, C, T, n_cand, n_max, cells_max, ctas);
+    plan->workspace_bytes = L.total;
+    plan->params_len = PAR;
+    plan->fgmask_len = FG;
+    plan->n_max = n_max;
+    plan->cells_max = cells_max;
+    plan->solver_ctas = ctas;
+    plan->reserved = 0;
+    ctx->P = P; ctx->C = C; ctx->T = T; ctx->n_cand = n_cand;
+    return SDSM_OK;
+}
+
+static int check_plan(sdsm_ctx* ctx, const sdsm_plan* plan, int32_t n_cand, size_t workspace_bytes, Layout* L)
+{
+    if (n_cand != ctx->n_cand) { ctx->err = "batch does not match the last sdsm_plan_batch"; return SDSM_E_ARG; }
+    *L = make_layout(ctx->P, ctx->C, ctx->T, n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    if (L->total > workspace_bytes) { ctx->err = "workspace too small"; return SDSM_E_WORKSPACE; }
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t n_cand,
+                                const int32_t* d_footprints, const int32_t* d_order, void* d_workspace, size_t workspace_bytes,
+                                const sdsm_out* out, void* stream_)
+{
+    if (!ctx || !plan || !d_cands || !d_footprints || !d_order || !d_workspace || !out) return SDSM_E_ARG;
+    if (!out->d_energy || !out->d_status || !out->d_info || !out->d_params || !out->d_fgbox || !out->d_onboundary || !out->d_fgmask) return SDSM_E_ARG;
+    Layout L;
+    int rc = check_plan(ctx, plan, n_cand, workspace_bytes, &L);
+    if (rc) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    WS ws = make_ws(d_workspace, L);
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(int32_t) * 16, stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(out->d_fgmask, 0, (size_t)plan->fgmask_len, stream));
+
+    const int pack_grid = n_cand < 8 * ctx->sm_count ? n_cand : 8 * ctx->sm_count;
+    k_pack<<<pack_grid, PACK_BLOCK, 0, stream>>>(ctx->img, ctx->par, d_cands, n_cand, d_footprints, ws);
+    ctx->launches++;
+    if (ctx->par.has_smooth) {
+        const size_t psf_bytes = sizeof(float) * (size_t)(ctx->par.R + 1) * (ctx->par.R + 1);
+        if (psf_bytes > 48 * 1024)
+            CUDA_TRY(ctx, cudaFuncSetAttribute(k_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psf_bytes));
+        k_grid<<<pack_grid, GRID_BLOCK, psf_bytes, stream>>>(ctx->par, d_cands, n_cand, d_order, ws);
+        ctx->launches++;
+    }
+    k_solve<<<plan->solver_ctas, SOLVER_BLOCK, SOLVER_SMEM, stream>>>(ctx->img, ctx->par, d_cands, n_cand, d_order, ws, *out);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, const double* d_x,
+                                   double* d_value, double* d_grad, double* d_H, void* d_workspace, void* stream_)
+{
+    if (!ctx || !plan || !d_cands || !d_x || !d_value || !d_grad || !d_H || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
+    Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    WS ws = make_ws(d_workspace, L);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    k_eval<<<1, SOLVER_BLOCK, SOLVER_SMEM, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, ws, d_x, d_value, d_grad, d_H);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, uint32_t* d_rc,
+                                  int32_t* d_cols, float* d_vals, uint32_t* d_grid, void* d_workspace, void* stream_)
+{
+    if (!ctx || !plan || !d_cands || !d_rc || !d_cols || !d_vals || !d_grid || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
+    Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    WS ws = make_ws(d_workspace, L);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    k_export<<<64, 128, 0, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, ws, d_rc, d_cols, d_vals, d_grid);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}

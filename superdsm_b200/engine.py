@@ -1,0 +1,335 @@
+"""Host driver of the CUDA solver: owns the device buffers (torch tensors), prepares the candidate descriptors and
+calls through the C ABI (``include/superdsm_b200.h``).  One ``Engine`` per device; one process per GPU.
+
+PyTorch is used for device memory, pinned staging buffers and streams only.  There is no CPU path.
+"""
+import ctypes
+import time
+
+import numpy as np
+import scipy.ndimage as ndi
+
+from . import _lib
+
+
+class SolverError(RuntimeError):
+    pass
+
+
+def gaussian_psf32(smooth_amount, gaussian_shape_multiplier):
+    """The float32 Gaussian kernel of the reference (``dsm.py:137-142,226``) and its radius R.
+
+    Built exactly as the reference builds it (``scipy.ndimage.gaussian_filter`` of a centred delta), so the values are
+    bit-identical by construction; the device receives the quarter ``psf[R:, R:]`` of the symmetric box.
+    """
+    size = round(1 + smooth_amount * 4 * gaussian_shape_multiplier)
+    assert size % 2 == 1, size                              # dsm.py:147
+    inp = np.zeros((size, size))
+    inp[size // 2, size // 2] = 1
+    psf = ndi.gaussian_filter(inp, smooth_amount).astype(np.float32)
+    R = size // 2
+    if not (np.array_equal(psf, psf[::-1, :]) and np.array_equal(psf, psf[:, ::-1])):
+        raise SolverError('asymmetric Gaussian kernel: not supported')
+    return np.ascontiguousarray(psf[R:, R:]), R
+
+
+def lpt_shards(costs, n_shards):
+    """Longest-processing-time assignment of candidates to shards (ranks); returns a list of index arrays."""
+    order = np.argsort(-np.asarray(costs, dtype=float), kind='stable')
+    loads = np.zeros(n_shards)
+    shards = [[] for _ in range(n_shards)]
+    for k in order:
+        r = int(np.argmin(loads))
+        shards[r].append(int(k))
+        loads[r] += costs[k]
+    return [np.array(sorted(s), dtype=np.int64) for s in shards]
+
+
+def prepare_image(y_model, y_mask, atoms, background_margin):
+    """Host-side, once per image: the candidate-independent part of ``Object.get_cvxprog_region`` (objects.py:126-127).
+
+    A pixel is usable iff ``y_mask`` and ``EDT(y <= 0) <= background_margin``; unusable pixels get atom label 0, so that a
+    candidate's region is simply {pixels whose label is in its footprint}.  Returns the masked atoms map (int32), the
+    number of usable pixels per label and the bounding box (r0, r1, c0, c1; end-exclusive) of each label's usable pixels.
+    """
+    atoms = np.asarray(atoms)
+    assert y_model.ndim == 2 and atoms.shape == y_model.shape and y_mask.shape == y_model.shape
+    usable = np.logical_and(y_mask, ndi.distance_transform_edt(y_model <= 0) <= background_margin)
+    atoms_v = np.where(usable, atoms, 0).astype(np.int32)
+    n_labels = int(atoms.max()) if atoms.size else 0
+    count = np.bincount(atoms_v.reshape(-1), minlength=n_labels + 1).astype(np.int64)
+    count[0] = 0
+    box = np.zeros((n_labels + 1, 4), dtype=np.int64)
+    for lab, sl in enumerate(ndi.find_objects(atoms_v, max_label=n_labels), start=1):
+        if sl is not None: box[lab] = (sl[0].start, sl[0].stop, sl[1].start, sl[1].stop)
+    return atoms_v, count, box
+
+
+def describe_candidates(atom_count, atom_box, footprints):
+    """Candidate descriptors (``sdsm_cand``: bounding box, pixel count, footprint slice) and the flat footprint array."""
+    n = len(footprints)
+    lens = np.fromiter((len(fp) for fp in footprints), dtype=np.int64, count=n)
+    if n == 0 or (lens < 1).any(): raise SolverError('empty batch or empty footprint')
+    flat = np.fromiter((lab for fp in footprints for lab in sorted(fp)), dtype=np.int64, count=int(lens.sum()))
+    if flat.min() < 1 or flat.max() >= len(atom_count):
+        raise SolverError('footprint label outside the atoms map')
+    offs = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64)
+    cnt = atom_count[flat]
+    box = atom_box[flat]
+    big = np.iinfo(np.int64).max
+    present = cnt > 0
+    r0 = np.minimum.reduceat(np.where(present, box[:, 0], big), offs)
+    r1 = np.maximum.reduceat(np.where(present, box[:, 1], 0), offs)
+    c0 = np.minimum.reduceat(np.where(present, box[:, 2], big), offs)
+    c1 = np.maximum.reduceat(np.where(present, box[:, 3], 0), offs)
+    npix = np.add.reduceat(cnt, offs)
+    if (npix < 1).any():
+        raise SolverError(f'candidate {int(np.argmax(npix < 1))} has no usable pixel')
+    cands = np.zeros(n, dtype=_lib.CAND_DTYPE)
+    cands['r0'], cands['c0'], cands['h'], cands['w'] = r0, c0, r1 - r0, c1 - c0
+    cands['fp_off'], cands['fp_len'], cands['n'] = offs, lens, npix
+    return cands, flat.astype(np.int32)
+
+
+class BatchResult(object):
+    """Raw per-candidate results of one batch (host numpy arrays)."""
+
+    def __init__(self, cands, energy, status, info, params, fgbox, on_boundary, fgmask, elapsed):
+        self.cands, self.energy, self.status, self.info = cands, energy, status, info
+        self.params_flat, self.fgbox, self.on_boundary, self.fgmask = params, fgbox, on_boundary, fgmask
+        self.elapsed = elapsed
+
+    def __len__(self): return len(self.cands)
+
+    def m(self, k): return int(self.info[k, 0])
+
+    def params(self, k):
+        off = int(self.cands['par_off'][k])
+        return self.params_flat[off:off + 6 + self.m(k)].copy()
+
+    def foreground(self, k):
+        """(fg_offset, fg_fragment) as ``objects.extract_foreground_fragment`` returns them (objects.py:148-174)."""
+        rmin, rmax, cmin, cmax = (int(v) for v in self.fgbox[k])
+        if rmax < 0: return np.zeros(2, int), np.zeros((1, 1), bool)
+        cd = self.cands[k]
+        h, w, off = int(cd['h']), int(cd['w']), int(cd['fg_off'])
+        box = self.fgmask[off:off + h * w].reshape(h, w)
+        return np.array([int(cd['r0']) + rmin, int(cd['c0']) + cmin]), box[rmin:rmax + 1, cmin:cmax + 1].astype(bool)
+
+
+class Engine(object):
+    """One device context of the CUDA solver."""
+
+    def __init__(self, device=0):
+        import torch
+        if not torch.cuda.is_available():
+            raise SolverError('superdsm_b200 needs a CUDA device (B200); there is no CPU fallback')
+        self.torch = torch
+        self.lib = _lib.load()
+        self.device = torch.device('cuda', device)
+        self.device_index = device
+        self.ctx = ctypes.c_void_p()
+        rc = self.lib.sdsm_create(ctypes.byref(self.ctx), device)
+        self._check(rc)
+        self.stream = torch.cuda.Stream(device=self.device)
+        self._image_key = None
+        self._params_key = None
+        self._bufs = {}
+        self._last = None
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    def close(self):
+        if self.ctx:
+            self.torch.cuda.synchronize(self.device)
+            self.lib.sdsm_destroy(self.ctx)
+            self.ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try: self.close()
+        except Exception: pass
+
+    def _check(self, rc):
+        if rc != _lib.SDSM_OK:
+            msg = self.lib.sdsm_last_error(self.ctx)
+            raise SolverError(f'superdsm_b200 error {rc}: {msg.decode() if msg else ""}')
+
+    @property
+    def launch_count(self):
+        return int(self.lib.sdsm_launch_count(self.ctx))
+
+    # -- buffers -------------------------------------------------------------------------------------------------
+
+    def _buf(self, name, nbytes, pinned=False):
+        """Grow-only byte buffers, device or pinned host."""
+        torch = self.torch
+        cur = self._bufs.get(name)
+        if cur is None or cur.numel() < nbytes:
+            cap = max(int(nbytes * 1.25), 1024)
+            if pinned: cur = torch.empty(cap, dtype=torch.uint8, pin_memory=True)
+            else: cur = torch.empty(cap, dtype=torch.uint8, device=self.device)
+            self._bufs[name] = cur
+        return cur
+
+    def _upload(self, name, array):
+        """numpy -> pinned staging -> device, on the engine's stream.  Returns the device byte tensor."""
+        torch = self.torch
+        array = np.ascontiguousarray(array)
+        nbytes = array.nbytes
+        self.stream.synchronize()                      # the staging buffer may still feed an earlier copy
+        host = self._buf('h_' + name, nbytes, pinned=True)
+        host[:nbytes].numpy()[:] = array.reshape(-1).view(np.uint8)
+        dev = self._buf('d_' + name, nbytes)
+        with torch.cuda.stream(self.stream):
+            dev[:nbytes].copy_(host[:nbytes], non_blocking=True)
+        self.h2d_bytes += nbytes
+        return dev
+
+    # -- per image -----------------------------------------------------------------------------------------------
+
+    def set_image(self, y_model, y_mask, atoms, background_margin):
+        """Uploads the offset image and the atoms map (see :func:`prepare_image`)."""
+        y_model = np.ascontiguousarray(y_model, dtype=np.float64)
+        atoms_v, self.atom_count, self.atom_box = prepare_image(y_model, y_mask, atoms, background_margin)
+        H, W = y_model.shape
+        self.shape = (H, W)
+        d_y = self._upload('y', y_model)
+        d_atoms = self._upload('atoms', atoms_v)
+        self._check(self.lib.sdsm_set_image(self.ctx, d_y.data_ptr(), d_atoms.data_ptr(), H, W))
+        self._last = None
+
+    def set_params(self, dsm_cfg):
+        """``dsm_cfg`` is the dictionary of ``dsmcfg.py:82-89``."""
+        cfg = dict(dsm_cfg)
+        if cfg.get('smooth_mat_dtype', 'float32') != 'float32':
+            raise SolverError('only dsm/smooth_mat_dtype = float32 (the default) is implemented')
+        if callable(cfg.get('init')):
+            raise SolverError('callable dsm/init is not implemented on the device')
+        key = tuple(sorted((k, str(v)) for k, v in cfg.items() if k in
+                           ('alpha', 'epsilon', 'scale', 'sparsity_tol', 'smooth_amount', 'smooth_subsample',
+                            'gaussian_shape_multiplier', 'init')))
+        if key == self._params_key: return
+        p = _lib.Params()
+        p.alpha, p.epsilon, p.scale = float(cfg['alpha']), float(cfg['epsilon']), float(cfg['scale'])
+        p.sparsity_tol = float(cfg.get('sparsity_tol', 0))
+        p.subsample = int(cfg['smooth_subsample']) if np.isfinite(cfg['smooth_subsample']) else 16
+        p.init_elliptical = 1 if cfg.get('init', 'elliptical') == 'elliptical' else 0
+        p.maxiters, p.abstol, p.reltol, p.feastol = 100, 1e-7, 1e-6, 1e-7      # cvxopt defaults (never changed by the reference)
+        self._psf = None
+        if cfg['smooth_amount'] < np.inf:
+            self._psf, R = gaussian_psf32(cfg['smooth_amount'], cfg['gaussian_shape_multiplier'])
+            p.has_smooth, p.radius = 1, R
+            p.h_psf = self._psf.ctypes.data
+        else:
+            p.has_smooth, p.radius, p.h_psf = 0, 0, None
+        self._check(self.lib.sdsm_set_params(self.ctx, ctypes.byref(p)))
+        self._params_key = key
+        self._last = None
+
+    # -- per batch -----------------------------------------------------------------------------------------------
+
+    def describe(self, footprints):
+        return describe_candidates(self.atom_count, self.atom_box, footprints)
+
+    def solve(self, footprints, keep_device_state=False):
+        """Fits every candidate of the batch; returns a :class:`BatchResult`."""
+        torch, lib = self.torch, self.lib
+        t0 = time.perf_counter()
+        cands, flat = self.describe(footprints)
+        n = len(cands)
+        plan = _lib.Plan()
+        self._check(lib.sdsm_plan_batch(self.ctx, cands.ctypes.data, n, ctypes.byref(plan)))
+        # most expensive first: the persistent solver pulls candidates from a queue
+        cost = cands['n'].astype(np.float64) * (1.0 + 0.02 * cands['cell_cap'])
+        order = np.argsort(-cost, kind='stable').astype(np.int32)
+        d_cands = self._upload('cands', cands)
+        d_fp = self._upload('fp', flat)
+        d_order = self._upload('order', order)
+        ws = self._buf('d_ws', plan.workspace_bytes)
+        sizes = dict(energy=8 * n, status=4 * n, info=32 * n, params=8 * plan.params_len, fgbox=16 * n, onb=n, fgmask=plan.fgmask_len)
+        dev = {k: self._buf('d_out_' + k, v) for k, v in sizes.items()}
+        out = _lib.Out(dev['energy'].data_ptr(), dev['status'].data_ptr(), dev['info'].data_ptr(), dev['params'].data_ptr(),
+                       dev['fgbox'].data_ptr(), dev['onb'].data_ptr(), dev['fgmask'].data_ptr())
+        self._check(lib.sdsm_solve_batch(self.ctx, ctypes.byref(plan), d_cands.data_ptr(), n, d_fp.data_ptr(), d_order.data_ptr(),
+                                         ws.data_ptr(), ws.numel(), ctypes.byref(out), self.stream.cuda_stream))
+        host = {}
+        with torch.cuda.stream(self.stream):
+            for k, v in sizes.items():
+                h = self._buf('h_out_' + k, v, pinned=True)
+                h[:v].copy_(dev[k][:v], non_blocking=True)
+                host[k] = h
+                self.d2h_bytes += v
+        self.stream.synchronize()
+        res = BatchResult(cands,
+                          host['energy'][:sizes['energy']].numpy().view(np.float64).copy(),
+                          host['status'][:sizes['status']].numpy().view(np.int32).copy(),
+                          host['info'][:sizes['info']].numpy().view(np.int32).reshape(n, 8).copy(),
+                          host['params'][:sizes['params']].numpy().view(np.float64).copy(),
+                          host['fgbox'][:sizes['fgbox']].numpy().view(np.int32).reshape(n, 4).copy(),
+                          host['onb'][:n].numpy().copy(),
+                          host['fgmask'][:sizes['fgmask']].numpy().copy(),
+                          time.perf_counter() - t0)
+        self._last = (plan, d_cands, ws, cands)
+        return res
+
+    # -- device-resident variant used by bench.py: inputs already in HBM, outputs stay there -------------------------
+
+    def prepare(self, footprints):
+        """Uploads a batch and returns a handle for :meth:`run_prepared` (no host work inside the timed region)."""
+        cands, flat = self.describe(footprints)
+        n = len(cands)
+        plan = _lib.Plan()
+        self._check(self.lib.sdsm_plan_batch(self.ctx, cands.ctypes.data, n, ctypes.byref(plan)))
+        cost = cands['n'].astype(np.float64) * (1.0 + 0.02 * cands['cell_cap'])
+        order = np.argsort(-cost, kind='stable').astype(np.int32)
+        torch = self.torch
+        to_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).reshape(-1).view(np.uint8).copy()).to(self.device)
+        h = dict(plan=plan, n=n, cands=cands, d_cands=to_dev(cands), d_fp=to_dev(flat), d_order=to_dev(order))
+        h['ws'] = torch.empty(plan.workspace_bytes, dtype=torch.uint8, device=self.device)
+        sizes = dict(energy=8 * n, status=4 * n, info=32 * n, params=8 * plan.params_len, fgbox=16 * n, onb=n, fgmask=plan.fgmask_len)
+        h['out'] = {k: torch.empty(max(v, 8), dtype=torch.uint8, device=self.device) for k, v in sizes.items()}
+        o = h['out']
+        h['out_struct'] = _lib.Out(o['energy'].data_ptr(), o['status'].data_ptr(), o['info'].data_ptr(), o['params'].data_ptr(),
+                                   o['fgbox'].data_ptr(), o['onb'].data_ptr(), o['fgmask'].data_ptr())
+        torch.cuda.synchronize(self.device)
+        return h
+
+    def run_prepared(self, h, stream=None):
+        stream = stream if stream is not None else self.torch.cuda.current_stream(self.device)
+        self._check(self.lib.sdsm_solve_batch(self.ctx, ctypes.byref(h['plan']), h['d_cands'].data_ptr(), h['n'], h['d_fp'].data_ptr(),
+                                              h['d_order'].data_ptr(), h['ws'].data_ptr(), h['ws'].numel(),
+                                              ctypes.byref(h['out_struct']), stream.cuda_stream))
+        self._last = (h['plan'], h['d_cands'], h['ws'], h['cands'])
+
+    # -- diagnostics (parity tests) ----------------------------------------------------------------------------------
+
+    def eval_candidate(self, k, params):
+        """psi, grad psi, Hessian of candidate ``k`` of the last batch at ``params`` (device evaluation)."""
+        torch = self.torch
+        plan, d_cands, ws, cands = self._last
+        params = np.ascontiguousarray(params, dtype=np.float64)
+        N = len(params)
+        d_x = torch.from_numpy(params).to(self.device)
+        d_val = torch.zeros(1, dtype=torch.float64, device=self.device)
+        d_g = torch.zeros(N, dtype=torch.float64, device=self.device)
+        d_H = torch.zeros(N * N, dtype=torch.float64, device=self.device)
+        torch.cuda.synchronize(self.device)
+        self._check(self.lib.sdsm_eval_candidate(self.ctx, ctypes.byref(plan), d_cands.data_ptr(), k, d_x.data_ptr(), d_val.data_ptr(),
+                                                 d_g.data_ptr(), d_H.data_ptr(), ws.data_ptr(), self.stream.cuda_stream))
+        self.stream.synchronize()
+        return float(d_val.item()), d_g.cpu().numpy(), d_H.cpu().numpy().reshape(N, N)
+
+    def export_smooth(self, k, n, m):
+        """G~ of candidate ``k`` of the last batch: (pixel rc [n], cols [n, 25], vals [n, 25], grid rc [m])."""
+        torch = self.torch
+        plan, d_cands, ws, cands = self._last
+        d_rc = torch.zeros(n, dtype=torch.int32, device=self.device)
+        d_cols = torch.full((n * 25,), -1, dtype=torch.int32, device=self.device)
+        d_vals = torch.zeros(n * 25, dtype=torch.float32, device=self.device)
+        d_grid = torch.zeros(max(m, 1), dtype=torch.int32, device=self.device)
+        torch.cuda.synchronize(self.device)
+        self._check(self.lib.sdsm_export_smooth(self.ctx, ctypes.byref(plan), d_cands.data_ptr(), k, d_rc.data_ptr(), d_cols.data_ptr(),
+                                                d_vals.data_ptr(), d_grid.data_ptr(), ws.data_ptr(), self.stream.cuda_stream))
+        self.stream.synchronize()
+        return (d_rc.cpu().numpy().view(np.uint32), d_cols.cpu().numpy().reshape(n, 25), d_vals.cpu().numpy().reshape(n, 25),
+                d_grid.cpu().numpy().view(np.uint32)[:m])

@@ -1,0 +1,164 @@
+"""Parity of the CUDA path (through the C ABI) with the golden vectors of the reference and with the oracle.  -m gpu."""
+import numpy as np
+import pytest
+import scipy.sparse
+
+from tests.golden_util import CASES, GoldenCase, probe_matrix
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def eng():
+    from superdsm_b200.objects import get_engine
+    return get_engine(0)
+
+
+@pytest.fixture(scope='module', params=CASES)
+def solved(request, eng):
+    case = GoldenCase(request.param)
+    eng.set_image(case.y, case.y_mask, case.atoms, case.dsm_cfg['background_margin'])
+    eng.set_params(case.dsm_cfg)
+    res = eng.solve(case.footprints)
+    return case, res
+
+
+def _device_G(eng, case, res, k):
+    """The device's G~ of candidate k as CSR in the reference's row (row-major pixel) and column order."""
+    n, m = int(res.cands['n'][k]), res.m(k)
+    rc, cols, vals, grid = eng.export_smooth(k, n, m)
+    pr, pc = (rc & 0xffff).astype(np.int64), (rc >> 16).astype(np.int64)
+    order = np.lexsort((pc, pr))                      # compacted row-major = the reference's pixel order
+    rows = np.repeat(np.arange(n), 25)
+    keep = (cols.reshape(-1) >= 0) & (vals.reshape(-1) != 0)
+    G = scipy.sparse.csr_matrix((vals.reshape(-1)[keep].astype(np.float64), (rows[keep], cols.reshape(-1)[keep])), shape=(n, m))
+    return G[order], order, grid
+
+
+def test_smooth_matrix_bit_exact(solved, eng):
+    """SmoothMatrixFactory.get (dsm.py:217-235): same sparsity pattern, same float32 values, bit for bit."""
+    case, res = solved
+    for k in range(len(case)):
+        ref = case.G(k)
+        assert res.m(k) == ref.shape[1], (case.name, k)
+        if ref.shape[1] == 0: continue
+        G, _, grid = _device_G(eng, case, res, k)
+        G.sort_indices(); ref.sort_indices()
+        assert np.array_equal(G.indptr, ref.indptr) and np.array_equal(G.indices, ref.indices), (case.name, k)
+        assert np.array_equal(G.data, ref.data), (case.name, k)
+
+
+def test_energy_gradient_hessian(solved, eng):
+    """Energy.__call__/grad/hessian (dsm.py:312-385) at the golden parameter points; tolerance 1e-10 relative."""
+    case, res = solved
+    for k in range(len(case)):
+        if int(res.status[k]) == 2: continue      # skipped (single foreground pixel): never packed for evaluation
+        for pt in case.energy_points(k):
+            val, g, H = eng.eval_candidate(k, pt['p'])
+            assert val == pytest.approx(pt['value'], rel=1e-11, abs=1e-11), (case.name, k)
+            assert np.allclose(g, pt['grad'], rtol=1e-10, atol=1e-10 * max(1, np.abs(pt['grad']).max()))
+            assert np.allclose(H, H.T, rtol=0, atol=0)
+            probe = H @ probe_matrix(len(pt['p']))
+            assert np.allclose(probe, pt['hess_probe'], rtol=1e-9, atol=1e-10 * max(1, np.abs(probe).max()))
+            if pt['hess_lower'] is not None:
+                assert np.allclose(np.tril(H), pt['hess_lower'], rtol=1e-9, atol=1e-12 * max(1, np.abs(H).max()))
+
+
+def test_fit_results_match_reference_driver(solved):
+    """objects._compute_object (objects.py:177-212): energy within 1e-6 relative (north-star tolerance), identical status,
+    boundary flag and foreground mask."""
+    case, res = solved
+    from superdsm_b200 import _lib
+    for k in range(len(case)):
+        ref = case.fit(k)
+        st = int(res.status[k])
+        if st == _lib.ST_SKIPPED:
+            assert float(ref['energy']) == 0.0 and not bool(ref['is_optimal'])
+            continue
+        assert float(res.energy[k]) == pytest.approx(float(ref['energy']), rel=1e-6, abs=1e-9), (case.name, k)
+        assert (st == _lib.ST_OPTIMAL) == bool(ref['is_optimal']) and (st == _lib.ST_FALLBACK) == bool(ref['fallback'])
+        assert bool(res.on_boundary[k]) == bool(ref['on_boundary'])
+        off, frag = res.foreground(k)
+        assert np.array_equal(off, ref['fg_offset']) and np.array_equal(frag, ref['fg_fragment']), (case.name, k)
+
+
+def test_compute_objects_api_against_oracle(eng):
+    """The drop-in seam compute_objects() on the synthetic toy workload, every candidate against the oracle."""
+    from oracle import dsm_oracle as orc
+    from superdsm_b200 import synth
+    from superdsm_b200.image import Image
+    from superdsm_b200.objects import Object, compute_objects
+    w = synth.make_workload('toy', oversegment=2, max_set_size=3)
+    objs = []
+    for fp in w['footprints']:
+        o = Object(); o.footprint = set(fp); objs.append(o)
+    y = Image.create_from_array(w['y'], normalize=False, mask=w['y_mask'])
+    compute_objects(objs, y, w['atoms'], w['dsm_cfg'], None)
+    worst = 0
+    for o in objs:
+        ref = orc.compute_object(w['y'], w['y_mask'], w['atoms'], o.footprint, w['dsm_cfg'])
+        rel = abs(o.energy - ref['energy']) / max(abs(ref['energy']), 1e-9)
+        worst = max(worst, rel)
+        assert rel < 1e-6, (sorted(o.footprint), o.energy, ref['energy'])
+        assert o.is_optimal == ref['is_optimal'] and o.on_boundary == ref['on_boundary']
+        assert np.array_equal(o.fg_offset, ref['fg_offset']) and np.array_equal(o.fg_fragment, ref['fg_fragment'])
+    print('worst relative energy error', worst)
+
+
+def test_iterates_track_the_oracle(solved):
+    """Same interior-point state machine: the device needs the same number of iterations as the restated cp."""
+    from oracle import dsm_oracle as orc
+    case, res = solved
+    for k in range(min(len(case), 4)):
+        if int(res.status[k]) == 2: continue
+        info = {}
+        orc.compute_object(case.y, case.y_mask, case.atoms, case.footprints[k], case.dsm_cfg, info=info)
+        assert info['pass1'][1] == int(res.info[k, 1]), (case.name, k, info, res.info[k])
+        assert info['dsm'][1] == int(res.info[k, 3]), (case.name, k, info, res.info[k])
+
+
+def test_cvxprog_seam_without_deformations(eng):
+    """objects.cvxprog as c2f calls it (smooth_amount = inf, c2freganal.py:126): a 6-parameter fit; optimality certificate
+    and agreement with the oracle."""
+    from oracle import dsm_oracle as orc
+    from superdsm_b200.image import Image
+    from superdsm_b200.objects import cvxprog
+    case = GoldenCase('hand')
+    mask = case.mask(0)
+    cfg = dict(case.dsm_cfg); cfg['smooth_amount'] = np.inf
+    cfg.pop('background_margin')
+    keys = ('scale', 'epsilon', 'alpha', 'smooth_amount', 'smooth_subsample', 'gaussian_shape_multiplier', 'smooth_mat_dtype', 'init')
+    J, model, status = cvxprog(Image(case.y, mask), smooth_mat_allocation_lock=None, **{k: cfg[k] for k in keys})
+    Jo, po, so = orc.cvxprog(case.y, mask, **{k: cfg[k] for k in keys})
+    assert status == so == 'optimal' and J.smooth_mat.shape == (int(mask.sum()), 0)
+    assert J(model) == pytest.approx(Jo(po), rel=1e-9)
+    assert np.allclose(model.array, po, rtol=1e-6, atol=1e-8)
+    assert np.abs(J.grad(model)).max() < 1e-5 * mask.sum()
+    assert J(np.zeros(6)) == pytest.approx(mask.sum() * np.log(2), rel=1e-12)      # psi(0) = n log 2
+
+
+def test_full_size_properties(eng):
+    """BASELINE config 1 (GOWT1-shaped 1024 x 1024): size-independent properties of the solves."""
+    from superdsm_b200 import synth, _lib
+    w = synth.make_workload('gowt1', max_set_size=2)
+    eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
+    eng.set_params(w['dsm_cfg'])
+    fps = w['footprints'][:96]
+    res = eng.solve(fps)
+    res2 = eng.solve(fps)
+    assert np.array_equal(res.energy, res2.energy) and np.array_equal(res.params_flat, res2.params_flat)   # bit-reproducible
+    assert np.array_equal(res.fgmask, res2.fgmask)
+    ok = res.status == _lib.ST_OPTIMAL
+    assert ok.mean() > 0.9
+    for k in np.nonzero(ok)[0][:24]:
+        p = res.params(k)
+        val, g, H = eng.eval_candidate(int(k), p)
+        assert val == pytest.approx(res.energy[k], rel=1e-12)
+        n = int(res.cands['n'][k])
+        assert np.abs(g).max() * (w['dsm_cfg']['scale'] / n) < 1e-4            # stationary: the scaled gradient cvxopt saw
+        assert np.linalg.eigvalsh(H).min() > -1e-9 * np.abs(H).max()          # convex
+        p_ell = np.concatenate([p[:6], np.zeros(len(p) - 6)])
+        assert val <= eng.eval_candidate(int(k), p_ell)[0] + 1e-9             # deformation can only lower the energy
+        assert val <= n * np.log(2) + 1e-9                                    # never worse than the zero model
+        off, frag = res.foreground(k)
+        assert frag.any() and off[0] >= 0 and off[1] >= 0

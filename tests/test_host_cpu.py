@@ -1,0 +1,100 @@
+"""CPU-only checks of the host logic and of the C-ABI library (no compute calls)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from superdsm_b200 import _lib, engine, image, objects, dsm, dsmcfg
+from tests.golden_util import CASES, GoldenCase
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    header = open(os.path.join(ROOT, 'include', 'superdsm_b200.h')).read()
+    declared = set(re.findall(r'\b(sdsm_[a-z_]+)\s*\(', header))
+    assert declared == set(_lib.EXPORTS)
+    lib = _lib.load()
+    for name in declared: assert hasattr(lib, name), name
+    assert lib.sdsm_abi_version() == 1
+
+
+def test_struct_layouts_match_the_header():
+    assert _lib.CAND_DTYPE.itemsize == 72 and _lib.CAND_DTYPE.fields['pix_off'][1] == 32
+    assert ctypes.sizeof(_lib.Params) == 88 and ctypes.sizeof(_lib.Plan) == 40 and ctypes.sizeof(_lib.Out) == 56
+
+
+@pytest.mark.parametrize('name', CASES)
+def test_host_region_descriptors(name):
+    """prepare_image + describe_candidates reproduce Object.get_cvxprog_region (objects.py:95-128) exactly."""
+    c = GoldenCase(name)
+    atoms_v, count, box = engine.prepare_image(c.y, c.y_mask, c.atoms, c.dsm_cfg['background_margin'])
+    cands, flat = engine.describe_candidates(count, box, c.footprints)
+    for k in range(len(c)):
+        mask = c.mask(k)
+        assert np.array_equal(np.isin(atoms_v, sorted(c.footprints[k])), mask)
+        rows, cols = np.nonzero(mask.any(axis=1))[0], np.nonzero(mask.any(axis=0))[0]
+        assert int(cands['n'][k]) == mask.sum()
+        assert (cands['r0'][k], cands['h'][k]) == (rows[0], rows[-1] - rows[0] + 1)
+        assert (cands['c0'][k], cands['w'][k]) == (cols[0], cols[-1] - cols[0] + 1)
+
+
+def test_describe_rejects_bad_footprints():
+    c = GoldenCase('hand')
+    _, count, box = engine.prepare_image(c.y, c.y_mask, c.atoms, 9)
+    with pytest.raises(engine.SolverError): engine.describe_candidates(count, box, [{99}])
+    with pytest.raises(engine.SolverError): engine.describe_candidates(count, box, [set()])
+
+
+def test_psf_quarter_table_is_the_reference_kernel():
+    import scipy.ndimage as ndi
+    q, R = engine.gaussian_psf32(4, 2)
+    assert R == 16 and q.shape == (17, 17) and q.dtype == np.float32
+    inp = np.zeros((33, 33)); inp[16, 16] = 1
+    full = ndi.gaussian_filter(inp, 4).astype(np.float32)
+    for dr in (-16, -3, 0, 5, 16):
+        for dc in (-16, 0, 7): assert full[16 + dr, 16 + dc] == q[abs(dr), abs(dc)]
+    with pytest.raises(AssertionError): engine.gaussian_psf32(3.3, 1)        # even box: dsm.py:147 asserts
+
+
+def test_lpt_shards_balance_and_cover():
+    rng = np.random.default_rng(0)
+    costs = rng.integers(1, 1000, 500).astype(float)
+    shards = engine.lpt_shards(costs, 8)
+    assert sorted(np.concatenate(shards).tolist()) == list(range(500))
+    loads = np.array([costs[s].sum() for s in shards])
+    assert loads.max() / loads.mean() < 1.02
+
+
+def test_reference_unit_fixtures_on_the_mirror():
+    """tests/test_objects.py and tests/test_image.py of the reference, run on the mirrored classes."""
+    obj = objects.BaseObject()
+    obj.fg_fragment = np.array([[False, True], [True, True], [True, False]])
+    obj.fg_offset = (1, 2)
+    actual = np.zeros((4, 5), bool)
+    obj.fill_foreground(actual)
+    expected = np.array([[0, 0, 0, 0, 0], [0, 0, 0, 1, 0], [0, 0, 1, 1, 0], [0, 0, 1, 0, 0]], bool)
+    assert np.array_equal(actual, expected)
+    off, frag = objects.extract_foreground_fragment(expected)
+    assert np.array_equal(off, [1, 2]) and np.array_equal(frag, obj.fg_fragment)
+    o = objects.Object(); o.footprint = {2, 3}
+    assert np.array_equal(o.get_mask(np.array([[1, 1, 2], [1, 3, 2], [3, 3, 3]])), np.array([[0, 0, 1], [0, 1, 1], [1, 1, 1]], bool))
+    y = np.array([[-1] * 5] * 3 + [[-1, 1, -1, -1, -1], [-1, 1, -1, -1, 1], [-1, 1, -1, -1, 1]])
+    atoms = np.array([[1] * 5, [1] * 5, [1, 1, 1, 1, 2], [1, 1, 1, 2, 2], [1, 1, 1, 2, 2], [1, 1, 1, 2, 2]])
+    o = objects.Object(); o.footprint = {1}
+    region = o.get_cvxprog_region(image.Image(y), atoms, background_margin=2)
+    assert np.array_equal(region.mask, np.array([[0] * 5, [0, 1, 0, 0, 0]] + [[1, 1, 1, 0, 0]] * 4, bool))
+    assert np.allclose(image.get_pixel_map((6, 3), normalized=True)[0][:, 0], np.arange(6) / 5)
+    b, sel = image.bbox(expected)
+    assert np.array_equal(b, [[1, 4], [2, 4]])
+    m = dsm.DeformableShapeModel(np.arange(8.))
+    assert np.array_equal(m.A, [[0, 2], [2, 1]]) and np.array_equal(m.ξ, [6, 7])
+    assert dsmcfg.get_dsm_cfg({'alpha': 3})['alpha'] == 3 and dsmcfg.get_dsm_cfg()['smooth_subsample'] == 20
+
+
+def test_engine_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available(): pytest.skip('GPU present')
+    with pytest.raises(engine.SolverError, match='no CPU fallback'): engine.Engine(0)
