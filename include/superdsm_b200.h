@@ -90,7 +90,7 @@ typedef struct sdsm_out {
     double*  d_energy;       /* [n_cand]   psi at the result, unscaled (objects.py:208) */
     int32_t* d_status;       /* [n_cand]   SDSM_ST_* */
     int32_t* d_info;         /* [n_cand*8] m, iterations (elliptical pass 1, pass 2, DSM), #fg pixels, cvxopt status
-                                           bits, compacted box h', w' */
+                                           bits, #value+gradient evaluations, #Hessian evaluations */
     double*  d_params;       /* [params_len] (theta, xi) of candidate c at cands[c].par_off, 6 + m values */
     int32_t* d_fgbox;        /* [n_cand*4] rmin, rmax, cmin, cmax of the foreground inside the bounding box, -1 if none */
     uint8_t* d_onboundary;   /* [n_cand]   objects.py:209 */
@@ -127,6 +127,16 @@ int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d
  * d_rc[n] = compacted (row | col << 16), d_cols[n * 25] grid index or -1, d_vals[n * 25]; d_grid[m] = (row | col << 16). */
 int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, uint32_t* d_rc,
                        int32_t* d_cols, float* d_vals, uint32_t* d_grid, void* d_workspace, void* stream);
+
+/* Diagnostics: one interior-point solve (dsm.py:478-490) of candidate c of the last batch from d_x0 (6 + m values; only
+ * the first 6 are used if !use_xi).  d_trace[(maxiters + 1) * 8] receives per iteration: f, gap, primal and dual
+ * infeasibility, t, s, z, relaxed-iteration counter; d_status_iters[2] = {0 optimal | 1 unknown | 2 exception, iterations}. */
+int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, int32_t use_xi,
+                     const double* d_x0, double* d_trace, double* d_xout, int32_t* d_status_iters, void* d_workspace, void* stream);
+
+/* Measurement aid: enqueues a register-resident FP64 FMA loop on every SM (8 CTAs of 256 threads per SM, 8 independent
+ * chains per thread); *flops receives the floating-point operations of the launch.  Time it with CUDA events. */
+int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flops, void* stream);
 
 /* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
 int64_t sdsm_launch_count(const sdsm_ctx* ctx);

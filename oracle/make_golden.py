@@ -28,9 +28,9 @@ def toy_cases():
     w = synth.make_workload('toy', oversegment=2, max_set_size=3)
     fps = w['footprints']
     cases.append(('toy', w['y'], w['y_mask'], w['atoms'], fps[:8] + fps[10:12] + fps[-2:], w['dsm_cfg']))
-    # default-config shapes (sigma_G 10, sub-sample 20) on a mid-size image -> larger kernel than most regions
+    # hand-set hyper-parameters off the automation lattice (sigma_G 5, sub-sample 11: R = 20 < 2 * 11), larger m
     w2 = synth.make_workload('toy', oversegment=1, max_set_size=2, seed=11, shape=(220, 260), n=5)
-    cfg2 = synth.dsm_config(None, smooth_amount=5, smooth_subsample=7, background_margin=12, alpha=0.2)
+    cfg2 = synth.dsm_config(None, smooth_amount=5, smooth_subsample=11, background_margin=12, alpha=0.2)
     cases.append(('odd', w2['y'], w2['y_mask'], w2['atoms'], [w2['footprints'][k] for k in (0, 2, 6)], cfg2))
     return cases
 

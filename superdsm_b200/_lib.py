@@ -39,7 +39,8 @@ class Out(ctypes.Structure):
 
 
 EXPORTS = ('sdsm_abi_version', 'sdsm_create', 'sdsm_destroy', 'sdsm_last_error', 'sdsm_set_image', 'sdsm_set_params',
-           'sdsm_plan_batch', 'sdsm_solve_batch', 'sdsm_eval_candidate', 'sdsm_export_smooth', 'sdsm_launch_count')
+           'sdsm_plan_batch', 'sdsm_solve_batch', 'sdsm_eval_candidate', 'sdsm_export_smooth', 'sdsm_trace_solve',
+           'sdsm_dfma_peak', 'sdsm_launch_count')
 
 _lib = None
 
@@ -65,6 +66,8 @@ def load():
     lib.sdsm_solve_batch.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, ctypes.c_size_t, ctypes.POINTER(Out), vp]
     lib.sdsm_eval_candidate.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, vp, vp, vp]
     lib.sdsm_export_smooth.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, vp, vp, vp]
+    lib.sdsm_trace_solve.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, i32, vp, vp, vp, vp, vp, vp]
+    lib.sdsm_dfma_peak.argtypes = [vp, vp, i32, ctypes.POINTER(ctypes.c_int64), vp]
     lib.sdsm_launch_count.argtypes = [vp]
     lib.sdsm_launch_count.restype = i64
     if lib.sdsm_abi_version() != 1:

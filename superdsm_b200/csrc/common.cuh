@@ -54,14 +54,14 @@ struct WS {
     CInfo*    cinfo;       // [n_cand]
     int32_t*  counters;    // [16]
     char*     cta;         // per-CTA solver workspace
-    size_t    cta_bytes, off_H, off_L, off_scrH, off_scrG, off_vec;
+    size_t    cta_bytes, off_H, off_H2, off_L, off_scrH, off_scrG, off_vec;
 };
 
 struct Layout {
     size_t total;
     size_t o_pix_y, o_pix_rc, o_pix_s, o_pix_dist, o_gval, o_cell_start, o_cell_amask, o_cellmap, o_grid_rc, o_grid_tmp,
            o_xtab, o_inv, o_fwd, o_cinfo, o_counters, o_cta;
-    size_t cta_bytes, off_H, off_L, off_scrH, off_scrG, off_vec;
+    size_t cta_bytes, off_H, off_H2, off_L, off_scrH, off_scrG, off_vec;
 };
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
@@ -89,6 +89,7 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int32_t n_cand, int32
     size_t c = 0;
     auto ctake = [&](size_t bytes) { size_t at = c; c = align_up(c + bytes); return at; };
     L.off_H = ctake(sizeof(double) * (size_t)n_max * n_max);
+    L.off_H2 = ctake(sizeof(double) * (size_t)n_max * n_max);
     L.off_L = ctake(sizeof(double) * ((size_t)n_max * (n_max + 1) / 2));
     L.off_scrH = ctake(sizeof(double) * (size_t)cells_max * SCRH);
     L.off_scrG = ctake(sizeof(double) * (size_t)cells_max * SCRG);
@@ -120,7 +121,7 @@ inline WS make_ws(void* base, const Layout& L)
     w.counters = (int32_t*)(b + L.o_counters);
     w.cta = b + L.o_cta;
     w.cta_bytes = L.cta_bytes;
-    w.off_H = L.off_H; w.off_L = L.off_L; w.off_scrH = L.off_scrH; w.off_scrG = L.off_scrG; w.off_vec = L.off_vec;
+    w.off_H = L.off_H; w.off_H2 = L.off_H2; w.off_L = L.off_L; w.off_scrH = L.off_scrH; w.off_scrG = L.off_scrG; w.off_vec = L.off_vec;
     return w;
 }
 

@@ -52,6 +52,7 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     if (prop.major < 10) { ctx->err = "superdsm_b200 is built for sm_100a (B200) only"; return SDSM_E_UNSUPPORTED; }
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
     return SDSM_OK;
 }
 
@@ -221,6 +222,31 @@ extern "C" int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sd
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     k_export<<<64, 128, 0, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, ws, d_rc, d_cols, d_vals, d_grid);
     ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, int32_t use_xi,
+                                const double* d_x0, double* d_trace, double* d_xout, int32_t* d_status_iters, void* d_workspace, void* stream_)
+{
+    if (!ctx || !plan || !d_cands || !d_x0 || !d_trace || !d_xout || !d_status_iters || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
+    Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    WS ws = make_ws(d_workspace, L);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    k_trace<<<1, SOLVER_BLOCK, SOLVER_SMEM, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, use_xi, ws, d_x0, d_trace, d_xout, d_status_iters);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flops, void* stream_)
+{
+    if (!ctx || !d_scratch || !flops || iters < 1) return SDSM_E_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const int blocks = ctx->sm_count * 8;
+    k_dfma_peak<<<blocks, 256, 0, (cudaStream_t)stream_>>>(d_scratch, iters);
+    ctx->launches++;
+    *flops = (int64_t)blocks * 256 * 8 * 2 * (int64_t)iters;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
 }

@@ -26,7 +26,7 @@ struct Prob {
     const int32_t* cstart; const uint32_t* amask; const int32_t* cellmap; const uint32_t* grid;
     const double* xr; const double* xc;
     double scale_cp, alpha, eps, tol;
-    double *H, *Lg, *scrH, *scrG;
+    double *H, *H2, *Lg, *scrH, *scrG;
     int sub;
 };
 
@@ -402,6 +402,7 @@ __device__ __noinline__ double eval(const Prob& P, Sm& sm, const double* x, doub
     if (bad) sm.flag[1] = 1;
     __syncthreads();
     if (sm.flag[1]) return 0.0;
+    if (tid == 0) sm.flag[want_h ? 3 : 2] += 1;          // evaluation counters (reported in out.info)
     if (!use_xi) {
         double* out = sm.red_out;
         if (want_h) eval_poly<BLOCK, true>(P, sm, x, out); else eval_poly<BLOCK, false>(P, sm, x, out);
@@ -497,7 +498,7 @@ __device__ double bdot(const double* a, const double* b, int N, Sm& sm)
 // Returns 0 'optimal', 1 'unknown', 2 exception (rank error at the first factorisation, non-finite point, stalled search).
 
 template <int BLOCK>
-__device__ __noinline__ int ipm(const Prob& P, Sm& sm, double* V, int ld, bool use_xi, const Par& par, int* iters_out)
+__device__ __noinline__ int ipm(const Prob& P, Sm& sm, double* V, int ld, bool use_xi, const Par& par, int* iters_out, double* trace = nullptr)
 {
     const int tid = threadIdx.x;
     const int N = use_xi ? P.N : 6;
@@ -536,6 +537,10 @@ __device__ __noinline__ int ipm(const Prob& P, Sm& sm, double* V, int ld, bool u
         }
         double phi = th1 * gap + th2 * resx + th3 * resznl;
         pres /= pres0; dres /= dres0;
+        if (trace && tid == 0) {
+            double* tr = trace + (size_t)iters * 8;
+            tr[0] = f0; tr[1] = gap; tr[2] = pres; tr[3] = dres; tr[4] = t; tr[5] = s; tr[6] = z; tr[7] = (double)relaxed;
+        }
         if ((pres <= par.feastol && dres <= par.feastol && (gap <= par.abstol || (relgap >= 0.0 && relgap <= par.reltol))) || iters == par.maxiters)
             return iters == par.maxiters ? 1 : 0;
 
@@ -543,18 +548,27 @@ __device__ __noinline__ int ipm(const Prob& P, Sm& sm, double* V, int ld, bool u
         double lmsq = lm * lm;
 
         bool ok = cholesky<BLOCK>(P.H, N, Lf, rd, sm);
+        // cpl's own Df and H (used by the residual of the iterative refinement) vs. the ones cp's KKT wrapper sees
+        const double* Hres = P.H;
+        const double* gres = g;
         if (!ok) {
             if (iters == 0) return 2;                                       // ValueError("Rank(A) < p or ...")
             if (0 < relaxed && relaxed < MAX_RELAXED) {
-                // restart a standard line search from the last saved state
+                // Restart a standard line search from the last saved state.  cvxopt re-evaluates F at the restored
+                // point inside the KKT solver only: cpl's residual closures keep the Df and H of the abandoned point.
                 phi = phi0s; gap = gap0s;
                 d = sv_d; lm = sv_lm; t = sv_t; s = sv_s; z = sv_z; lmsq = lm * lm;
-                for (int i = tid; i < N; i += BLOCK) x[i] = sx[i];
+                __syncthreads();
+                for (int i = tid; i < N; i += BLOCK) { x[i] = sx[i]; sdx[i] = g[i]; }
+                for (size_t i = tid; i < (size_t)N * N; i += BLOCK) P.H2[i] = P.H[i];
                 rxt = sv_rxt; resx = sv_resx; rznl = sv_rznl; resznl = fabs(rznl);
                 relaxed = -1;
+                __syncthreads();
                 eval<BLOCK>(P, sm, x, g, true, z, use_xi);
                 if (sm.flag[1]) return 2;
                 ok = cholesky<BLOCK>(P.H, N, Lf, rd, sm);
+                Hres = P.H2;
+                gres = sdx;
             }
             if (!ok) return 1;                                              // 'unknown' (singular KKT matrix)
         }
@@ -574,13 +588,14 @@ __device__ __noinline__ int ipm(const Prob& P, Sm& sm, double* V, int ld, bool u
             const int lane = tid & 31, warp = tid >> 5;
             for (int i = warp; i < N; i += NW) {
                 double a = 0;
-                const double* hr = P.H + (size_t)i * N;
+                const double* hr = Hres + (size_t)i * N;
                 for (int j = lane; j < N; j += 32) a += hr[j] * tv[j];
                 a = warp_sum(a);
-                if (lane == 0) { const double vx = -(z * g[i]) - a - g[i] * wz3; ev[i] = vx + g[i] * vt; }
+                if (lane == 0) { const double vx = -(z * g[i]) - a - gres[i] * wz3; ev[i] = vx + g[i] * vt; }
             }
         }
         const double gux = bdot<BLOCK>(g, tv, N, sm);
+        const double gux_res = (gres == g) ? gux : bdot<BLOCK>(gres, tv, N, sm);
         if (tid < 32) chol_solve_warp(Lf, rd, N, ev);
         __syncthreads();
         const double gex = bdot<BLOCK>(g, ev, N, sm);
@@ -596,7 +611,7 @@ __device__ __noinline__ int ipm(const Prob& P, Sm& sm, double* V, int ld, bool u
             const double bs1 = bs / lm, bz1 = bz - d * bs1;
             double uz = uz0, ut = gux + d * d * bt - bz1, us = bs1 - uz;
             // residual + second f4_no_ir
-            const double vz = bz - (gux - ut) - d * us;
+            const double vz = bz - (gux_res - ut) - d * us;
             const double vs = bs - lm * (uz + us);
             const double vs1 = vs / lm, vz1 = vz - d * vs1;
             const double ez = -d * vt, et = gex + d * d * vt - vz1, es = vs1 - ez;
@@ -751,7 +766,7 @@ __device__ void setup_problem(Prob& P, const Par& par, const sdsm_cand& cd, cons
     P.xr = ws.xtab + cd.tab_off; P.xc = P.xr + cd.h;
     P.scale_cp = par.scale / (double)cd.n;                                   // objects.py:380
     P.alpha = par.alpha; P.eps = par.epsilon; P.tol = par.sparsity_tol; P.sub = par.sub;
-    P.H = (double*)(cta + ws.off_H); P.Lg = (double*)(cta + ws.off_L);
+    P.H = (double*)(cta + ws.off_H); P.H2 = (double*)(cta + ws.off_H2); P.Lg = (double*)(cta + ws.off_L);
     P.scrH = (double*)(cta + ws.off_scrH); P.scrG = (double*)(cta + ws.off_scrG);
 }
 
@@ -792,7 +807,8 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const
         const CInfo ci = ws.cinfo[c];
         int32_t* info = out.d_info + (size_t)c * 8;
         if (tid == 0) {
-            info[0] = ci.m; info[1] = -1; info[2] = -1; info[3] = -1; info[4] = ci.n_fg; info[5] = 0; info[6] = ci.hp; info[7] = ci.wp;
+            sm.flag[2] = 0; sm.flag[3] = 0;
+            info[0] = ci.m; info[1] = -1; info[2] = -1; info[3] = -1; info[4] = ci.n_fg; info[5] = 0; info[6] = 0; info[7] = 0;
             out.d_fgbox[c * 4 + 0] = -1; out.d_fgbox[c * 4 + 1] = -1; out.d_fgbox[c * 4 + 2] = -1; out.d_fgbox[c * 4 + 3] = -1;
             out.d_onboundary[c] = 0;
             out.d_energy[c] = 0.0;
@@ -950,7 +966,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const
             out.d_energy[c] = energy;
             out.d_onboundary[c] = (uint8_t)s_any;
             if (s_box[1] >= 0) { out.d_fgbox[c * 4 + 0] = s_box[0]; out.d_fgbox[c * 4 + 1] = s_box[1]; out.d_fgbox[c * 4 + 2] = s_box[2]; out.d_fgbox[c * 4 + 3] = s_box[3]; }
-            info[1] = it1; info[2] = it2; info[3] = it3; info[5] = bits;
+            info[1] = it1; info[2] = it2; info[3] = it3; info[5] = bits; info[6] = sm.flag[2]; info[7] = sm.flag[3];
         }
     }
 }
@@ -983,6 +999,51 @@ k_eval(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, const double*
     if (tid == 0) *value = f;
     for (int i = tid; i < N; i += BLOCK) grad[i] = g[i];
     for (size_t i = tid; i < (size_t)N * N; i += BLOCK) Hout[i] = P.H[i];
+}
+
+// runs one interior-point solve of candidate c (packed by the last batch) from x0 and records the iterates
+__global__ void __launch_bounds__(SOLVER_BLOCK, 2)
+k_trace(Par par, const sdsm_cand* __restrict__ cands, int c, int use_xi_, WS ws, const double* __restrict__ x0, double* trace,
+        double* xout, int32_t* status_iters)
+{
+    constexpr int BLOCK = SOLVER_BLOCK;
+    extern __shared__ __align__(16) char smem_raw[];
+    Sm sm;
+    carve_smem(sm, smem_raw);
+    const int tid = threadIdx.x;
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    Prob P;
+    setup_problem<BLOCK>(P, par, cd, ci, ws, ws.cta);
+    const bool use_xi = use_xi_ && P.m > 0;
+    const int N = use_xi ? P.N : 6;
+    double* V; int ld;
+    if (P.N <= NV_SMEM) { V = sm.vec; ld = NV_SMEM; } else { V = (double*)(ws.cta + ws.off_vec); ld = P.N; }
+    for (int i = tid; i < N; i += BLOCK) V[V_X * ld + i] = x0[i];
+    if (use_xi) for (size_t i = tid; i < (size_t)N * N; i += BLOCK) P.H[i] = 0.0;
+    __syncthreads();
+    int iters = -1;
+    const int r = ipm<BLOCK>(P, sm, V, ld, use_xi, par, &iters, trace);
+    __syncthreads();
+    for (int i = tid; i < N; i += BLOCK) xout[i] = V[V_X * ld + i];
+    if (tid == 0) { status_iters[0] = r; status_iters[1] = iters; }
+}
+
+// register-resident FP64 FMA peak (the FP64 roofline denominator; MEASURED_PEAKS.json has none)
+__global__ void __launch_bounds__(256) k_dfma_peak(double* out, int iters)
+{
+    double a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = 1.0 + 1e-9 * (threadIdx.x + k);
+    const double b = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = fma(a[k], b, c);
+    }
+    double r = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r += a[k];
+    if (r == 12345.678) out[0] = r;
 }
 
 __global__ void k_export(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, uint32_t* rc, int32_t* cols, float* vals, uint32_t* grid)

@@ -319,6 +319,39 @@ class Engine(object):
         self.stream.synchronize()
         return float(d_val.item()), d_g.cpu().numpy(), d_H.cpu().numpy().reshape(N, N)
 
+    def trace_solve(self, k, x0, use_xi=True, maxiters=100):
+        """One interior-point solve of candidate ``k`` of the last batch from ``x0``; returns (status, iterations, x, trace)."""
+        torch = self.torch
+        plan, d_cands, ws, cands = self._last
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        d_x0 = torch.from_numpy(x0).to(self.device)
+        d_tr = torch.zeros((maxiters + 1) * 8, dtype=torch.float64, device=self.device)
+        d_x = torch.zeros(len(x0), dtype=torch.float64, device=self.device)
+        d_si = torch.zeros(2, dtype=torch.int32, device=self.device)
+        torch.cuda.synchronize(self.device)
+        self._check(self.lib.sdsm_trace_solve(self.ctx, ctypes.byref(plan), d_cands.data_ptr(), k, 1 if use_xi else 0, d_x0.data_ptr(),
+                                              d_tr.data_ptr(), d_x.data_ptr(), d_si.data_ptr(), ws.data_ptr(), self.stream.cuda_stream))
+        self.stream.synchronize()
+        si = d_si.cpu().numpy()
+        n_it = int(si[1])
+        return int(si[0]), n_it, d_x.cpu().numpy(), d_tr.cpu().numpy().reshape(-1, 8)[:n_it + 1]
+
+    def dfma_peak_gflops(self, iters=20000, repeats=5):
+        """Measured register-resident FP64 FMA throughput of this device (GFLOP/s): the FP64 roofline denominator."""
+        torch = self.torch
+        scratch = torch.zeros(8, dtype=torch.float64, device=self.device)
+        flops = ctypes.c_int64()
+        best = 0.0
+        stream = torch.cuda.current_stream(self.device)
+        for _ in range(repeats + 1):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            self._check(self.lib.sdsm_dfma_peak(self.ctx, scratch.data_ptr(), iters, ctypes.byref(flops), stream.cuda_stream))
+            e1.record(stream)
+            e1.synchronize()
+            best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+        return best
+
     def export_smooth(self, k, n, m):
         """G~ of candidate ``k`` of the last batch: (pixel rc [n], cols [n, 25], vals [n, 25], grid rc [m])."""
         torch = self.torch
