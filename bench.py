@@ -251,7 +251,7 @@ def run_gpu(args):
             'e2e': {'value': cand_total * e2e_steps / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
                     'd2h_bytes_per_step': int(d2h), 'includes': 'host EDT + descriptors, pinned H2D of y/atoms/descriptors, solve, D2H, Object materialisation'},
             'gpu_launches': int(gpu_launches),
-            'roofline': {'kernel': 'k_solve (persistent per-candidate solver)', 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak,
+            'roofline': {'kernel': 'lock-step solver: k_eval + k_ctrl rounds', 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak,
                          'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': None, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': alg_bytes,
                          'fp64': {'achieved_gflops': alg_flops / (solver_ms * 1e-3) / 1e9, 'peak_gflops': dfma,

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define SDSM_ABI_VERSION 1
+#define SDSM_ABI_VERSION 2
 
 /* return codes */
 #define SDSM_OK              0
@@ -73,6 +73,8 @@ typedef struct sdsm_cand {
     int64_t tab_off;         /* out: offset into the per-row/column tables */
     int64_t par_off;         /* out: offset into out.params (6 + cell_cap doubles reserved) */
     int64_t fg_off;          /* out: offset into out.fgmask (h * w bytes, row-major over the bounding box) */
+    int64_t vec_off;         /* out: offset into the solver's vector workspace (12 vectors of 6 + cell_cap doubles) */
+    int64_t mat_off;         /* out: offset into the solver's matrix workspace (Hessians and Cholesky factor) */
 } sdsm_cand;
 
 typedef struct sdsm_plan {
@@ -81,8 +83,8 @@ typedef struct sdsm_plan {
     int64_t fgmask_len;      /* bytes in out.fgmask */
     int32_t n_max;           /* largest 6 + cell_cap of the batch */
     int32_t cells_max;       /* largest cell_cap of the batch */
-    int32_t solver_ctas;     /* grid size of the persistent solver kernel */
-    int32_t reserved;
+    int32_t reserved0;
+    int32_t reserved1;
 } sdsm_plan;
 
 /* device output arrays of one batch, all caller-owned */

@@ -14,8 +14,8 @@ ST_OPTIMAL, ST_FALLBACK, ST_SKIPPED, ST_ERROR, ST_BADREGION = range(5)
 #: numpy mirror of ``struct sdsm_cand``
 CAND_DTYPE = np.dtype([('r0', '<i4'), ('c0', '<i4'), ('h', '<i4'), ('w', '<i4'), ('fp_off', '<i4'), ('fp_len', '<i4'),
                        ('n', '<i4'), ('cell_cap', '<i4'), ('pix_off', '<i8'), ('cell_off', '<i8'), ('tab_off', '<i8'),
-                       ('par_off', '<i8'), ('fg_off', '<i8')], align=True)
-assert CAND_DTYPE.itemsize == 72
+                       ('par_off', '<i8'), ('fg_off', '<i8'), ('vec_off', '<i8'), ('mat_off', '<i8')], align=True)
+assert CAND_DTYPE.itemsize == 88
 
 
 class Params(ctypes.Structure):
@@ -28,8 +28,8 @@ class Params(ctypes.Structure):
 
 class Plan(ctypes.Structure):
     _fields_ = [('workspace_bytes', ctypes.c_size_t), ('params_len', ctypes.c_int64), ('fgmask_len', ctypes.c_int64),
-                ('n_max', ctypes.c_int32), ('cells_max', ctypes.c_int32), ('solver_ctas', ctypes.c_int32),
-                ('reserved', ctypes.c_int32)]
+                ('n_max', ctypes.c_int32), ('cells_max', ctypes.c_int32), ('reserved0', ctypes.c_int32),
+                ('reserved1', ctypes.c_int32)]
 
 
 class Out(ctypes.Structure):
@@ -70,7 +70,7 @@ def load():
     lib.sdsm_dfma_peak.argtypes = [vp, vp, i32, ctypes.POINTER(ctypes.c_int64), vp]
     lib.sdsm_launch_count.argtypes = [vp]
     lib.sdsm_launch_count.restype = i64
-    if lib.sdsm_abi_version() != 1:
+    if lib.sdsm_abi_version() != 2:
         raise ImportError('libsuperdsm_b200.so: ABI version mismatch')
     _lib = lib
     return lib

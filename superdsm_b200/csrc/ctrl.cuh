@@ -1,0 +1,1064 @@
+// K3b: k_ctrl -- one CTA per live candidate, between two evaluations of F.  It gathers the per-cell results of k_eval into
+// value / gradient / Hessian, advances the candidate's state machine
+//   elliptical initialisation (objects.py:321-358) -> DSM solve (objects.py:394-410, dsm.py:431-490) -> result
+// up to the next point where F must be evaluated, files that request (work items for the next k_eval) and returns.
+// The interior-point iterations restate cvxopt.solvers.cp (oracle/cpsolver.py, which this mirrors line by line); the
+// local variables of that loop live in CState across rounds.
+#pragma once
+#include "common.cuh"
+#include "eval.cuh"
+
+namespace sdsm {
+
+constexpr int MAX_RELAXED = 8;
+constexpr double CP_STEP = 0.99, CP_BETA = 0.5, CP_ALPHA = 0.01;
+
+enum { V_X = 0, V_G, V_DX, V_T, V_NX, V_NG, V_SX, V_SDX, V_RD, V_X0, V_E, V_W };
+enum { PC_START = 0, PC_TOP, PC_RESTORED, PC_TRIAL, PC_VAL1, PC_VALINIT, PC_JX, PC_J0, PC_FINAL, PC_DONE };
+enum { STG_ELL1 = 0, STG_ELL2, STG_DSM, STG_TRACE };
+
+struct Prob {
+    int n, m, N, ncells, cw, ch, ld;
+    const double* py; const uint32_t* prc;
+    const int32_t* cstart; const uint32_t* amask; const int32_t* cellmap; const uint32_t* grid; const int32_t* clist;
+    int n_ne;
+    const double* xr; const double* xc;
+    double scale_cp, alpha, eps, tol;
+    double *V, *H, *H2, *Lg;
+    const double *scrG, *scrH;
+    int sub;
+};
+
+struct Sm {
+    double* Lf;        // [lcap + CTRL_BPAD] packed Cholesky factor when it fits (else it lives in global memory), followed by /
+                       // replaced by the right-hand side of the triangular solves
+    double* red_part;  // [CTRL_WARPS * 32]
+    double* red_out;   // [32]
+    int*    flag;      // [8]
+    int     lcap;      // doubles available for the factor
+};
+constexpr int CTRL_BPAD = 128;
+__host__ __device__ inline size_t ctrl_smem_bytes(int lcap) { return sizeof(double) * (size_t)(lcap + CTRL_BPAD + CTRL_WARPS * 32 + 32) + sizeof(int) * 8; }
+// factor capacity (doubles) a batch whose largest system has n_max unknowns asks for: the whole packed factor if n_max <= 104
+__host__ __device__ inline int ctrl_lcap(int n_max) { const int need = n_max * (n_max + 1) / 2; return need <= SMEM_L_CAP ? (need < 64 ? 64 : need) : SMEM_L_CAP; }
+
+__device__ __forceinline__ void carve_smem(Sm& sm, char* base, int lcap)
+{
+    sm.Lf = (double*)base;
+    sm.red_part = sm.Lf + lcap + CTRL_BPAD;
+    sm.red_out = sm.red_part + CTRL_WARPS * 32;
+    sm.flag = (int*)(sm.red_out + 32);
+    sm.lcap = lcap;
+}
+
+__device__ __forceinline__ void setup_problem(Prob& P, const Par& par, const sdsm_cand& cd, const CInfo& ci, const WS& ws)
+{
+    P.n = cd.n; P.m = ci.m; P.N = 6 + ci.m; P.ncells = ci.ncells; P.cw = ci.cw; P.ch = ci.ch;
+    P.ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
+    P.py = ws.pix_y + cd.pix_off; P.prc = ws.pix_rc + cd.pix_off;
+    P.cstart = ws.cell_start + cd.cell_off; P.amask = ws.cell_amask + cd.cell_off; P.cellmap = ws.cellmap + cd.cell_off;
+    P.grid = ws.grid_rc + cd.cell_off; P.clist = ws.cell_list + cd.cell_off; P.n_ne = ci.n_ne;
+    P.xr = ws.xtab + cd.tab_off; P.xc = P.xr + cd.h;
+    P.scale_cp = par.scale / (double)cd.n;                                   // objects.py:380
+    P.alpha = par.alpha; P.eps = par.epsilon; P.tol = par.sparsity_tol; P.sub = par.sub;
+    P.V = ws.vecs + cd.vec_off;
+    const size_t nn = (size_t)P.ld * P.ld;
+    P.H = ws.mats + cd.mat_off; P.H2 = P.H + nn; P.Lg = P.H2 + nn;
+    P.scrG = ws.scrG + (size_t)cd.cell_off * SCRG; P.scrH = ws.scrH + (size_t)cd.cell_off * SCRH;
+}
+
+// slot index (0..24) of the cell at offset (da, db) from a cell, and the local index of that slot in the cell's vector
+__device__ __forceinline__ int local_index(uint32_t am, int da, int db)
+{
+    const int s = (da + NC) * 5 + (db + NC);
+    if (!((am >> s) & 1u)) return -1;
+    return 6 + __popc(am & ((1u << s) - 1u));
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Gathers the per-cell results of k_eval.  g: scaled gradient out; H (if HESS) = hz * scale_cp * Hess psi, full symmetric,
+// row stride N.  Returns the scaled value; *psi_out = unscaled psi.  Fixed summation order.
+
+template <int BLOCK, bool HESS>
+__device__ double gather_poly(const Prob& P, Sm& sm, double* g, double hz, double* psi_out)
+{
+    const int tid = threadIdx.x;
+    constexpr int K = HESS ? 28 : 7;
+    double acc[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) acc[k] = 0;
+    for (int i = tid; i < P.n_ne; i += BLOCK) {
+        const int cell = P.clist[i];
+        const double* sg = P.scrG + (size_t)cell * SCRG;
+        acc[0] += sg[31];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) acc[1 + k] += sg[k];
+        if (HESS) {
+            const double* sh = P.scrH + (size_t)cell * SCRH;
+#pragma unroll
+            for (int k = 0; k < 21; ++k) acc[7 + k] += sh[k];
+        }
+    }
+    block_sum<BLOCK, K>(acc, sm.red_part, sm.red_out);
+    const double psi = sm.red_out[0];
+    const double sc = P.scale_cp;
+    if (tid < 6) g[tid] = sc * sm.red_out[1 + tid];
+    if (HESS && tid < 21) {
+        int a = 0, t = tid;
+        while (t >= a + 1) { t -= a + 1; ++a; }
+        const double v = hz * sc * sm.red_out[7 + tid];
+        P.H[a * 6 + t] = v;
+        P.H[t * 6 + a] = v;
+    }
+    __syncthreads();
+    *psi_out = psi;
+    return sc * psi;
+}
+
+template <int BLOCK, bool HESS>
+__device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g, double hz, double* psi_out)
+{
+    const int tid = threadIdx.x;
+    const int m = P.m, N = P.N, cw = P.cw, ch = P.ch;
+    const double sc = P.scale_cp;
+    __syncthreads();
+    // (1) value, theta gradient, 6x6 block, regulariser: sums over all cells / grid points
+    constexpr int K = HESS ? 29 : 8;
+    double acc[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) acc[k] = 0;
+    for (int i = tid; i < P.n_ne; i += BLOCK) {
+        const int cell = P.clist[i];
+        const double* sg = P.scrG + (size_t)cell * SCRG;
+        acc[0] += sg[31];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) acc[1 + k] += sg[k];
+        if (HESS) {
+            const double* sh = P.scrH + (size_t)cell * SCRH;
+#pragma unroll
+            for (int k = 0; k < 21; ++k) acc[8 + k] += sh[k];
+        }
+    }
+    for (int j = tid; j < m; j += BLOCK) { const double v = x[6 + j]; acc[7] += sqrt(v * v + P.eps); }
+    block_sum<BLOCK, K>(acc, sm.red_part, sm.red_out);
+    double obj2 = P.alpha * sm.red_out[7] - P.alpha * sqrt(P.eps) * (double)m;   // dsm.py:325-331
+    if (obj2 < 0) obj2 = 0;
+    const double psi = sm.red_out[0] + obj2;
+    if (tid < 6) g[tid] = sc * sm.red_out[1 + tid];
+    if (HESS && tid < 21) {
+        int a = 0, t = tid;
+        while (t >= a + 1) { t -= a + 1; ++a; }
+        const double v = hz * sc * sm.red_out[8 + tid];
+        P.H[a * N + t] = v;
+        P.H[t * N + a] = v;
+    }
+    // (2) xi gradient: grid point j collects from the cells around its own
+    for (int j = tid; j < m; j += BLOCK) {
+        const uint32_t gp = P.grid[j];
+        const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
+        double s = 0;
+        for (int da = -NC; da <= NC; ++da) {
+            const int a = ja - da;
+            if (a < 0 || a >= ch) continue;
+            for (int db = -NC; db <= NC; ++db) {
+                const int b = jb - db;
+                if (b < 0 || b >= cw) continue;
+                const int cell = a * cw + b;
+                if (P.cstart[cell + 1] == P.cstart[cell]) continue;
+                const int li = local_index(P.amask[cell], da, db);
+                if (li >= 0) s += P.scrG[(size_t)cell * SCRG + li];
+            }
+        }
+        const double v = x[6 + j];
+        s += P.alpha * (v / sqrt(v * v + P.eps));                             // dsm.py:350
+        g[6 + j] = sc * s;
+    }
+    if (HESS) {
+        // (3) xi-theta block
+        for (int it = tid; it < m * 6; it += BLOCK) {
+            const int j = it / 6, q = it - j * 6;
+            const uint32_t gp = P.grid[j];
+            const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
+            double s = 0;
+            for (int da = -NC; da <= NC; ++da) {
+                const int a = ja - da;
+                if (a < 0 || a >= ch) continue;
+                for (int db = -NC; db <= NC; ++db) {
+                    const int b = jb - db;
+                    if (b < 0 || b >= cw) continue;
+                    const int cell = a * cw + b;
+                    if (P.cstart[cell + 1] == P.cstart[cell]) continue;
+                    const int li = local_index(P.amask[cell], da, db);
+                    if (li >= 0) s += P.scrH[(size_t)cell * SCRH + tri(li, q)];
+                }
+            }
+            s *= hz * sc;
+            P.H[(size_t)(6 + j) * N + q] = s;
+            P.H[(size_t)q * N + 6 + j] = s;
+        }
+        // (4) xi-xi block: pairs of grid points whose cells are at most 2 NC apart share pixels; all other entries stay 0
+        // (the matrix is cleared once when the DSM stage begins: the pattern does not change)
+        constexpr int SP = 4 * NC + 1;
+        for (int it = tid; it < m * SP * SP; it += BLOCK) {
+            const int j = it / (SP * SP), e = it - j * (SP * SP);
+            const int ea = e / SP - 2 * NC, eb = e % SP - 2 * NC;
+            const uint32_t gp = P.grid[j];
+            const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
+            const int ka = ja + ea, kb = jb + eb;
+            if (ka < 0 || ka >= ch || kb < 0 || kb >= cw) continue;
+            const int k = P.cellmap[ka * cw + kb];
+            if (k < 0 || k > j) continue;
+            double s = 0;
+            for (int da = -NC; da <= NC; ++da) {
+                const int a = ja - da;                       // cell c = j's cell - (da, db)
+                if (a < 0 || a >= ch || abs(ka - a) > NC) continue;
+                for (int db = -NC; db <= NC; ++db) {
+                    const int b = jb - db;
+                    if (b < 0 || b >= cw || abs(kb - b) > NC) continue;
+                    const int cell = a * cw + b;
+                    if (P.cstart[cell + 1] == P.cstart[cell]) continue;
+                    const uint32_t am = P.amask[cell];
+                    const int lj = local_index(am, da, db);
+                    const int lk = local_index(am, ka - a, kb - b);
+                    if (lj >= 0 && lk >= 0) s += P.scrH[(size_t)cell * SCRH + (lj >= lk ? tri(lj, lk) : tri(lk, lj))];
+                }
+            }
+            if (k == j) {
+                const double v = x[6 + j];
+                const double t3 = v * v, t2 = sqrt(t3 + P.eps);
+                double gd = P.alpha * (1.0 / t2 - t3 / (t2 * t2 * t2));      // dsm.py:372-374
+                if (gd < 0) gd = 0;
+                s += gd;
+            }
+            s *= hz * sc;
+            P.H[(size_t)(6 + j) * N + 6 + k] = s;
+            P.H[(size_t)(6 + k) * N + 6 + j] = s;
+        }
+    }
+    __syncthreads();
+    *psi_out = psi;
+    return sc * psi;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// dense Cholesky of the lower triangle of H (N x N, row-major, ld = N) into packed L; the diagonal of L is stored as its
+// reciprocal (the triangular solves only multiply by it).
+// Fails (returns false) on a non-positive or non-finite pivot, as lapack.potrf / cholmod.numeric do.
+
+template <int BLOCK>
+__device__ bool cholesky(const double* H, int N, double* L, Sm& sm)
+{
+    constexpr int NW = BLOCK / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __syncthreads();
+    for (int i = warp; i < N; i += NW)
+        for (int j = lane; j <= i; j += 32) L[tri(i, j)] = H[(size_t)i * N + j];
+    if (tid == 0) sm.flag[0] = 0;
+    __syncthreads();
+    for (int k = 0; k < N; ++k) {
+        if (tid == 0) {
+            const double dk = L[tri(k, k)];
+            if (!(dk > 0.0) || !isfinite(dk)) sm.flag[0] = 1;
+            else L[tri(k, k)] = 1.0 / sqrt(dk);
+        }
+        __syncthreads();
+        if (sm.flag[0]) return false;
+        const double rk = L[tri(k, k)];
+        for (int i = k + 1 + tid; i < N; i += BLOCK) L[tri(i, k)] *= rk;
+        __syncthreads();
+        for (int i = k + 1 + warp; i < N; i += NW) {
+            const double lik = L[tri(i, k)];
+            double* row = L + tri(i, 0);
+            for (int j = k + 1 + lane; j <= i; j += 32) row[j] -= lik * L[tri(j, k)];
+        }
+        __syncthreads();
+    }
+    return true;
+}
+
+// b := (L L^T)^-1 b, by warp 0.  Callers synchronise the block before and after.
+__device__ void chol_solve_warp(const double* L, int N, double* b)
+{
+    const int lane = threadIdx.x & 31;
+    for (int k = 0; k < N; ++k) {
+        const double yk = b[k] * L[tri(k, k)];
+        __syncwarp();
+        for (int i = k + 1 + lane; i < N; i += 32) b[i] -= L[tri(i, k)] * yk;
+        if (lane == 0) b[k] = yk;
+        __syncwarp();
+    }
+    for (int k = N - 1; k >= 0; --k) {
+        const double xk = b[k] * L[tri(k, k)];
+        __syncwarp();
+        const double* row = L + tri(k, 0);
+        for (int i = lane; i < k; i += 32) b[i] -= row[i] * xk;
+        if (lane == 0) b[k] = xk;
+        __syncwarp();
+    }
+}
+
+// v := (L L^T)^-1 v for a vector in global memory: staged through shared memory (bv, capacity bvcap) when it fits
+template <int BLOCK>
+__device__ void chol_solve(const double* L, int N, double* v, double* bv, int bvcap)
+{
+    const int tid = threadIdx.x;
+    __syncthreads();
+    if (N <= bvcap) {
+        for (int i = tid; i < N; i += BLOCK) bv[i] = v[i];
+        __syncthreads();
+        if (tid < 32) chol_solve_warp(L, N, bv);
+        __syncthreads();
+        for (int i = tid; i < N; i += BLOCK) v[i] = bv[i];
+    } else {
+        if (tid < 32) chol_solve_warp(L, N, v);
+    }
+    __syncthreads();
+}
+
+template <int BLOCK>
+__device__ double bdot(const double* a, const double* b, int N, Sm& sm)
+{
+    double s = 0;
+    for (int i = threadIdx.x; i < N; i += BLOCK) s += a[i] * b[i];
+    return block_sum1<BLOCK>(s, sm.red_part, sm.red_out);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// data-driven ellipse of objects.py:287-296 / dsm.py:96-111 (second elliptical pass).  Returns false if it raises.
+
+template <int BLOCK>
+__device__ bool estimate_initialization(const Prob& P, Sm& sm, const Img& img, const sdsm_cand& cd, const uint16_t* inv_r,
+                                        const uint16_t* inv_c, double* out6)
+{
+    double a[3] = {0, 0, 0};
+    for (int i = threadIdx.x; i < P.n; i += BLOCK) {
+        if (P.py[i] > 0) {
+            const uint32_t rc = P.prc[i];
+            a[0] += (double)(cd.r0 + inv_r[rc & 0xffffu]);
+            a[1] += (double)(cd.c0 + inv_c[rc >> 16]);
+            a[2] += 1.0;
+        }
+    }
+    block_sum<BLOCK, 3>(a, sm.red_part, sm.red_out);
+    const double cnt = sm.red_out[2];
+    if (!(cnt > 0)) return false;                       // center_of_mass of an empty mask: NaN -> IndexError
+    const double cr = rint(sm.red_out[0] / cnt), cc = rint(sm.red_out[1] / cnt);   // np.round: half to even
+    __syncthreads();
+    const double zr = img.H > 1 ? (double)(img.H - 1) : 1.0, zc = img.W > 1 ? (double)(img.W - 1) : 1.0;
+    const double c1 = cr / zr, c2 = cc / zc;
+    double b[2] = {0, 0};
+    for (int i = threadIdx.x; i < P.n; i += BLOCK) {
+        if (P.py[i] > 0) {
+            const uint32_t rc = P.prc[i];
+            b[0] += P.xr[rc & 0xffffu] - c1;
+            b[1] += P.xc[rc >> 16] - c2;
+        }
+    }
+    block_sum<BLOCK, 2>(b, sm.red_part, sm.red_out);
+    const double m1 = sm.red_out[0] / cnt, m2 = sm.red_out[1] / cnt;
+    __syncthreads();
+    double v[2] = {0, 0};
+    for (int i = threadIdx.x; i < P.n; i += BLOCK) {
+        if (P.py[i] > 0) {
+            const uint32_t rc = P.prc[i];
+            const double e1 = (P.xr[rc & 0xffffu] - c1) - m1, e2 = (P.xc[rc >> 16] - c2) - m2;
+            v[0] += e1 * e1;
+            v[1] += e2 * e2;
+        }
+    }
+    block_sum<BLOCK, 2>(v, sm.red_part, sm.red_out);
+    const double h1 = fmax(sqrt(sm.red_out[0] / cnt), 1e-8), h2 = fmax(sqrt(sm.red_out[1] / cnt), 1e-8);
+    __syncthreads();
+    const double A1 = 1.0 / (h1 * h1), A2 = 1.0 / (h2 * h2);
+    const double bb1 = A1 * c1, bb2 = A2 * c2;
+    const double cc0 = (c1 * bb1 + c2 * bb2) - 1.0;
+    if (threadIdx.x == 0) { out6[0] = -A1; out6[1] = -A2; out6[2] = -0.0; out6[3] = bb1; out6[4] = bb2; out6[5] = -cc0; }
+    __syncthreads();
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// the candidate's state machine
+
+// internal (never stored across rounds) continuation points
+enum { PC_IPMDONE = 32, PC_BEGIN_DSM, PC_EST_INIT, PC_FINISH, PC_KKT, PC_PASS, PC_TRIALREQ, PC_ACCEPT, PC_IPMSTART };
+
+__device__ __forceinline__ void ipm_begin(CState& S)
+{
+    S.t = 0.0; S.s = 1.0; S.z = 1.0; S.d = 1.0; S.lm = 1.0;
+    S.relaxed = 0; S.iters = 0;
+    S.th1 = S.th2 = S.th3 = 0.0; S.pres0 = S.dres0 = 1.0;
+    S.phi0s = S.dphi0s = S.gap0s = S.step0s = S.dsdz0s = S.sigma0s = S.eta0s = 0.0;
+    S.sv_t = S.sv_s = S.sv_z = S.sv_d = S.sv_lm = S.sv_dt = S.sv_dz = S.sv_ds = S.sv_resx = S.sv_rznl = S.sv_rxt = 0.0;
+}
+
+// Files the evaluation of F at vector `vec` for the next k_eval (work list parity ^ 1).  Returns false, filing nothing,
+// if the point is not finite (the reference's Energy would raise on NaN parameters).
+template <int BLOCK>
+__device__ bool file_request(const Prob& P, Sm& sm, CState& S, const WS& ws, int c, int parity, int vec, int gvec, int want_h)
+{
+    const int tid = threadIdx.x;
+    const int N = S.use_xi ? P.N : 6;
+    const double* x = P.V + (size_t)vec * P.ld;
+    int bad = 0;
+    for (int i = tid; i < N; i += BLOCK) bad |= !isfinite(x[i]);
+    if (__syncthreads_or(bad)) return false;
+    S.req_vec = vec; S.req_gvec = gvec; S.req_h = want_h;
+    if (want_h) S.nh += 1; else S.nf += 1;                      // evaluation counters (reported in out.info)
+    const int other = parity ^ 1;
+    if (tid == 0) {
+        EvalReq rq; rq.x = x; rq.want_h = want_h; rq.use_xi = S.use_xi;
+        ws.req[c] = rq;
+        const unsigned long long old = atomicAdd(&ws.counters[other], (1ull << 32) | (unsigned long long)P.n_ne);
+        ws.live[(size_t)other * ws.n_cand + (int)(old >> 32)] = c;
+        sm.flag[2] = (int)(old & 0xffffffffull);
+    }
+    __syncthreads();
+    const int start = sm.flag[2];
+    uint2* items = ws.items + (size_t)other * ws.items_cap + start;
+    for (int i = tid; i < P.n_ne; i += BLOCK) items[i] = make_uint2((unsigned)c, (unsigned)P.clist[i]);
+    __syncthreads();
+    return true;
+}
+
+// Advances candidate c by one round: consumes the evaluation it asked for, runs up to the next evaluation request.
+template <int BLOCK>
+__device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c, int parity,
+                          Sm& sm, const sdsm_out& out, double* trace)
+{
+    const int tid = threadIdx.x;
+    CState S = ws.cstate[c];                 // every thread keeps its own copy; all threads compute the same scalars
+    Prob P;
+    setup_problem(P, par, cd, ci, ws);
+    const int ld = P.ld;
+    double* x = P.V + V_X * ld;  double* g = P.V + V_G * ld;   double* dx = P.V + V_DX * ld; double* tv = P.V + V_T * ld;
+    double* nx = P.V + V_NX * ld; double* ng = P.V + V_NG * ld; double* sx = P.V + V_SX * ld; double* sdx = P.V + V_SDX * ld;
+    double* x0 = P.V + V_X0 * ld; double* ev = P.V + V_E * ld; double* w6 = P.V + V_W * ld;
+    int32_t* info = out.d_info + (size_t)c * 8;
+
+    double f0 = 0.0;
+    if (S.pc != PC_START) {
+        double psi = 0.0;
+        double* gout = P.V + (size_t)S.req_gvec * ld;
+        if (!S.use_xi) f0 = S.req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
+        else {
+            const double* xe = P.V + (size_t)S.req_vec * ld;
+            f0 = S.req_h ? gather_cells<BLOCK, true>(P, sm, xe, gout, S.z, &psi) : gather_cells<BLOCK, false>(P, sm, xe, gout, S.z, &psi);
+        }
+        S.psi_last = psi;
+    }
+    bool hres_alt = false;
+    bool yield = false;
+
+#define REQUEST(vec_, gvec_, h_, next_, onbad_)                                                       \
+    do {                                                                                              \
+        if (file_request<BLOCK>(P, sm, S, ws, c, parity, vec_, gvec_, h_)) { S.pc = next_; yield = true; } \
+        else { onbad_; }                                                                              \
+    } while (0)
+
+    while (!yield) {
+        const int Nc = S.use_xi ? P.N : 6;
+        const int tri_n = Nc * (Nc + 1) / 2;
+        const bool l_sm = tri_n <= sm.lcap && Nc <= CTRL_BPAD;
+        double* Lf = l_sm ? sm.Lf : P.Lg;
+        double* bv = l_sm ? sm.Lf + tri_n : sm.Lf;
+        const int bvcap = l_sm ? CTRL_BPAD : sm.lcap + CTRL_BPAD;
+        switch (S.pc) {
+        case PC_START: {
+            if (tid == 0) {
+                info[0] = ci.m; info[1] = -1; info[2] = -1; info[3] = -1; info[4] = ci.n_fg; info[5] = 0; info[6] = 0; info[7] = 0;
+                out.d_fgbox[c * 4 + 0] = -1; out.d_fgbox[c * 4 + 1] = -1; out.d_fgbox[c * 4 + 2] = -1; out.d_fgbox[c * 4 + 3] = -1;
+                out.d_onboundary[c] = 0;
+                out.d_energy[c] = 0.0;
+            }
+            S.status = SDSM_ST_OPTIMAL; S.bits = 0; S.it1 = S.it2 = S.it3 = -1; S.nf = S.nh = 0; S.have1 = 0; S.r_ipm = 0;
+            S.val1 = 0; S.psi_last = 0; S.energy = 0;
+            if (ci.flags) { S.status = SDSM_ST_BADREGION; if (tid == 0) out.d_status[c] = S.status; S.pc = PC_DONE; yield = true; break; }
+            if (ci.n_fg == 1) { S.status = SDSM_ST_SKIPPED; if (tid == 0) out.d_status[c] = S.status; S.pc = PC_DONE; yield = true; break; }   // objects.py:184-191
+            for (int i = tid; i < P.N; i += BLOCK) x[i] = 0.0;
+            __syncthreads();
+            if (par.init_elliptical) { S.stage = STG_ELL1; S.use_xi = 0; S.pc = PC_IPMSTART; }
+            else S.pc = PC_BEGIN_DSM;
+            break;
+        }
+        case PC_IPMSTART: {
+            ipm_begin(S);
+            REQUEST(V_X, V_G, 1, PC_TOP, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+            break;
+        }
+        // ---- cvxopt.solvers.cp, scalar-epigraph specialisation (oracle/cpsolver.py::cp) ----
+        case PC_TOP: {                       // F(x), Df(x) and H = z * Hess f(x) are in (f0, g, P.H)
+            const double f = f0 - S.t;
+            S.gap = S.s * S.z;
+            S.rxt = 1.0 - S.z;
+            double gg;
+            { double a = 0; for (int i = tid; i < Nc; i += BLOCK) { const double r = S.z * g[i]; a += r * r; } gg = block_sum1<BLOCK>(a, sm.red_part, sm.red_out); }
+            S.resx = sqrt(gg + S.rxt * S.rxt);
+            S.rznl = S.s + f; S.resznl = fabs(S.rznl);
+            const double pcost = S.t, dcost = pcost + S.z * S.rznl - S.gap;
+            double relgap = -1.0;   // None
+            if (pcost < 0.0) relgap = S.gap / -pcost; else if (dcost > 0.0) relgap = S.gap / dcost;
+            double pres = S.resznl, dres = S.resx;
+            if (S.iters == 0) {
+                const double resx0 = fmax(1.0, S.resx), resznl0 = fmax(1.0, S.resznl);
+                S.pres0 = fmax(1.0, pres); S.dres0 = fmax(1.0, dres);
+                S.th1 = 1.0 / S.gap; S.th2 = 1.0 / resx0; S.th3 = 1.0 / resznl0;
+            }
+            S.phi = S.th1 * S.gap + S.th2 * S.resx + S.th3 * S.resznl;
+            pres /= S.pres0; dres /= S.dres0;
+            if (trace && tid == 0) {
+                double* tr = trace + (size_t)S.iters * 8;
+                tr[0] = f0; tr[1] = S.gap; tr[2] = pres; tr[3] = dres; tr[4] = S.t; tr[5] = S.s; tr[6] = S.z; tr[7] = (double)S.relaxed;
+            }
+            if ((pres <= par.feastol && dres <= par.feastol && (S.gap <= par.abstol || (relgap >= 0.0 && relgap <= par.reltol))) || S.iters == par.maxiters) {
+                S.r_ipm = (S.iters == par.maxiters) ? 1 : 0;
+                S.pc = PC_IPMDONE;
+                break;
+            }
+            if (S.iters == 0) { S.d = sqrt(S.s / S.z); S.lm = sqrt(S.s * S.z); }
+            S.lmsq = S.lm * S.lm;
+            const bool ok = cholesky<BLOCK>(P.H, Nc, Lf, sm);
+            hres_alt = false;
+            if (ok) { S.pc = PC_KKT; break; }
+            if (S.iters == 0) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }                 // ValueError("Rank(A) < p or ...")
+            if (0 < S.relaxed && S.relaxed < MAX_RELAXED) {
+                // Restart a standard line search from the last saved state.  cvxopt re-evaluates F at the restored
+                // point inside the KKT solver only: cpl's residual closures keep the Df and H of the abandoned point.
+                S.phi = S.phi0s; S.gap = S.gap0s;
+                S.d = S.sv_d; S.lm = S.sv_lm; S.t = S.sv_t; S.s = S.sv_s; S.z = S.sv_z; S.lmsq = S.lm * S.lm;
+                __syncthreads();
+                for (int i = tid; i < Nc; i += BLOCK) { x[i] = sx[i]; sdx[i] = g[i]; }
+                for (size_t i = tid; i < (size_t)Nc * Nc; i += BLOCK) P.H2[i] = P.H[i];
+                S.rxt = S.sv_rxt; S.resx = S.sv_resx; S.rznl = S.sv_rznl; S.resznl = fabs(S.rznl);
+                S.relaxed = -1;
+                __syncthreads();
+                REQUEST(V_X, V_G, 1, PC_RESTORED, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+                break;
+            }
+            S.r_ipm = 1; S.pc = PC_IPMDONE;                                               // 'unknown' (singular KKT matrix)
+            break;
+        }
+        case PC_RESTORED: {
+            const bool ok = cholesky<BLOCK>(P.H, Nc, Lf, sm);
+            if (!ok) { S.r_ipm = 1; S.pc = PC_IPMDONE; break; }
+            hres_alt = true;
+            S.pc = PC_KKT;
+            break;
+        }
+        case PC_KKT: {
+            // KKT solves (cp's epigraph wrapper around kkt_chol2 + one step of iterative refinement).  With eta = 0 the
+            // x-part of both passes is the same vector: it is computed once (bit-identical to recomputing it).
+            const double* Hres = hres_alt ? P.H2 : P.H;
+            const double* gres = hres_alt ? sdx : g;
+            const double z = S.z, d = S.d;
+            S.bt = -S.rxt;
+            const double bt = S.bt;
+            __syncthreads();
+            for (int i = tid; i < Nc; i += BLOCK) { const double bx = -(z * g[i]); tv[i] = bx + g[i] * bt; }
+            chol_solve<BLOCK>(Lf, Nc, tv, bv, bvcap);
+            S.uz0 = -d * bt;
+            const double wz3 = S.uz0 / d;
+            S.vt = bt + wz3;
+            const double vt = S.vt;
+            {   // vx = bx - H ux - g wz3, then ex = K^-1 (vx + g vt)
+                constexpr int NW = BLOCK / 32;
+                const int lane = tid & 31, warp = tid >> 5;
+                for (int i = warp; i < Nc; i += NW) {
+                    double a = 0;
+                    const double* hr = Hres + (size_t)i * Nc;
+                    for (int j = lane; j < Nc; j += 32) a += hr[j] * tv[j];
+                    a = warp_sum(a);
+                    if (lane == 0) { const double vx = -(z * g[i]) - a - gres[i] * wz3; ev[i] = vx + g[i] * vt; }
+                }
+            }
+            S.gux = bdot<BLOCK>(g, tv, Nc, sm);
+            S.gux_res = hres_alt ? bdot<BLOCK>(gres, tv, Nc, sm) : S.gux;
+            chol_solve<BLOCK>(Lf, Nc, ev, bv, bvcap);
+            S.gex = bdot<BLOCK>(g, ev, Nc, sm);
+            for (int i = tid; i < Nc; i += BLOCK) dx[i] = tv[i] + ev[i];
+            __syncthreads();
+            S.sigma = 0.0; S.eta = 0.0; S.step = 1.0; S.pass = 0;
+            S.pc = PC_PASS;
+            break;
+        }
+        case PC_PASS: {
+            const double d = S.d, lm = S.lm;
+            const double mu = S.gap;
+            const double bs = -S.lmsq + S.sigma * mu;
+            const double bz = -(1.0 - S.eta) * S.rznl;
+            // f4_no_ir
+            const double bs1 = bs / lm, bz1 = bz - d * bs1;
+            double uz = S.uz0, ut = S.gux + d * d * S.bt - bz1, us = bs1 - uz;
+            // residual + second f4_no_ir
+            const double vz = bz - (S.gux_res - ut) - d * us;
+            const double vs = bs - lm * (uz + us);
+            const double vs1 = vs / lm, vz1 = vz - d * vs1;
+            const double ez = -d * S.vt, et = S.gex + d * d * S.vt - vz1, es = vs1 - ez;
+            ut += et; uz += ez; us += es;
+            S.dt = ut; S.dz = uz; S.ds = us;
+            S.dsdz = S.ds * S.dz;
+            S.dz2 = S.dz / d; S.ds2 = S.ds * d;
+            S.ds /= lm; S.dz /= lm;
+            const double tmax = fmax(0.0, fmax(-S.ds, -S.dz));
+            S.step = (tmax == 0.0) ? 1.0 : fmin(1.0, CP_STEP / tmax);
+            S.phi = S.th1 * S.gap + S.th2 * S.resx + S.th3 * S.resznl;
+            S.dphi = (S.pass == 0) ? -S.phi : (-S.th1 * (1 - S.sigma) * S.gap - S.th2 * (1 - S.eta) * S.resx - S.th3 * (1 - S.eta) * S.resznl);
+            S.pc = PC_TRIALREQ;
+            break;
+        }
+        case PC_TRIALREQ: {
+            __syncthreads();
+            for (int i = tid; i < Nc; i += BLOCK) nx[i] = x[i] + S.step * dx[i];
+            __syncthreads();
+            REQUEST(V_NX, V_NG, 0, PC_TRIAL, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+            break;
+        }
+        case PC_TRIAL: {                     // F and Df at x + step dx are in (f0, ng)
+            const double step = S.step;
+            const double newt = S.t + step * S.dt, newz = S.z + step * S.dz2, news = S.s + step * S.ds2;
+            const double newf = f0 - newt;
+            double ngg;
+            { double a = 0; for (int i = tid; i < Nc; i += BLOCK) { const double r = newz * ng[i]; a += r * r; } ngg = block_sum1<BLOCK>(a, sm.red_part, sm.red_out); }
+            const double nrxt = 1.0 - newz;
+            const double newresx = sqrt(ngg + nrxt * nrxt);
+            const double newresznl = fabs(news + newf);
+            const double newgap = (1.0 - (1.0 - S.sigma) * step) * S.gap + step * step * S.dsdz;
+            const double newphi = S.th1 * newgap + S.th2 * newresx + S.th3 * newresznl;
+            bool backtrack = true;
+            if (S.pass == 0) {
+                if (newgap <= (1.0 - CP_ALPHA * step) * S.gap && ((0 <= S.relaxed && S.relaxed < MAX_RELAXED) || newphi <= S.phi + CP_ALPHA * step * S.dphi)) {
+                    backtrack = false;
+                    const double r = newgap / S.gap;
+                    S.sigma = fmin(r, r * r * r);
+                    S.eta = 0.0;
+                } else S.step *= CP_BETA;
+            } else {
+                if (S.relaxed == -1) {
+                    if (newphi <= S.phi + CP_ALPHA * step * S.dphi) backtrack = false; else S.step *= CP_BETA;
+                } else if (S.relaxed == 0) {
+                    if (newphi <= S.phi + CP_ALPHA * step * S.dphi) S.relaxed = 0;
+                    else {
+                        S.phi0s = S.phi; S.dphi0s = S.dphi; S.gap0s = S.gap; S.step0s = step;
+                        S.sv_d = S.d; S.sv_lm = S.lm; S.sv_t = S.t; S.sv_s = S.s; S.sv_z = S.z;
+                        S.sv_rxt = S.rxt; S.sv_resx = S.resx; S.sv_rznl = S.rznl;
+                        __syncthreads();
+                        for (int i = tid; i < Nc; i += BLOCK) { sx[i] = x[i]; sdx[i] = dx[i]; }
+                        __syncthreads();
+                        S.sv_dt = S.dt; S.sv_dz = S.dz; S.sv_ds = S.ds;
+                        S.dsdz0s = S.dsdz; S.sigma0s = S.sigma; S.eta0s = S.eta;
+                        S.relaxed = 1;
+                    }
+                    backtrack = false;
+                } else if (S.relaxed < MAX_RELAXED) {
+                    if (newphi <= S.phi0s + CP_ALPHA * S.step0s * S.dphi0s) S.relaxed = 0; else S.relaxed += 1;
+                    backtrack = false;
+                } else {   // relaxed == MAX_RELAXED
+                    if (newphi <= S.phi0s + CP_ALPHA * S.step0s * S.dphi0s) { backtrack = false; S.relaxed = 0; }
+                    else if (newphi >= S.phi0s) {
+                        // resume the last saved line search
+                        S.phi = S.phi0s; S.dphi = S.dphi0s; S.gap = S.gap0s; S.step = S.step0s;
+                        S.d = S.sv_d; S.lm = S.sv_lm; S.lmsq = S.lm * S.lm; S.t = S.sv_t; S.s = S.sv_s; S.z = S.sv_z;
+                        S.rxt = S.sv_rxt; S.resx = S.sv_resx; S.rznl = S.sv_rznl; S.resznl = fabs(S.rznl);
+                        __syncthreads();
+                        for (int i = tid; i < Nc; i += BLOCK) { x[i] = sx[i]; dx[i] = sdx[i]; }
+                        __syncthreads();
+                        S.dt = S.sv_dt; S.dz = S.sv_dz; S.ds = S.sv_ds;
+                        S.dz2 = S.dz * S.lm / S.d; S.ds2 = S.ds * S.lm * S.d;
+                        S.dsdz = S.dsdz0s; S.sigma = S.sigma0s; S.eta = S.eta0s;
+                        S.relaxed = -1;
+                    } else if (newphi <= S.phi + CP_ALPHA * step * S.dphi) { backtrack = false; S.relaxed = -1; }
+                    else { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }   // cvxopt would repeat this trial until the reference's SIGALRM time-out fires
+                }
+            }
+            if (backtrack) S.pc = PC_TRIALREQ;
+            else if (S.pass == 0) { S.pass = 1; S.pc = PC_PASS; }
+            else S.pc = PC_ACCEPT;
+            break;
+        }
+        case PC_ACCEPT: {
+            __syncthreads();
+            for (int i = tid; i < Nc; i += BLOCK) x[i] = x[i] + S.step * dx[i];
+            S.t = S.t + S.step * S.dt;
+            const double ds = (1.0 + S.step * S.ds) * S.lm;
+            const double dz = (1.0 + S.step * S.dz) * S.lm;
+            const double sq_s = sqrt(ds), sq_z = sqrt(dz);
+            S.d = S.d * sq_s / sq_z;
+            S.lm = sq_s * sq_z;
+            S.s = S.lm * S.d;
+            S.z = S.lm / S.d;
+            S.iters += 1;
+            __syncthreads();
+            REQUEST(V_X, V_G, 1, PC_TOP, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+            break;
+        }
+        // ---- the driver around the solves: objects.py:321-358 (elliptical initialisation), 361-412 (cvxprog) ----
+        case PC_IPMDONE: {
+            const int r = S.r_ipm;
+            if (S.stage == STG_TRACE) { S.pc = PC_DONE; yield = true; break; }
+            if (S.stage == STG_ELL1) {
+                S.it1 = S.iters; S.bits |= r; S.have1 = (r != 2);
+                if (r == 0) { S.pc = PC_BEGIN_DSM; break; }
+                if (S.have1) {
+                    __syncthreads();
+                    for (int i = tid; i < 6; i += BLOCK) w6[i] = x[i];        // pass-1 solution
+                    __syncthreads();
+                    REQUEST(V_X, V_G, 0, PC_VAL1, { S.val1 = NAN; S.pc = PC_EST_INIT; });
+                } else { S.val1 = INFINITY; S.pc = PC_EST_INIT; }
+                break;
+            }
+            if (S.stage == STG_ELL2) {
+                S.it2 = S.iters; S.bits |= r << 2;
+                if (r == 2) {
+                    if (!S.have1) { S.status = SDSM_ST_ERROR; S.pc = PC_FINISH; break; }   // CvxprogError (objects.py:351-353)
+                    __syncthreads();
+                    for (int i = tid; i < 6; i += BLOCK) x[i] = w6[i];
+                    __syncthreads();
+                }
+                S.pc = PC_BEGIN_DSM;
+                break;
+            }
+            // STG_DSM (objects.py:393-410)
+            S.it3 = S.iters; S.bits |= r << 4;
+            if (r == 0) { S.energy = S.psi_last; S.pc = PC_FINISH; break; }
+            if (r == 1) {
+                // status 'unknown': accepted unless the energy got worse than at the initialisation (objects.py:399-403);
+                // J(x) is the value of the evaluation that ended the solve
+                S.energy = S.psi_last;
+                REQUEST(V_X0, V_NG, 0, PC_J0, { S.pc = PC_FINISH; });
+                break;
+            }
+            // the solver raised: fall back to the initialisation
+            S.status = SDSM_ST_FALLBACK;
+            __syncthreads();
+            for (int i = tid; i < Nc; i += BLOCK) x[i] = x0[i];
+            __syncthreads();
+            REQUEST(V_X, V_NG, 0, PC_FINAL, { S.energy = NAN; S.pc = PC_FINISH; });
+            break;
+        }
+        case PC_VAL1: { S.val1 = S.psi_last; S.pc = PC_EST_INIT; break; }
+        case PC_EST_INIT: {
+            const uint16_t* inv_r = ws.inv + cd.tab_off; const uint16_t* inv_c = inv_r + cd.h;
+            const bool ok = estimate_initialization<BLOCK>(P, sm, img, cd, inv_r, inv_c, x);
+            if (!ok) { S.status = SDSM_ST_ERROR; S.pc = PC_FINISH; break; }                // the reference raises here
+            REQUEST(V_X, V_G, 0, PC_VALINIT, { S.stage = STG_ELL2; S.pc = PC_IPMSTART; });
+            break;
+        }
+        case PC_VALINIT: {
+            const double init_val = S.psi_last;
+            if (init_val > S.val1) {                                                        // "initialization worse than previous solution"
+                __syncthreads();
+                for (int i = tid; i < 6; i += BLOCK) x[i] = w6[i];
+                __syncthreads();
+                S.pc = PC_BEGIN_DSM;
+            } else { S.stage = STG_ELL2; S.pc = PC_IPMSTART; }
+            break;
+        }
+        case PC_BEGIN_DSM: {
+            S.stage = STG_DSM;
+            S.use_xi = P.m > 0 ? 1 : 0;
+            const int Nd = S.use_xi ? P.N : 6;
+            __syncthreads();
+            for (int i = tid + 6; i < Nd; i += BLOCK) x[i] = 0.0;
+            __syncthreads();
+            for (int i = tid; i < Nd; i += BLOCK) x0[i] = x[i];
+            if (S.use_xi) for (size_t i = tid; i < (size_t)Nd * Nd; i += BLOCK) P.H[i] = 0.0;
+            __syncthreads();
+            S.pc = PC_IPMSTART;
+            break;
+        }
+        case PC_J0: {
+            const double j0 = S.psi_last;
+            if (S.energy > j0) {
+                S.status = SDSM_ST_FALLBACK;
+                S.energy = j0;
+                __syncthreads();
+                for (int i = tid; i < Nc; i += BLOCK) x[i] = x0[i];
+                __syncthreads();
+            }
+            S.pc = PC_FINISH;
+            break;
+        }
+        case PC_FINAL: { S.energy = S.psi_last; S.pc = PC_FINISH; break; }
+        case PC_FINISH: {
+            if (S.status == SDSM_ST_OPTIMAL || S.status == SDSM_ST_FALLBACK) {
+                double* pout = out.d_params + cd.par_off;
+                const int Nf = 6 + P.m;
+                for (int i = tid; i < Nf; i += BLOCK) pout[i] = (i < Nc) ? x[i] : 0.0;
+            }
+            if (tid == 0) {
+                out.d_status[c] = S.status;
+                out.d_energy[c] = (S.status == SDSM_ST_OPTIMAL || S.status == SDSM_ST_FALLBACK) ? S.energy : 0.0;
+                info[1] = S.it1; info[2] = S.it2; info[3] = S.it3; info[5] = S.bits; info[6] = S.nf; info[7] = S.nh;
+            }
+            S.pc = PC_DONE;
+            yield = true;
+            break;
+        }
+        default: { yield = true; break; }    // PC_DONE
+        }
+    }
+#undef REQUEST
+    __syncthreads();
+    if (tid == 0) ws.cstate[c] = S;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// kernels
+
+// Round 0 (order != nullptr): CTA b starts candidate order[b].  Later rounds: CTA b advances the b-th live candidate of
+// work list `parity`.  Requests go to work list parity ^ 1.
+__global__ void __launch_bounds__(CTRL_BLOCK, 4)
+k_ctrl(Img img, Par par, const sdsm_cand* __restrict__ cands, const int32_t* __restrict__ order, int n_first, WS ws, sdsm_out out,
+       int parity, int lcap, double* trace)
+{
+    extern __shared__ __align__(16) char smem_ctrl[];
+    Sm sm;
+    carve_smem(sm, smem_ctrl, lcap);
+    int c;
+    if (order) {
+        if ((int)blockIdx.x >= n_first) return;
+        c = order[blockIdx.x];
+    } else {
+        const int n_live = (int)(ws.counters[parity] >> 32);
+        if ((int)blockIdx.x >= n_live) return;
+        c = ws.live[(size_t)parity * ws.n_cand + blockIdx.x];
+    }
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    ctrl_step<CTRL_BLOCK>(par, img, cd, ci, ws, c, parity, sm, out, trace);
+}
+
+// Publishes the size of work list `parity` for the host (pinned memory), after k_ctrl has filled it.
+__global__ void k_publish(WS ws, int parity, unsigned long long* host_flag)
+{
+    *host_flag = ws.counters[parity];
+}
+
+// Result rasterisation (objects.py:198-211): foreground inside omega, its bounding box, on_boundary.  One CTA per candidate.
+constexpr int FIN_BLOCK = 256;
+__global__ void __launch_bounds__(FIN_BLOCK)
+k_finish(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, sdsm_out out)
+{
+    constexpr int BLOCK = FIN_BLOCK;
+    __shared__ int s_box[4];
+    __shared__ int s_any;
+    __shared__ int s_slotj[(BLOCK / 32) * 32];
+    const int tid = threadIdx.x;
+    for (int c = blockIdx.x; c < n_cand; c += gridDim.x) {
+        const int status = out.d_status[c];
+        if (status != SDSM_ST_OPTIMAL && status != SDSM_ST_FALLBACK) continue;
+        const sdsm_cand cd = cands[c];
+        const CInfo ci = ws.cinfo[c];
+        const double* x = out.d_params + cd.par_off;
+        const bool use_xi = ci.m > 0;
+        const int32_t* cstart = ws.cell_start + cd.cell_off;
+        const uint32_t* amask = ws.cell_amask + cd.cell_off;
+        const int32_t* cellmap = ws.cellmap + cd.cell_off;
+        const uint32_t* prc_c = ws.pix_rc + cd.pix_off;
+        const float* gv = ws.gval + (size_t)NSLOT * cd.pix_off;
+        const uint16_t* inv_r = ws.inv + cd.tab_off; const uint16_t* inv_c = inv_r + cd.h;
+        // model in the pixel coordinates of the image padded by 1 (dsm.py:113-128 with roi = whole image, pad = 1)
+        const double gr = 1.0 / ((double)img.H - 1.0), gc = 1.0 / ((double)img.W - 1.0);
+        const double A11 = x[0], A22 = x[1], A12 = x[2], pb1 = x[3], pb2 = x[4], pc = x[5];
+        const double v1 = -gr, v2 = -gc;
+        const double M11 = gr * A11 * gr, M12 = gr * A12 * gc, M22 = gc * A22 * gc;
+        const double mb1 = gr * (A11 * v1 + A12 * v2 + pb1), mb2 = gc * (A12 * v1 + A22 * v2 + pb2);
+        const double mc = (v1 * (A11 * v1 + A12 * v2) + v2 * (A12 * v1 + A22 * v2)) + 2 * (pb1 * v1 + pb2 * v2) + pc;
+        __syncthreads();
+        if (tid == 0) { s_box[0] = 0x7fffffff; s_box[1] = -1; s_box[2] = 0x7fffffff; s_box[3] = -1; s_any = 0; }
+        __syncthreads();
+        {
+            // foreground inside omega: S > 0 (objects.py:200-204); G~ xi through the cell structure
+            constexpr int NW = BLOCK / 32;
+            const int lane = tid & 31, warp = tid >> 5;
+            int* slotj = s_slotj + warp * 32;
+            uint8_t* fg = out.d_fgmask + cd.fg_off;
+            for (int cell = warp; cell < ci.ncells; cell += NW) {
+                const int st = cstart[cell], npix = cstart[cell + 1] - st;
+                if (npix == 0) continue;
+                int na = 0;
+                if (use_xi) {
+                    const uint32_t am = amask[cell];
+                    na = __popc(am);
+                    const int ca = cell / ci.cw, cb = cell - ca * ci.cw;
+                    __syncwarp();
+                    if (lane < na) { const int sl = nth_set_bit(am, lane); slotj[lane] = cellmap[(ca + sl / 5 - NC) * ci.cw + (cb + sl % 5 - NC)]; }
+                    __syncwarp();
+                }
+                const float* gcell = gv + (size_t)NSLOT * st;
+                for (int p = lane; p < npix; p += 32) {
+                    const uint32_t rc = prc_c[st + p];
+                    const int br = inv_r[rc & 0xffffu], bc = inv_c[rc >> 16];
+                    const double X1 = (double)(cd.r0 + br + 1), X2 = (double)(cd.c0 + bc + 1);
+                    double S = (X1 * M11 + X2 * M12) * X1 + (X1 * M12 + X2 * M22) * X2 + 2 * (X1 * mb1 + X2 * mb2) + mc;
+                    double sxi = 0;
+                    for (int a = 0; a < na; ++a) sxi += (double)gcell[(size_t)a * npix + p] * x[6 + slotj[a]];
+                    S += sxi;
+                    if (S > 0) {
+                        fg[(size_t)br * cd.w + bc] = 1;
+                        atomicMin(&s_box[0], br); atomicMax(&s_box[1], br); atomicMin(&s_box[2], bc); atomicMax(&s_box[3], bc);
+                    }
+                }
+            }
+            // on_boundary: S > 0 anywhere on the 1-pixel pad ring (objects.py:209); only the polynomial lives there
+            const int HP = img.H + 2, WP = img.W + 2;
+            int any = 0;
+            for (int k = tid; k < 2 * WP + 2 * HP; k += BLOCK) {
+                double X1, X2;
+                if (k < WP) { X1 = 0; X2 = k; }
+                else if (k < 2 * WP) { X1 = HP - 1; X2 = k - WP; }
+                else if (k < 2 * WP + HP) { X1 = k - 2 * WP; X2 = 0; }
+                else { X1 = k - 2 * WP - HP; X2 = WP - 1; }
+                const double S = (X1 * M11 + X2 * M12) * X1 + (X1 * M12 + X2 * M22) * X2 + 2 * (X1 * mb1 + X2 * mb2) + mc;
+                any |= (S > 0);
+            }
+            if (any) s_any = 1;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            out.d_onboundary[c] = (uint8_t)s_any;
+            if (s_box[1] >= 0) { out.d_fgbox[c * 4 + 0] = s_box[0]; out.d_fgbox[c * 4 + 1] = s_box[1]; out.d_fgbox[c * 4 + 2] = s_box[2]; out.d_fgbox[c * 4 + 3] = s_box[3]; }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// diagnostics for the parity tests (single candidate of the last solved batch)
+
+// files the evaluation of F (with Hessian) of candidate c at xin into work list `parity ^ 1`
+__global__ void __launch_bounds__(CTRL_BLOCK)
+k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, const double* __restrict__ xin, int parity, int lcap)
+{
+    extern __shared__ __align__(16) char smem_ctrl[];
+    Sm sm;
+    carve_smem(sm, smem_ctrl, lcap);
+    const int tid = threadIdx.x;
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    CState S = ws.cstate[c];
+    Prob P;
+    setup_problem(P, par, cd, ci, ws);
+    S.use_xi = P.m > 0 ? 1 : 0;
+    const int N = P.N;
+    double* nx = P.V + (size_t)V_NX * P.ld;
+    for (int i = tid; i < N; i += CTRL_BLOCK) nx[i] = xin[i];
+    for (size_t i = tid; i < (size_t)N * N; i += CTRL_BLOCK) P.H[i] = 0.0;
+    __syncthreads();
+    const bool ok = file_request<CTRL_BLOCK>(P, sm, S, ws, c, parity, V_NX, V_NG, 1);
+    S.pc = ok ? PC_DONE : -1;
+    __syncthreads();
+    if (tid == 0) ws.cstate[c] = S;
+}
+
+__global__ void __launch_bounds__(CTRL_BLOCK)
+k_diag_eval_end(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, double* value, double* grad, double* Hout, int lcap)
+{
+    extern __shared__ __align__(16) char smem_ctrl[];
+    Sm sm;
+    carve_smem(sm, smem_ctrl, lcap);
+    const int tid = threadIdx.x;
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    Prob P;
+    setup_problem(P, par, cd, ci, ws);
+    P.scale_cp = 1.0;
+    const int N = P.N;
+    double* g = P.V + (size_t)V_NG * P.ld;
+    const double* xe = P.V + (size_t)V_NX * P.ld;
+    double psi = 0;
+    double f;
+    if (ws.cstate[c].pc == -1) f = NAN;
+    else if (P.m > 0) f = gather_cells<CTRL_BLOCK, true>(P, sm, xe, g, 1.0, &psi);
+    else f = gather_poly<CTRL_BLOCK, true>(P, sm, g, 1.0, &psi);
+    __syncthreads();
+    if (tid == 0) *value = f;
+    for (int i = tid; i < N; i += CTRL_BLOCK) grad[i] = g[i];
+    for (size_t i = tid; i < (size_t)N * N; i += CTRL_BLOCK) Hout[i] = P.H[i];
+}
+
+// starts one interior-point solve of candidate c from x0 (STG_TRACE); k_ctrl rounds record the iterates
+__global__ void __launch_bounds__(CTRL_BLOCK)
+k_diag_trace_begin(Par par, const sdsm_cand* __restrict__ cands, int c, int use_xi_, WS ws, const double* __restrict__ x0, int parity, int lcap)
+{
+    extern __shared__ __align__(16) char smem_ctrl[];
+    Sm sm;
+    carve_smem(sm, smem_ctrl, lcap);
+    const int tid = threadIdx.x;
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    CState S = ws.cstate[c];
+    Prob P;
+    setup_problem(P, par, cd, ci, ws);
+    S.use_xi = (use_xi_ && P.m > 0) ? 1 : 0;
+    S.stage = STG_TRACE;
+    const int N = S.use_xi ? P.N : 6;
+    double* x = P.V + (size_t)V_X * P.ld;
+    for (int i = tid; i < N; i += CTRL_BLOCK) x[i] = x0[i];
+    if (S.use_xi) for (size_t i = tid; i < (size_t)N * N; i += CTRL_BLOCK) P.H[i] = 0.0;
+    __syncthreads();
+    ipm_begin(S);
+    S.r_ipm = 0;
+    if (file_request<CTRL_BLOCK>(P, sm, S, ws, c, parity, V_X, V_G, 1)) S.pc = PC_TOP;
+    else { S.r_ipm = 2; S.pc = PC_DONE; }
+    __syncthreads();
+    if (tid == 0) ws.cstate[c] = S;
+}
+
+__global__ void k_diag_trace_end(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, double* xout, int32_t* status_iters)
+{
+    const sdsm_cand cd = cands[c];
+    const CState* S = ws.cstate + c;
+    const int ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
+    const int N = S->use_xi ? 6 + ws.cinfo[c].m : 6;
+    const double* x = ws.vecs + cd.vec_off + (size_t)V_X * ld;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) xout[i] = x[i];
+    if (threadIdx.x == 0) { status_iters[0] = S->r_ipm; status_iters[1] = S->iters; }
+}
+
+// register-resident FP64 FMA peak (the FP64 roofline denominator; MEASURED_PEAKS.json has none)
+__global__ void __launch_bounds__(256) k_dfma_peak(double* out, int iters)
+{
+    double a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = 1.0 + 1e-9 * (threadIdx.x + k);
+    const double b = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) a[k] = fma(a[k], b, c);
+    }
+    double r = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) r += a[k];
+    if (r == 12345.678) out[0] = r;
+}
+
+__global__ void k_export(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, uint32_t* rc, int32_t* cols, float* vals, uint32_t* grid)
+{
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    const int32_t* cstart = ws.cell_start + cd.cell_off;
+    const uint32_t* prc = ws.pix_rc + cd.pix_off;
+    const float* gv = ws.gval + (size_t)NSLOT * cd.pix_off;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < ci.m; j += gridDim.x * blockDim.x) grid[j] = ws.grid_rc[cd.cell_off + j];
+    for (int cell = blockIdx.x; cell < ci.ncells; cell += gridDim.x) {
+        const int st = cstart[cell], npix = cstart[cell + 1] - st;
+        const uint32_t am = ci.m > 0 ? ws.cell_amask[cd.cell_off + cell] : 0u;
+        const int na = __popc(am);
+        const int ca = cell / ci.cw, cb = cell - ca * ci.cw;
+        for (int p = threadIdx.x; p < npix; p += blockDim.x) {
+            rc[st + p] = prc[st + p];
+            for (int a = 0; a < NSLOT; ++a) {
+                int col = -1; float v = 0.f;
+                if (a < na) {
+                    const int s = nth_set_bit(am, a);
+                    col = ws.cellmap[cd.cell_off + (ca + s / 5 - NC) * ci.cw + (cb + s % 5 - NC)];
+                    v = gv[(size_t)NSLOT * st + (size_t)a * npix + p];
+                }
+                cols[(size_t)(st + p) * NSLOT + a] = col;
+                vals[(size_t)(st + p) * NSLOT + a] = v;
+            }
+        }
+    }
+}
+
+}  // namespace sdsm

@@ -118,7 +118,7 @@ k_pack(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const 
         for (int i = tid; i <= ncells; i += BLOCK) cstart[i] = 0;
         if (tid == 0) {
             CInfo ci;
-            ci.hp = hp; ci.wp = wp; ci.ch = ch; ci.cw = cw; ci.ncells = ncells; ci.m = 0; ci.n_fg = n_fg;
+            ci.hp = hp; ci.wp = wp; ci.ch = ch; ci.cw = cw; ci.ncells = ncells; ci.m = 0; ci.n_fg = n_fg; ci.n_ne = 0; ci.pad = 0;
             ci.flags = (n_found != cd.n || n_found == 0) ? 1 : 0;
             ws.cinfo[c] = ci;
         }
@@ -133,6 +133,17 @@ k_pack(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const 
                 const int cell = (fwd_r[r] / sub) * cw + (fwd_c[q] / sub);
                 atomicAdd(&cstart[cell], 1);
             }
+        }
+        __syncthreads();
+        // the non-empty cells, in cell order: the work items of k_eval
+        {
+            int32_t* pos = (int32_t*)(ws.grid_tmp + cd.cell_off);          // free until k_grid
+            int32_t* clist = ws.cell_list + cd.cell_off;
+            for (int i = tid; i <= ncells; i += BLOCK) pos[i] = (i < ncells && cstart[i] > 0) ? 1 : 0;
+            __syncthreads();
+            const int n_ne = excl_scan_i32<BLOCK>(pos, ncells + 1, s_scan);
+            for (int i = tid; i < ncells; i += BLOCK) if (cstart[i] > 0) clist[pos[i]] = i;
+            if (tid == 0) ws.cinfo[c].n_ne = n_ne;
         }
         __syncthreads();
         excl_scan_i32<BLOCK>(cstart, ncells + 1, s_scan);

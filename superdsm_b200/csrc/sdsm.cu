@@ -8,7 +8,8 @@
 #include "common.cuh"
 #include "pack.cuh"
 #include "grid.cuh"
-#include "solver.cuh"
+#include "eval.cuh"
+#include "ctrl.cuh"
 
 using namespace sdsm;
 
@@ -22,8 +23,10 @@ struct sdsm_ctx {
     size_t psf_cap = 0;
     int64_t launches = 0;
     // totals of the last plan (the layout is a pure function of these)
-    int64_t P = 0, C = 0, T = 0;
+    int64_t P = 0, C = 0, T = 0, V = 0, M = 0;
     int32_t n_cand = 0;
+    unsigned long long* h_flag = nullptr;   // pinned: size of the next work list, published by the device every few rounds
+    int64_t rounds = 0;                      // rounds of the last solve (diagnostics)
     std::string err;
 };
 
@@ -50,16 +53,22 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     if (prop.major < 10) { ctx->err = "superdsm_b200 is built for sm_100a (B200) only"; return SDSM_E_UNSUPPORTED; }
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOLVER_SMEM));
+    const int ctrl_max = (int)ctrl_smem_bytes(SMEM_L_CAP);
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EVAL_SMEM));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_ctrl, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_begin, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_end, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_trace_begin, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
+    CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->h_flag, 64, cudaHostAllocDefault));
     return SDSM_OK;
 }
 
 extern "C" void sdsm_destroy(sdsm_ctx* ctx)
 {
     if (!ctx) return;
-    if (ctx->d_psf) { cudaSetDevice(ctx->device); cudaFree(ctx->d_psf); }
+    cudaSetDevice(ctx->device);
+    if (ctx->d_psf) cudaFree(ctx->d_psf);
+    if (ctx->h_flag) cudaFreeHost(ctx->h_flag);
     delete ctx;
 }
 
@@ -116,12 +125,13 @@ extern "C" int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* p)
     return SDSM_OK;
 }
 
+
 extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, sdsm_plan* plan)
 {
     if (!ctx || !cands || !plan || n_cand < 1) return SDSM_E_ARG;
     if (!ctx->have_par || !ctx->img.y) { ctx->err = "sdsm_set_image / sdsm_set_params must precede sdsm_plan_batch"; return SDSM_E_ARG; }
     const int sub = ctx->par.sub;
-    int64_t P = 0, C = 0, T = 0, PAR = 0, FG = 0;
+    int64_t P = 0, C = 0, T = 0, V = 0, M = 0, PAR = 0, FG = 0;
     int32_t n_max = 6, cells_max = 1;
     for (int32_t i = 0; i < n_cand; ++i) {
         sdsm_cand& c = cands[i];
@@ -130,42 +140,70 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
             return SDSM_E_ARG;
         }
         const int32_t cap = ((c.h + sub - 1) / sub) * ((c.w + sub - 1) / sub);
+        const int64_t ld = 6 + (ctx->par.has_smooth ? cap : 0);
         c.cell_cap = cap;
         c.pix_off = P;  P += (c.n + 31) / 32 * 32;
         c.cell_off = C; C += cap + 1;
         c.tab_off = T;  T += (c.h + c.w + 3) / 4 * 4;
-        c.par_off = PAR; PAR += 6 + (ctx->par.has_smooth ? cap : 0);
+        c.par_off = PAR; PAR += ld;
         c.fg_off = FG;  FG += (int64_t)c.h * c.w;
-        const int32_t nmax_c = 6 + (ctx->par.has_smooth ? cap : 0);
-        if (nmax_c > n_max) n_max = nmax_c;
+        c.vec_off = V;  V += (int64_t)NVEC * ld;
+        c.mat_off = M;  M += 2 * ld * ld + (ld * (ld + 1) / 2 + 1) / 2 * 2;
+        if (ld > n_max) n_max = (int32_t)ld;
         if (cap > cells_max) cells_max = cap;
     }
-    // persistent solver grid: two CTAs per SM, fewer if the per-CTA workspace of this batch is large
-    int ctas = 2 * ctx->sm_count;
-    if (ctas > n_cand) ctas = n_cand;
-    Layout L = make_layout(P, C, T, n_cand, n_max, cells_max, 1);
-    const size_t budget = (size_t)12 << 30;
-    if (L.cta_bytes * (size_t)ctas > budget) {
-        ctas = (int)(budget / L.cta_bytes);
-        if (ctas < 1) ctas = 1;
-    }
-    L = make_layout(P, C, T, n_cand, n_max, cells_max, ctas);
+    const Layout L = make_layout(P, C, T, V, M, n_cand);
     plan->workspace_bytes = L.total;
     plan->params_len = PAR;
     plan->fgmask_len = FG;
     plan->n_max = n_max;
     plan->cells_max = cells_max;
-    plan->solver_ctas = ctas;
-    plan->reserved = 0;
-    ctx->P = P; ctx->C = C; ctx->T = T; ctx->n_cand = n_cand;
+    plan->reserved0 = 0;
+    plan->reserved1 = 0;
+    ctx->P = P; ctx->C = C; ctx->T = T; ctx->V = V; ctx->M = M; ctx->n_cand = n_cand;
     return SDSM_OK;
 }
 
-static int check_plan(sdsm_ctx* ctx, const sdsm_plan* plan, int32_t n_cand, size_t workspace_bytes, Layout* L)
+static int check_plan(sdsm_ctx* ctx, int32_t n_cand, size_t workspace_bytes, Layout* L)
 {
     if (n_cand != ctx->n_cand) { ctx->err = "batch does not match the last sdsm_plan_batch"; return SDSM_E_ARG; }
-    *L = make_layout(ctx->P, ctx->C, ctx->T, n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    *L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, n_cand);
     if (L->total > workspace_bytes) { ctx->err = "workspace too small"; return SDSM_E_WORKSPACE; }
+    return SDSM_OK;
+}
+
+// Drives the lock-step rounds k_eval -> k_ctrl until no candidate is live.  `parity` names the work list that is ready.
+// The size of the next work list is published to pinned memory every few rounds; the host only waits on that.
+static int run_rounds(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_cands, const WS& ws, const sdsm_out& out, int lcap,
+                      int64_t live_bound, int64_t item_bound, int parity, double* trace)
+{
+    const size_t csmem = ctrl_smem_bytes(lcap);
+    const int max_rounds = 64 * (ctx->par.maxiters + 2) * 3;
+    int round = 0;
+    int burst = 4;
+    while (true) {
+        for (int b = 0; b < burst; ++b, ++round) {
+            int64_t ge = (item_bound + EVAL_WARPS - 1) / EVAL_WARPS;
+            const int64_t ge_max = (int64_t)ctx->sm_count * 16;
+            if (ge > ge_max) ge = ge_max;
+            if (ge < 1) ge = 1;
+            k_eval<<<(unsigned)ge, EVAL_BLOCK, EVAL_SMEM, stream>>>(ctx->par, d_cands, ws, parity);
+            k_ctrl<<<(unsigned)live_bound, CTRL_BLOCK, csmem, stream>>>(ctx->img, ctx->par, d_cands, nullptr, 0, ws, out, parity, lcap, trace);
+            ctx->launches += 2;
+            parity ^= 1;
+        }
+        k_publish<<<1, 1, 0, stream>>>(ws, parity, ctx->h_flag);
+        ctx->launches++;
+        CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+        const unsigned long long f = *(volatile unsigned long long*)ctx->h_flag;
+        const int64_t n_live = (int64_t)(f >> 32), n_items = (int64_t)(f & 0xffffffffull);
+        if (n_live == 0) break;
+        if (n_live > live_bound || n_items > item_bound) { ctx->err = "work list grew: internal error"; return SDSM_E_CUDA; }
+        live_bound = n_live; item_bound = n_items;
+        if (round > max_rounds) { ctx->err = "solver did not terminate within the round limit"; return SDSM_E_CUDA; }
+        if (burst < 8) burst *= 2;
+    }
+    ctx->rounds = round;
     return SDSM_OK;
 }
 
@@ -176,12 +214,13 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     if (!ctx || !plan || !d_cands || !d_footprints || !d_order || !d_workspace || !out) return SDSM_E_ARG;
     if (!out->d_energy || !out->d_status || !out->d_info || !out->d_params || !out->d_fgbox || !out->d_onboundary || !out->d_fgmask) return SDSM_E_ARG;
     Layout L;
-    int rc = check_plan(ctx, plan, n_cand, workspace_bytes, &L);
+    int rc = check_plan(ctx, n_cand, workspace_bytes, &L);
     if (rc) return rc;
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     WS ws = make_ws(d_workspace, L);
-    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(int32_t) * 16, stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.cstate, 0, sizeof(CState) * (size_t)n_cand, stream));
     CUDA_TRY(ctx, cudaMemsetAsync(out->d_fgmask, 0, (size_t)plan->fgmask_len, stream));
 
     const int pack_grid = n_cand < 8 * ctx->sm_count ? n_cand : 8 * ctx->sm_count;
@@ -194,7 +233,15 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
         k_grid<<<pack_grid, GRID_BLOCK, psf_bytes, stream>>>(ctx->par, d_cands, n_cand, d_order, ws);
         ctx->launches++;
     }
-    k_solve<<<plan->solver_ctas, SOLVER_BLOCK, SOLVER_SMEM, stream>>>(ctx->img, ctx->par, d_cands, n_cand, d_order, ws, *out);
+    const int lcap = ctrl_lcap(plan->n_max);
+    // round 0: every candidate starts (work list 0 receives the first requests)
+    k_ctrl<<<n_cand, CTRL_BLOCK, ctrl_smem_bytes(lcap), stream>>>(ctx->img, ctx->par, d_cands, d_order, n_cand, ws, *out, 1, lcap, nullptr);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    rc = run_rounds(ctx, stream, d_cands, ws, *out, lcap, n_cand, ctx->C, 0, nullptr);
+    if (rc) return rc;
+    const int fin_grid = n_cand < 16 * ctx->sm_count ? n_cand : 16 * ctx->sm_count;
+    k_finish<<<fin_grid, FIN_BLOCK, 0, stream>>>(ctx->img, ctx->par, d_cands, n_cand, ws, *out);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
@@ -204,11 +251,17 @@ extern "C" int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const s
                                    double* d_value, double* d_grad, double* d_H, void* d_workspace, void* stream_)
 {
     if (!ctx || !plan || !d_cands || !d_x || !d_value || !d_grad || !d_H || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->n_cand);
     WS ws = make_ws(d_workspace, L);
+    cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    k_eval<<<1, SOLVER_BLOCK, SOLVER_SMEM, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, ws, d_x, d_value, d_grad, d_H);
-    ctx->launches++;
+    const int lcap = ctrl_lcap(plan->n_max);
+    const size_t csmem = ctrl_smem_bytes(lcap);
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
+    k_diag_eval_begin<<<1, CTRL_BLOCK, csmem, stream>>>(ctx->par, d_cands, c, ws, d_x, 1, lcap);
+    k_eval<<<ctx->sm_count, EVAL_BLOCK, EVAL_SMEM, stream>>>(ctx->par, d_cands, ws, 0);
+    k_diag_eval_end<<<1, CTRL_BLOCK, csmem, stream>>>(ctx->par, d_cands, c, ws, d_value, d_grad, d_H, lcap);
+    ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
 }
@@ -217,7 +270,7 @@ extern "C" int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sd
                                   int32_t* d_cols, float* d_vals, uint32_t* d_grid, void* d_workspace, void* stream_)
 {
     if (!ctx || !plan || !d_cands || !d_rc || !d_cols || !d_vals || !d_grid || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->n_cand);
     WS ws = make_ws(d_workspace, L);
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     k_export<<<64, 128, 0, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, ws, d_rc, d_cols, d_vals, d_grid);
@@ -230,10 +283,18 @@ extern "C" int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
                                 const double* d_x0, double* d_trace, double* d_xout, int32_t* d_status_iters, void* d_workspace, void* stream_)
 {
     if (!ctx || !plan || !d_cands || !d_x0 || !d_trace || !d_xout || !d_status_iters || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->n_cand, plan->n_max, plan->cells_max, plan->solver_ctas);
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->n_cand);
     WS ws = make_ws(d_workspace, L);
+    cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    k_trace<<<1, SOLVER_BLOCK, SOLVER_SMEM, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, use_xi, ws, d_x0, d_trace, d_xout, d_status_iters);
+    const int lcap = ctrl_lcap(plan->n_max);
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
+    k_diag_trace_begin<<<1, CTRL_BLOCK, ctrl_smem_bytes(lcap), stream>>>(ctx->par, d_cands, c, use_xi, ws, d_x0, 1, lcap);
+    ctx->launches++;
+    sdsm_out none{};   // STG_TRACE never writes results
+    int rc = run_rounds(ctx, stream, d_cands, ws, none, lcap, 1, ctx->C, 0, d_trace);
+    if (rc) return rc;
+    k_diag_trace_end<<<1, 128, 0, stream>>>(ctx->par, d_cands, c, ws, d_xout, d_status_iters);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;

@@ -18,11 +18,11 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(_lib.EXPORTS)
     lib = _lib.load()
     for name in declared: assert hasattr(lib, name), name
-    assert lib.sdsm_abi_version() == 1
+    assert lib.sdsm_abi_version() == 2
 
 
 def test_struct_layouts_match_the_header():
-    assert _lib.CAND_DTYPE.itemsize == 72 and _lib.CAND_DTYPE.fields['pix_off'][1] == 32
+    assert _lib.CAND_DTYPE.itemsize == 88 and _lib.CAND_DTYPE.fields['pix_off'][1] == 32
     assert ctypes.sizeof(_lib.Params) == 88 and ctypes.sizeof(_lib.Plan) == 40 and ctypes.sizeof(_lib.Out) == 56
 
 
