@@ -143,6 +143,9 @@ int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flo
 /* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
 int64_t sdsm_launch_count(const sdsm_ctx* ctx);
 
+/* number of lock-step rounds (one k_eval + one k_ctrl launch each) the last sdsm_solve_batch() took */
+int64_t sdsm_round_count(const sdsm_ctx* ctx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,6 +19,8 @@ constexpr int TILE_DOUBLES = 32 * TILE_LD + 64;                 // tile + u[32] 
 constexpr int CTRL_BLOCK = 128;   // k_ctrl: one CTA per live candidate
 constexpr int CTRL_WARPS = CTRL_BLOCK / 32;
 constexpr int SMEM_L_CAP = 5504;  // doubles of shared memory for the packed Cholesky factor (N <= 104)
+constexpr int SMALL_N_MAX = 104;  // systems up to this size are factorised in shared memory by k_ctrl, larger ones by k_ctrl_big
+constexpr int BIG_BLOCK  = 256;   // k_ctrl_big
 constexpr int NVEC       = 12;    // N-vectors of the interior-point solver
 
 struct Img { const double* y; const int32_t* atoms; int32_t H, W; };
@@ -84,8 +86,9 @@ struct WS {
     double*   vecs;        // [V]      NVEC vectors of length 6 + cell_cap per candidate
     double*   mats;        // [M]      H, H2 (N x N) and the packed Cholesky factor per candidate
     uint2*    items;       // [2 * C]  work lists of k_eval (candidate, cell), double-buffered by round parity
-    int32_t*  live;        // [2 * n_cand]  live candidates of a round, double-buffered
-    unsigned long long* counters;   // [16]  [0], [1]: (#live << 32 | #items) of the two work lists
+    uint2*    hitems;      // [2 * C]  work lists of k_hgather (candidate, grid point), double-buffered
+    int32_t*  live;        // [2 * n_cand]  live candidates of a round (small systems from the front, big ones from the back)
+    unsigned long long* counters;   // [16]  [p]: (#live small << 32 | #items), [2 + p]: (#live big << 32 | #hitems), p = parity
     int64_t   items_cap;
     int32_t   n_cand;
 };
@@ -93,7 +96,7 @@ struct WS {
 struct Layout {
     size_t total;
     size_t o_pix_y, o_pix_rc, o_pix_s, o_pix_dist, o_gval, o_cell_start, o_cell_amask, o_cellmap, o_grid_rc, o_grid_tmp, o_cell_list,
-           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_scrH, o_vecs, o_mats, o_items, o_live, o_counters;
+           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_scrH, o_vecs, o_mats, o_items, o_hitems, o_live, o_counters;
     int64_t C;
     int32_t n_cand;
 };
@@ -128,6 +131,7 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_vecs = take(sizeof(double) * V);
     L.o_mats = take(sizeof(double) * M);
     L.o_items = take(sizeof(uint2) * 2 * C);
+    L.o_hitems = take(sizeof(uint2) * 2 * C);
     L.o_live = take(sizeof(int32_t) * 2 * (size_t)n_cand);
     L.o_counters = take(sizeof(unsigned long long) * 16);
     L.C = C;
@@ -162,6 +166,7 @@ inline WS make_ws(void* base, const Layout& L)
     w.vecs = (double*)(b + L.o_vecs);
     w.mats = (double*)(b + L.o_mats);
     w.items = (uint2*)(b + L.o_items);
+    w.hitems = (uint2*)(b + L.o_hitems);
     w.live = (int32_t*)(b + L.o_live);
     w.counters = (unsigned long long*)(b + L.o_counters);
     w.items_cap = L.C;

@@ -36,6 +36,7 @@ struct Sm {
     double* red_out;   // [32]
     int*    flag;      // [8]
     int     lcap;      // doubles available for the factor
+    double *D, *Xj, *yv;   // k_ctrl_big only: diagonal block, panel block, solved block (see cholesky_big)
 };
 constexpr int CTRL_BPAD = 128;
 __host__ __device__ inline size_t ctrl_smem_bytes(int lcap) { return sizeof(double) * (size_t)(lcap + CTRL_BPAD + CTRL_WARPS * 32 + 32) + sizeof(int) * 8; }
@@ -49,6 +50,7 @@ __device__ __forceinline__ void carve_smem(Sm& sm, char* base, int lcap)
     sm.red_out = sm.red_part + CTRL_WARPS * 32;
     sm.flag = (int*)(sm.red_out + 32);
     sm.lcap = lcap;
+    sm.D = sm.Xj = sm.yv = nullptr;
 }
 
 __device__ __forceinline__ void setup_problem(Prob& P, const Par& par, const sdsm_cand& cd, const CInfo& ci, const WS& ws)
@@ -173,71 +175,95 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
         s += P.alpha * (v / sqrt(v * v + P.eps));                             // dsm.py:350
         g[6 + j] = sc * s;
     }
-    if (HESS) {
-        // (3) xi-theta block
-        for (int it = tid; it < m * 6; it += BLOCK) {
-            const int j = it / 6, q = it - j * 6;
-            const uint32_t gp = P.grid[j];
-            const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
-            double s = 0;
-            for (int da = -NC; da <= NC; ++da) {
-                const int a = ja - da;
-                if (a < 0 || a >= ch) continue;
-                for (int db = -NC; db <= NC; ++db) {
-                    const int b = jb - db;
-                    if (b < 0 || b >= cw) continue;
-                    const int cell = a * cw + b;
-                    if (P.cstart[cell + 1] == P.cstart[cell]) continue;
-                    const int li = local_index(P.amask[cell], da, db);
-                    if (li >= 0) s += P.scrH[(size_t)cell * SCRH + tri(li, q)];
-                }
-            }
-            s *= hz * sc;
-            P.H[(size_t)(6 + j) * N + q] = s;
-            P.H[(size_t)q * N + 6 + j] = s;
-        }
-        // (4) xi-xi block: pairs of grid points whose cells are at most 2 NC apart share pixels; all other entries stay 0
-        // (the matrix is cleared once when the DSM stage begins: the pattern does not change)
-        constexpr int SP = 4 * NC + 1;
-        for (int it = tid; it < m * SP * SP; it += BLOCK) {
-            const int j = it / (SP * SP), e = it - j * (SP * SP);
-            const int ea = e / SP - 2 * NC, eb = e % SP - 2 * NC;
-            const uint32_t gp = P.grid[j];
-            const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
-            const int ka = ja + ea, kb = jb + eb;
-            if (ka < 0 || ka >= ch || kb < 0 || kb >= cw) continue;
-            const int k = P.cellmap[ka * cw + kb];
-            if (k < 0 || k > j) continue;
-            double s = 0;
-            for (int da = -NC; da <= NC; ++da) {
-                const int a = ja - da;                       // cell c = j's cell - (da, db)
-                if (a < 0 || a >= ch || abs(ka - a) > NC) continue;
-                for (int db = -NC; db <= NC; ++db) {
-                    const int b = jb - db;
-                    if (b < 0 || b >= cw || abs(kb - b) > NC) continue;
-                    const int cell = a * cw + b;
-                    if (P.cstart[cell + 1] == P.cstart[cell]) continue;
-                    const uint32_t am = P.amask[cell];
-                    const int lj = local_index(am, da, db);
-                    const int lk = local_index(am, ka - a, kb - b);
-                    if (lj >= 0 && lk >= 0) s += P.scrH[(size_t)cell * SCRH + (lj >= lk ? tri(lj, lk) : tri(lk, lj))];
-                }
-            }
-            if (k == j) {
-                const double v = x[6 + j];
-                const double t3 = v * v, t2 = sqrt(t3 + P.eps);
-                double gd = P.alpha * (1.0 / t2 - t3 / (t2 * t2 * t2));      // dsm.py:372-374
-                if (gd < 0) gd = 0;
-                s += gd;
-            }
-            s *= hz * sc;
-            P.H[(size_t)(6 + j) * N + 6 + k] = s;
-            P.H[(size_t)(6 + k) * N + 6 + j] = s;
-        }
-    }
+    // the xi-theta and xi-xi blocks of the Hessian are assembled by k_hgather (one warp per grid point), before k_ctrl runs
     __syncthreads();
     *psi_out = psi;
     return sc * psi;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// k_hgather: rows 6.. of the Hessian (the xi-theta and xi-xi blocks, dsm.py:369-374) of every candidate that asked for one.
+// One warp per (candidate, grid point j): it visits the <= 25 cells that see j in a fixed order and adds their local
+// Hessian rows into 81 + 6 accumulators (the grid points of the 9 x 9 cells around j's cell, and theta), then writes row
+// 6 + j of H = hz * scale_cp * Hess psi (both triangles; entries outside the 9 x 9 neighbourhood stay zero).
+
+constexpr int HG_BLOCK = 256;
+constexpr int HG_ACC = 96;
+
+__global__ void __launch_bounds__(HG_BLOCK)
+k_hgather(Par par, const sdsm_cand* __restrict__ cands, WS ws, int parity, int unit_scale)
+{
+    __shared__ double s_acc[(HG_BLOCK / 32) * HG_ACC];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double* acc = s_acc + warp * HG_ACC;
+    const int n_h = (int)(ws.counters[2 + parity] & 0xffffffffull);
+    const uint2* hitems = ws.hitems + (size_t)parity * ws.items_cap;
+    constexpr int SP = 4 * NC + 1;   // 9
+    for (int w = blockIdx.x * (HG_BLOCK / 32) + warp; w < n_h; w += gridDim.x * (HG_BLOCK / 32)) {
+        const uint2 it = hitems[w];
+        const int c = (int)it.x, j = (int)it.y;
+        const sdsm_cand* cd = cands + c;
+        const int64_t cell_off = cd->cell_off;
+        const CInfo ci = ws.cinfo[c];
+        const int cw = ci.cw, ch = ci.ch, N = 6 + ci.m;
+        const double fac = unit_scale ? 1.0 : ws.cstate[c].z * (par.scale / (double)cd->n);
+        const int32_t* cstart = ws.cell_start + cell_off;
+        const uint32_t* amask = ws.cell_amask + cell_off;
+        const int32_t* cellmap = ws.cellmap + cell_off;
+        const double* scrH = ws.scrH + (size_t)cell_off * SCRH;
+        double* H = ws.mats + cd->mat_off;
+        const uint32_t gp = ws.grid_rc[cell_off + j];
+        const int ja = (int)(gp & 0xffffu) / par.sub, jb = (int)(gp >> 16) / par.sub;
+        __syncwarp();
+        for (int t = lane; t < HG_ACC; t += 32) acc[t] = 0.0;
+        __syncwarp();
+        for (int da = -NC; da <= NC; ++da) {
+            const int a = ja - da;                       // cell = j's cell - (da, db): it sees j in slot (da, db)
+            if (a < 0 || a >= ch) continue;
+            for (int db = -NC; db <= NC; ++db) {
+                const int b = jb - db;
+                if (b < 0 || b >= cw) continue;
+                const int cell = a * cw + b;
+                if (cstart[cell + 1] == cstart[cell]) continue;
+                const uint32_t am = amask[cell];
+                const int lj = local_index(am, da, db);
+                if (lj < 0) continue;
+                const int L = 6 + __popc(am);
+                if (lane < L) {
+                    const double v = scrH[(size_t)cell * SCRH + (lane >= lj ? tri(lane, lj) : tri(lj, lane))];
+                    int t;
+                    if (lane < 6) t = SP * SP + lane;
+                    else {
+                        const int s = __fns(am, 0, lane - 6 + 1);           // slot of local entry `lane`
+                        t = (s / 5 - NC - da + 2 * NC) * SP + (s % 5 - NC - db + 2 * NC);
+                    }
+                    acc[t] += v;
+                }
+                __syncwarp();
+            }
+        }
+        const double* x = ws.req[c].x;
+        for (int t = lane; t < SP * SP; t += 32) {
+            const int ka = ja + t / SP - 2 * NC, kb = jb + t % SP - 2 * NC;
+            if (ka < 0 || ka >= ch || kb < 0 || kb >= cw) continue;
+            const int k = cellmap[ka * cw + kb];
+            if (k < 0) continue;
+            double s = acc[t];
+            if (k == j) {
+                const double v = x[6 + j];
+                const double t3 = v * v, t2 = sqrt(t3 + par.epsilon);
+                double gd = par.alpha * (1.0 / t2 - t3 / (t2 * t2 * t2));      // dsm.py:372-374
+                if (gd < 0) gd = 0;
+                s += gd;
+            }
+            H[(size_t)(6 + j) * N + 6 + k] = s * fac;
+        }
+        if (lane < 6) {
+            const double s = acc[SP * SP + lane] * fac;
+            H[(size_t)(6 + j) * N + lane] = s;
+            H[(size_t)lane * N + 6 + j] = s;
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -313,6 +339,173 @@ __device__ void chol_solve(const double* L, int N, double* v, double* bv, int bv
         if (tid < 32) chol_solve_warp(L, N, v);
     }
     __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Large systems (N > SMALL_N_MAX): blocked right-looking Cholesky of the lower triangle of H into A (N x N row-major,
+// global memory / L2), 32-wide panels staged in shared memory; same conventions (reciprocal diagonal, failure on a
+// non-positive pivot).  One CTA of BLOCK threads.
+
+constexpr int CB = 32;               // panel width
+constexpr int CB_LD = CB + 1;
+
+constexpr size_t BIG_SMEM = sizeof(double) * (2 * CB * CB_LD + CB + (BIG_BLOCK / 32) * 32 + 32) + sizeof(int) * 8;
+
+__device__ __forceinline__ void carve_smem_big(Sm& sm, char* base)
+{
+    sm.D = (double*)base;
+    sm.Xj = sm.D + CB * CB_LD;
+    sm.yv = sm.Xj + CB * CB_LD;
+    sm.red_part = sm.yv + CB;
+    sm.red_out = sm.red_part + (BIG_BLOCK / 32) * 32;
+    sm.flag = (int*)(sm.red_out + 32);
+    sm.Lf = nullptr;
+    sm.lcap = 0;
+}
+
+template <int BLOCK>
+__device__ bool cholesky_big(const double* __restrict__ H, int N, double* __restrict__ A, Sm& sb)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = BLOCK / 32;
+    __syncthreads();
+    for (int i = warp; i < N; i += NW)
+        for (int j = lane; j <= i; j += 32) A[(size_t)i * N + j] = H[(size_t)i * N + j];
+    if (tid == 0) sb.flag[0] = 0;
+    __syncthreads();
+    for (int k0 = 0; k0 < N; k0 += CB) {
+        const int kw = min(CB, N - k0);
+        // (a) diagonal block -> shared memory, factorised by warp 0 (lane = row)
+        for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        __syncthreads();
+        if (warp == 0) {
+            for (int cc = 0; cc < kw; ++cc) {
+                const double dk = sb.D[cc * CB_LD + cc];
+                if (!(dk > 0.0) || !isfinite(dk)) { if (lane == 0) sb.flag[0] = 1; break; }
+                const double rinv = 1.0 / sqrt(dk);
+                __syncwarp();
+                if (lane == cc) sb.D[cc * CB_LD + cc] = rinv;
+                if (lane > cc && lane < kw) {
+                    const double l = sb.D[lane * CB_LD + cc] * rinv;
+                    sb.D[lane * CB_LD + cc] = l;
+                }
+                __syncwarp();
+                if (lane > cc && lane < kw) {
+                    const double l = sb.D[lane * CB_LD + cc];
+                    for (int j = cc + 1; j <= lane; ++j) sb.D[lane * CB_LD + j] -= l * sb.D[j * CB_LD + cc];
+                }
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+        if (sb.flag[0]) return false;
+        for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) A[(size_t)(k0 + r) * N + k0 + q] = sb.D[r * CB_LD + q]; }
+        const int r0 = k0 + kw;
+        if (r0 >= N) break;
+        // (b) panel: rows below the block, X = A[i, k0:k0+kw] D^-T, one thread per row
+        for (int i = r0 + tid; i < N; i += BLOCK) {
+            double* ar = A + (size_t)i * N + k0;
+            double r[CB];
+#pragma unroll
+            for (int q = 0; q < CB; ++q) r[q] = q < kw ? ar[q] : 0.0;
+#pragma unroll
+            for (int q = 0; q < CB; ++q) {
+                if (q < kw) {
+                    double v = r[q];
+#pragma unroll
+                    for (int p = 0; p < q; ++p) v -= r[p] * sb.D[q * CB_LD + p];
+                    r[q] = v * sb.D[q * CB_LD + q];
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < CB; ++q) if (q < kw) ar[q] = r[q];
+        }
+        __syncthreads();
+        // (c) trailing update A[ib, jb] -= X[ib] X[jb]^T for the 32 x 32 blocks jb <= ib below the panel;
+        //     all warps share X[jb] (shared memory), each takes block rows ib = jb, jb + NW, ...; lane = row
+        const int nbt = (N - r0 + CB - 1) / CB;
+        for (int jb = 0; jb < nbt; ++jb) {
+            const int j0 = r0 + jb * CB, jw = min(CB, N - j0);
+            __syncthreads();
+            for (int e = tid; e < CB * CB; e += BLOCK) {
+                const int r = e / CB, q = e - r * CB;
+                sb.Xj[r * CB_LD + q] = (r < jw && q < kw) ? A[(size_t)(j0 + r) * N + k0 + q] : 0.0;
+            }
+            __syncthreads();
+            for (int ib = jb + warp; ib < nbt; ib += NW) {
+                const int i = r0 + ib * CB + lane;
+                if (i >= N) continue;
+                const double* xr = A + (size_t)i * N + k0;
+                double xv[CB];
+#pragma unroll
+                for (int q = 0; q < CB; ++q) xv[q] = q < kw ? xr[q] : 0.0;
+                double* out = A + (size_t)i * N + j0;
+                const int cmax = min(jw, i - j0 + 1);      // stay inside the lower triangle
+                for (int cc = 0; cc < cmax; ++cc) {
+                    double a = 0;
+#pragma unroll
+                    for (int q = 0; q < CB; ++q) a += xv[q] * sb.Xj[cc * CB_LD + q];
+                    out[cc] -= a;
+                }
+            }
+        }
+        __syncthreads();
+    }
+    return true;
+}
+
+// v := (A A^T)^-1 v with the factor of cholesky_big; blocked forward / backward substitution, v in global memory.
+// Per 32-block: the diagonal block is staged in shared memory and solved by warp 0, then every thread updates one row.
+template <int BLOCK>
+__device__ void chol_solve_big(const double* __restrict__ A, int N, double* v, Sm& sb)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __syncthreads();
+    // forward: L y = v
+    for (int k0 = 0; k0 < N; k0 += CB) {
+        const int kw = min(CB, N - k0);
+        for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        __syncthreads();
+        if (warp == 0) {
+            double b = lane < kw ? v[k0 + lane] : 0.0;
+            for (int cc = 0; cc < kw; ++cc) {
+                const double yk = __shfl_sync(0xffffffffu, b, cc) * sb.D[cc * CB_LD + cc];
+                if (lane == cc) b = yk;
+                else if (lane > cc && lane < kw) b -= sb.D[lane * CB_LD + cc] * yk;
+            }
+            if (lane < kw) { v[k0 + lane] = b; sb.yv[lane] = b; }
+        }
+        __syncthreads();
+        for (int i = k0 + kw + tid; i < N; i += BLOCK) {
+            const double* ar = A + (size_t)i * N + k0;
+            double a = 0;
+            for (int q = 0; q < kw; ++q) a += ar[q] * sb.yv[q];
+            v[i] -= a;
+        }
+        __syncthreads();
+    }
+    // backward: L^T x = y
+    for (int k0 = ((N - 1) / CB) * CB; k0 >= 0; k0 -= CB) {
+        const int kw = min(CB, N - k0);
+        for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        __syncthreads();
+        if (warp == 0) {
+            double b = lane < kw ? v[k0 + lane] : 0.0;
+            for (int cc = kw - 1; cc >= 0; --cc) {
+                const double xk = __shfl_sync(0xffffffffu, b, cc) * sb.D[cc * CB_LD + cc];
+                if (lane == cc) b = xk;
+                else if (lane < cc) b -= sb.D[cc * CB_LD + lane] * xk;
+            }
+            if (lane < kw) { v[k0 + lane] = b; sb.yv[lane] = b; }
+        }
+        __syncthreads();
+        for (int i = tid; i < k0; i += BLOCK) {
+            double a = 0;
+            for (int q = 0; q < kw; ++q) a += A[(size_t)(k0 + q) * N + i] * sb.yv[q];
+            v[i] -= a;
+        }
+        __syncthreads();
+    }
 }
 
 template <int BLOCK>
@@ -406,23 +599,30 @@ __device__ bool file_request(const Prob& P, Sm& sm, CState& S, const WS& ws, int
     S.req_vec = vec; S.req_gvec = gvec; S.req_h = want_h;
     if (want_h) S.nh += 1; else S.nf += 1;                      // evaluation counters (reported in out.info)
     const int other = parity ^ 1;
+    const bool big = N > SMALL_N_MAX;                           // who advances this candidate next: k_ctrl or k_ctrl_big
+    const int n_h = (want_h && S.use_xi) ? P.m : 0;             // rows of the Hessian k_hgather assembles
     if (tid == 0) {
         EvalReq rq; rq.x = x; rq.want_h = want_h; rq.use_xi = S.use_xi;
         ws.req[c] = rq;
-        const unsigned long long old = atomicAdd(&ws.counters[other], (1ull << 32) | (unsigned long long)P.n_ne);
-        ws.live[(size_t)other * ws.n_cand + (int)(old >> 32)] = c;
-        sm.flag[2] = (int)(old & 0xffffffffull);
+        const unsigned long long old0 = atomicAdd(&ws.counters[other], ((big ? 0ull : 1ull) << 32) | (unsigned long long)P.n_ne);
+        const unsigned long long old2 = atomicAdd(&ws.counters[2 + other], ((big ? 1ull : 0ull) << 32) | (unsigned long long)n_h);
+        if (big) ws.live[(size_t)other * ws.n_cand + (ws.n_cand - 1 - (int)(old2 >> 32))] = c;
+        else ws.live[(size_t)other * ws.n_cand + (int)(old0 >> 32)] = c;
+        sm.flag[2] = (int)(old0 & 0xffffffffull);
+        sm.flag[3] = (int)(old2 & 0xffffffffull);
     }
     __syncthreads();
-    const int start = sm.flag[2];
+    const int start = sm.flag[2], hstart = sm.flag[3];
     uint2* items = ws.items + (size_t)other * ws.items_cap + start;
     for (int i = tid; i < P.n_ne; i += BLOCK) items[i] = make_uint2((unsigned)c, (unsigned)P.clist[i]);
+    uint2* hitems = ws.hitems + (size_t)other * ws.items_cap + hstart;
+    for (int i = tid; i < n_h; i += BLOCK) hitems[i] = make_uint2((unsigned)c, (unsigned)i);
     __syncthreads();
     return true;
 }
 
 // Advances candidate c by one round: consumes the evaluation it asked for, runs up to the next evaluation request.
-template <int BLOCK>
+template <int BLOCK, bool BIG>
 __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c, int parity,
                           Sm& sm, const sdsm_out& out, double* trace)
 {
@@ -459,7 +659,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
     while (!yield) {
         const int Nc = S.use_xi ? P.N : 6;
         const int tri_n = Nc * (Nc + 1) / 2;
-        const bool l_sm = tri_n <= sm.lcap && Nc <= CTRL_BPAD;
+        const bool l_sm = !BIG && tri_n <= sm.lcap && Nc <= CTRL_BPAD;
         double* Lf = l_sm ? sm.Lf : P.Lg;
         double* bv = l_sm ? sm.Lf + tri_n : sm.Lf;
         const int bvcap = l_sm ? CTRL_BPAD : sm.lcap + CTRL_BPAD;
@@ -517,7 +717,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
             }
             if (S.iters == 0) { S.d = sqrt(S.s / S.z); S.lm = sqrt(S.s * S.z); }
             S.lmsq = S.lm * S.lm;
-            const bool ok = cholesky<BLOCK>(P.H, Nc, Lf, sm);
+            const bool ok = BIG ? cholesky_big<BLOCK>(P.H, Nc, P.Lg, sm) : cholesky<BLOCK>(P.H, Nc, Lf, sm);
             hres_alt = false;
             if (ok) { S.pc = PC_KKT; break; }
             if (S.iters == 0) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }                 // ValueError("Rank(A) < p or ...")
@@ -539,7 +739,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
             break;
         }
         case PC_RESTORED: {
-            const bool ok = cholesky<BLOCK>(P.H, Nc, Lf, sm);
+            const bool ok = BIG ? cholesky_big<BLOCK>(P.H, Nc, P.Lg, sm) : cholesky<BLOCK>(P.H, Nc, Lf, sm);
             if (!ok) { S.r_ipm = 1; S.pc = PC_IPMDONE; break; }
             hres_alt = true;
             S.pc = PC_KKT;
@@ -555,7 +755,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
             const double bt = S.bt;
             __syncthreads();
             for (int i = tid; i < Nc; i += BLOCK) { const double bx = -(z * g[i]); tv[i] = bx + g[i] * bt; }
-            chol_solve<BLOCK>(Lf, Nc, tv, bv, bvcap);
+            if (BIG) chol_solve_big<BLOCK>(P.Lg, Nc, tv, sm); else chol_solve<BLOCK>(Lf, Nc, tv, bv, bvcap);
             S.uz0 = -d * bt;
             const double wz3 = S.uz0 / d;
             S.vt = bt + wz3;
@@ -573,7 +773,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
             }
             S.gux = bdot<BLOCK>(g, tv, Nc, sm);
             S.gux_res = hres_alt ? bdot<BLOCK>(gres, tv, Nc, sm) : S.gux;
-            chol_solve<BLOCK>(Lf, Nc, ev, bv, bvcap);
+            if (BIG) chol_solve_big<BLOCK>(P.Lg, Nc, ev, sm); else chol_solve<BLOCK>(Lf, Nc, ev, bv, bvcap);
             S.gex = bdot<BLOCK>(g, ev, Nc, sm);
             for (int i = tid; i < Nc; i += BLOCK) dx[i] = tv[i] + ev[i];
             __syncthreads();
@@ -806,7 +1006,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
 // kernels
 
 // Round 0 (order != nullptr): CTA b starts candidate order[b].  Later rounds: CTA b advances the b-th live candidate of
-// work list `parity`.  Requests go to work list parity ^ 1.
+// work list `parity` whose current system is small (N <= SMALL_N_MAX).  Requests go to work list parity ^ 1.
 __global__ void __launch_bounds__(CTRL_BLOCK, 4)
 k_ctrl(Img img, Par par, const sdsm_cand* __restrict__ cands, const int32_t* __restrict__ order, int n_first, WS ws, sdsm_out out,
        int parity, int lcap, double* trace)
@@ -825,13 +1025,29 @@ k_ctrl(Img img, Par par, const sdsm_cand* __restrict__ cands, const int32_t* __r
     }
     const sdsm_cand cd = cands[c];
     const CInfo ci = ws.cinfo[c];
-    ctrl_step<CTRL_BLOCK>(par, img, cd, ci, ws, c, parity, sm, out, trace);
+    ctrl_step<CTRL_BLOCK, false>(par, img, cd, ci, ws, c, parity, sm, out, trace);
+}
+
+// the live candidates whose current system is large (filed from the back of the live list)
+__global__ void __launch_bounds__(BIG_BLOCK, 1)
+k_ctrl_big(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out out, int parity, double* trace)
+{
+    extern __shared__ __align__(16) char smem_ctrl[];
+    Sm sm;
+    carve_smem_big(sm, smem_ctrl);
+    const int n_live = (int)(ws.counters[2 + parity] >> 32);
+    if ((int)blockIdx.x >= n_live) return;
+    const int c = ws.live[(size_t)parity * ws.n_cand + (ws.n_cand - 1 - blockIdx.x)];
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    ctrl_step<BIG_BLOCK, true>(par, img, cd, ci, ws, c, parity, sm, out, trace);
 }
 
 // Publishes the size of work list `parity` for the host (pinned memory), after k_ctrl has filled it.
 __global__ void k_publish(WS ws, int parity, unsigned long long* host_flag)
 {
-    *host_flag = ws.counters[parity];
+    host_flag[0] = ws.counters[parity];
+    host_flag[1] = ws.counters[2 + parity];
 }
 
 // Result rasterisation (objects.py:198-211): foreground inside omega, its bounding box, on_boundary.  One CTA per candidate.

@@ -245,7 +245,7 @@ k_eval(Par par, const sdsm_cand* __restrict__ cands, WS ws, int parity)
     int* slotj = s_slotj + warp * 32;
     const unsigned long long cnt = ws.counters[parity];
     const int n_items = (int)(cnt & 0xffffffffull);
-    if (blockIdx.x == 0 && threadIdx.x == 0) ws.counters[parity ^ 1] = 0ull;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { ws.counters[parity ^ 1] = 0ull; ws.counters[2 + (parity ^ 1)] = 0ull; }
     const uint2* items = ws.items + (size_t)parity * ws.items_cap;
 
     for (int w = blockIdx.x * EVAL_WARPS + warp; w < n_items; w += gridDim.x * EVAL_WARPS) {

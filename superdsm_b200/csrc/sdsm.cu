@@ -24,7 +24,7 @@ struct sdsm_ctx {
     int64_t launches = 0;
     // totals of the last plan (the layout is a pure function of these)
     int64_t P = 0, C = 0, T = 0, V = 0, M = 0;
-    int32_t n_cand = 0;
+    int32_t n_cand = 0, n_big = 0;
     unsigned long long* h_flag = nullptr;   // pinned: size of the next work list, published by the device every few rounds
     int64_t rounds = 0;                      // rounds of the last solve (diagnostics)
     std::string err;
@@ -56,6 +56,7 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     const int ctrl_max = (int)ctrl_smem_bytes(SMEM_L_CAP);
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EVAL_SMEM));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_ctrl, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_ctrl_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BIG_SMEM));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_begin, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_end, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_trace_begin, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
@@ -75,6 +76,7 @@ extern "C" void sdsm_destroy(sdsm_ctx* ctx)
 extern "C" const char* sdsm_last_error(const sdsm_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
 extern "C" int64_t sdsm_launch_count(const sdsm_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int64_t sdsm_round_count(const sdsm_ctx* ctx) { return ctx ? ctx->rounds : 0; }
 
 extern "C" int sdsm_set_image(sdsm_ctx* ctx, const double* d_y, const int32_t* d_atoms, int32_t H, int32_t W)
 {
@@ -132,7 +134,7 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
     if (!ctx->have_par || !ctx->img.y) { ctx->err = "sdsm_set_image / sdsm_set_params must precede sdsm_plan_batch"; return SDSM_E_ARG; }
     const int sub = ctx->par.sub;
     int64_t P = 0, C = 0, T = 0, V = 0, M = 0, PAR = 0, FG = 0;
-    int32_t n_max = 6, cells_max = 1;
+    int32_t n_max = 6, cells_max = 1, n_big = 0;
     for (int32_t i = 0; i < n_cand; ++i) {
         sdsm_cand& c = cands[i];
         if (c.h < 1 || c.w < 1 || c.n < 1 || c.r0 < 0 || c.c0 < 0 || c.r0 + c.h > ctx->img.H || c.c0 + c.w > ctx->img.W || c.fp_len < 1) {
@@ -148,7 +150,8 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
         c.par_off = PAR; PAR += ld;
         c.fg_off = FG;  FG += (int64_t)c.h * c.w;
         c.vec_off = V;  V += (int64_t)NVEC * ld;
-        c.mat_off = M;  M += 2 * ld * ld + (ld * (ld + 1) / 2 + 1) / 2 * 2;
+        c.mat_off = M;  M += 3 * ld * ld;
+        if (ld > SMALL_N_MAX) ++n_big;
         if (ld > n_max) n_max = (int32_t)ld;
         if (cap > cells_max) cells_max = cap;
     }
@@ -158,8 +161,9 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
     plan->fgmask_len = FG;
     plan->n_max = n_max;
     plan->cells_max = cells_max;
-    plan->reserved0 = 0;
+    plan->reserved0 = n_big;
     plan->reserved1 = 0;
+    ctx->n_big = n_big;
     ctx->P = P; ctx->C = C; ctx->T = T; ctx->V = V; ctx->M = M; ctx->n_cand = n_cand;
     return SDSM_OK;
 }
@@ -172,34 +176,53 @@ static int check_plan(sdsm_ctx* ctx, int32_t n_cand, size_t workspace_bytes, Lay
     return SDSM_OK;
 }
 
-// Drives the lock-step rounds k_eval -> k_ctrl until no candidate is live.  `parity` names the work list that is ready.
-// The size of the next work list is published to pinned memory every few rounds; the host only waits on that.
+// Drives the lock-step rounds k_eval -> k_hgather -> k_ctrl / k_ctrl_big until no candidate is live.  `parity` names the
+// work list that is ready.  The sizes of the next work lists are published to pinned memory every few rounds; the host
+// only waits on that.
+struct Bounds { int64_t live_small, live_big, items, hitems; };
+
 static int run_rounds(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_cands, const WS& ws, const sdsm_out& out, int lcap,
-                      int64_t live_bound, int64_t item_bound, int parity, double* trace)
+                      Bounds bd, int parity, double* trace, int unit_scale)
 {
     const size_t csmem = ctrl_smem_bytes(lcap);
     const int max_rounds = 64 * (ctx->par.maxiters + 2) * 3;
+    const int64_t g_max = (int64_t)ctx->sm_count * 16;
     int round = 0;
     int burst = 4;
     while (true) {
         for (int b = 0; b < burst; ++b, ++round) {
-            int64_t ge = (item_bound + EVAL_WARPS - 1) / EVAL_WARPS;
-            const int64_t ge_max = (int64_t)ctx->sm_count * 16;
-            if (ge > ge_max) ge = ge_max;
+            int64_t ge = (bd.items + EVAL_WARPS - 1) / EVAL_WARPS;
+            if (ge > g_max) ge = g_max;
             if (ge < 1) ge = 1;
             k_eval<<<(unsigned)ge, EVAL_BLOCK, EVAL_SMEM, stream>>>(ctx->par, d_cands, ws, parity);
-            k_ctrl<<<(unsigned)live_bound, CTRL_BLOCK, csmem, stream>>>(ctx->img, ctx->par, d_cands, nullptr, 0, ws, out, parity, lcap, trace);
-            ctx->launches += 2;
+            ctx->launches++;
+            if (bd.hitems > 0) {
+                int64_t gh = (bd.hitems + HG_BLOCK / 32 - 1) / (HG_BLOCK / 32);
+                if (gh > g_max) gh = g_max;
+                k_hgather<<<(unsigned)gh, HG_BLOCK, 0, stream>>>(ctx->par, d_cands, ws, parity, unit_scale);
+                ctx->launches++;
+            }
+            if (bd.live_big > 0) {
+                k_ctrl_big<<<(unsigned)bd.live_big, BIG_BLOCK, BIG_SMEM, stream>>>(ctx->img, ctx->par, d_cands, ws, out, parity, trace);
+                ctx->launches++;
+            }
+            if (bd.live_small > 0) {
+                k_ctrl<<<(unsigned)bd.live_small, CTRL_BLOCK, csmem, stream>>>(ctx->img, ctx->par, d_cands, nullptr, 0, ws, out, parity, lcap, trace);
+                ctx->launches++;
+            }
             parity ^= 1;
         }
         k_publish<<<1, 1, 0, stream>>>(ws, parity, ctx->h_flag);
         ctx->launches++;
         CUDA_TRY(ctx, cudaStreamSynchronize(stream));
-        const unsigned long long f = *(volatile unsigned long long*)ctx->h_flag;
-        const int64_t n_live = (int64_t)(f >> 32), n_items = (int64_t)(f & 0xffffffffull);
-        if (n_live == 0) break;
-        if (n_live > live_bound || n_items > item_bound) { ctx->err = "work list grew: internal error"; return SDSM_E_CUDA; }
-        live_bound = n_live; item_bound = n_items;
+        const unsigned long long f0 = ((volatile unsigned long long*)ctx->h_flag)[0], f2 = ((volatile unsigned long long*)ctx->h_flag)[1];
+        Bounds nb{(int64_t)(f0 >> 32), (int64_t)(f2 >> 32), (int64_t)(f0 & 0xffffffffull), (int64_t)(f2 & 0xffffffffull)};
+        if (nb.live_small + nb.live_big == 0) break;
+        // the live set only shrinks; a candidate can change class (small -> big) once, when its DSM stage begins
+        if (nb.live_small > bd.live_small || nb.items > bd.items) { ctx->err = "work list grew: internal error"; return SDSM_E_CUDA; }
+        bd.live_big = nb.live_small + nb.live_big < bd.live_big ? nb.live_small + nb.live_big : bd.live_big;
+        bd.live_small = nb.live_small;
+        bd.items = nb.items;
         if (round > max_rounds) { ctx->err = "solver did not terminate within the round limit"; return SDSM_E_CUDA; }
         if (burst < 8) burst *= 2;
     }
@@ -238,7 +261,10 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     k_ctrl<<<n_cand, CTRL_BLOCK, ctrl_smem_bytes(lcap), stream>>>(ctx->img, ctx->par, d_cands, d_order, n_cand, ws, *out, 1, lcap, nullptr);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
-    rc = run_rounds(ctx, stream, d_cands, ws, *out, lcap, n_cand, ctx->C, 0, nullptr);
+    {
+        const Bounds bd{n_cand, ctx->n_big, ctx->C, ctx->par.has_smooth ? ctx->C : 0};
+        rc = run_rounds(ctx, stream, d_cands, ws, *out, lcap, bd, 0, nullptr, 0);
+    }
     if (rc) return rc;
     const int fin_grid = n_cand < 16 * ctx->sm_count ? n_cand : 16 * ctx->sm_count;
     k_finish<<<fin_grid, FIN_BLOCK, 0, stream>>>(ctx->img, ctx->par, d_cands, n_cand, ws, *out);
@@ -260,6 +286,7 @@ extern "C" int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const s
     CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
     k_diag_eval_begin<<<1, CTRL_BLOCK, csmem, stream>>>(ctx->par, d_cands, c, ws, d_x, 1, lcap);
     k_eval<<<ctx->sm_count, EVAL_BLOCK, EVAL_SMEM, stream>>>(ctx->par, d_cands, ws, 0);
+    if (ctx->par.has_smooth) { k_hgather<<<ctx->sm_count, HG_BLOCK, 0, stream>>>(ctx->par, d_cands, ws, 0, 1); ctx->launches++; }
     k_diag_eval_end<<<1, CTRL_BLOCK, csmem, stream>>>(ctx->par, d_cands, c, ws, d_value, d_grad, d_H, lcap);
     ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -292,7 +319,8 @@ extern "C" int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     k_diag_trace_begin<<<1, CTRL_BLOCK, ctrl_smem_bytes(lcap), stream>>>(ctx->par, d_cands, c, use_xi, ws, d_x0, 1, lcap);
     ctx->launches++;
     sdsm_out none{};   // STG_TRACE never writes results
-    int rc = run_rounds(ctx, stream, d_cands, ws, none, lcap, 1, ctx->C, 0, d_trace);
+    const Bounds bd{1, 1, ctx->C, ctx->par.has_smooth ? ctx->C : 0};
+    int rc = run_rounds(ctx, stream, d_cands, ws, none, lcap, bd, 0, d_trace, 0);
     if (rc) return rc;
     k_diag_trace_end<<<1, 128, 0, stream>>>(ctx->par, d_cands, c, ws, d_xout, d_status_iters);
     ctx->launches++;

@@ -158,6 +158,10 @@ class Engine(object):
     def launch_count(self):
         return int(self.lib.sdsm_launch_count(self.ctx))
 
+    @property
+    def round_count(self):
+        return int(self.lib.sdsm_round_count(self.ctx))
+
     # -- buffers -------------------------------------------------------------------------------------------------
 
     def _buf(self, name, nbytes, pinned=False):
