@@ -18,6 +18,9 @@
  * memory: the caller provides the workspace sdsm_plan_batch() asked for.  All work is enqueued on the caller's
  * stream; nothing synchronises.  Errors are integer codes (0 = ok), solver trouble is per-candidate data
  * (status word), never a C++ exception.  One context per device; a context is not thread-safe.
+ *
+ * Environment (read by sdsm_create): SDSM_SOLO_CELLS (default 16) -- candidates with at most this many pixel cells run
+ * their whole chain of solver steps inside one CTA; SDSM_TIMEOUT_S (default 60) -- watchdog of the persistent solver kernel.
  */
 #ifndef SUPERDSM_B200_H
 #define SUPERDSM_B200_H
@@ -29,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SDSM_ABI_VERSION 2
+#define SDSM_ABI_VERSION 3
 
 /* return codes */
 #define SDSM_OK              0
@@ -143,8 +146,11 @@ int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flo
 /* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
 int64_t sdsm_launch_count(const sdsm_ctx* ctx);
 
-/* number of lock-step rounds (one k_eval + one k_ctrl launch each) the last sdsm_solve_batch() took */
-int64_t sdsm_round_count(const sdsm_ctx* ctx);
+/* Diagnostics / watchdog: copies the 16 counters of the persistent solver of the last sdsm_solve_batch() on this workspace to
+ * h_stats and SYNCHRONISES the stream.  [2] candidates finished, [3] != 0: the watchdog aborted the solve (results invalid),
+ * [4..7] busy clock cycles summed over CTAs in evaluation / Hessian-row / control tasks and idle, [8..10] number of
+ * evaluation / Hessian-row / control tasks, [11] CTA lifetime cycles summed over CTAs. */
+int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_t* h_stats, void* stream);
 
 #ifdef __cplusplus
 }

@@ -13,14 +13,15 @@ constexpr int LOCAL_MAX  = 32;    // 6 polynomial + 25 slots, padded
 constexpr int SCRH       = 496;   // packed lower triangle of a 31 x 31 local Hessian
 constexpr int SCRG       = 32;    // local gradient (31) + value
 constexpr int TILE_LD    = 34;    // row stride (doubles) of the per-warp pixel tile: conflict-free 128-bit rows
-constexpr int EVAL_BLOCK = 256;   // k_eval: one warp per pixel cell
+constexpr int SOLVE_BLOCK = 256;  // k_solve: persistent CTAs, every task is executed by one CTA
+constexpr int EVAL_BLOCK = SOLVE_BLOCK;   // evaluation task: one warp per pixel cell
 constexpr int EVAL_WARPS = EVAL_BLOCK / 32;
 constexpr int TILE_DOUBLES = 32 * TILE_LD + 64;                 // tile + u[32] + dd[32]
-constexpr int CTRL_BLOCK = 128;   // k_ctrl: one CTA per live candidate
+constexpr int CTRL_BLOCK = SOLVE_BLOCK;   // control task: one CTA advances one candidate's state machine
 constexpr int CTRL_WARPS = CTRL_BLOCK / 32;
 constexpr int SMEM_L_CAP = 5504;  // doubles of shared memory for the packed Cholesky factor (N <= 104)
-constexpr int SMALL_N_MAX = 104;  // systems up to this size are factorised in shared memory by k_ctrl, larger ones by k_ctrl_big
-constexpr int BIG_BLOCK  = 256;   // k_ctrl_big
+constexpr int SMALL_N_MAX = 104;  // systems up to this size are factorised in shared memory, larger ones blocked in global memory / L2
+constexpr int BIG_BLOCK  = SOLVE_BLOCK;
 constexpr int NVEC       = 12;    // N-vectors of the interior-point solver
 
 struct Img { const double* y; const int32_t* atoms; int32_t H, W; };
@@ -39,7 +40,7 @@ struct CInfo {
     int32_t n_ne, pad;     // number of non-empty cells (entries of cell_list)
 };
 
-// State of one candidate's fit between two rounds of the lock-step solver (k_eval <-> k_ctrl).  The interior-point
+// State of one candidate's fit between two control tasks (while its evaluation tasks run).  The interior-point
 // fields are the local variables of cvxopt's cpl (oracle/cpsolver.py) that live across an evaluation of F.
 struct CState {
     double t, s, z, d, lm;
@@ -55,9 +56,10 @@ struct CState {
     int32_t status, bits, it1, it2, it3, nf, nh, have1, r_ipm;
 };
 
-// what k_eval needs to know about a live candidate (written by k_ctrl when it files the request)
+// what the evaluation tasks need to know about a candidate (written by the control task that files the request)
 struct EvalReq {
     const double* x;       // point to evaluate (6 + m values, or 6)
+    double hfac;           // factor of the Hessian rows the T_HG tasks write: z * scale / n (objects.py:380), or 1 (diagnostics)
     int32_t want_h, use_xi;
 };
 
@@ -85,26 +87,28 @@ struct WS {
     double*   scrH;        // [C * 496]  per-cell packed local Hessian of the last evaluation
     double*   vecs;        // [V]      NVEC vectors of length 6 + cell_cap per candidate
     double*   mats;        // [M]      H, H2 (N x N) and the packed Cholesky factor per candidate
-    uint2*    items;       // [2 * C]  work lists of k_eval (candidate, cell), double-buffered by round parity
-    uint2*    hitems;      // [2 * C]  work lists of k_hgather (candidate, grid point), double-buffered
-    int32_t*  live;        // [2 * n_cand]  live candidates of a round (small systems from the front, big ones from the back)
-    unsigned long long* counters;   // [16]  [p]: (#live small << 32 | #items), [2 + p]: (#live big << 32 | #hitems), p = parity
-    int64_t   items_cap;
+    // device-side scheduler (sched.cuh): bounded multi-producer / multi-consumer ring of tasks
+    uint2*    q_task;      // [q_cap]  x = type << 28 | candidate, y = first item of the task
+    uint32_t* q_seq;       // [q_cap]  slot sequence numbers (slot i is free for ticket t when seq == t, full when seq == t + 1)
+    int32_t*  pending;     // [n_cand] tasks of the candidate's current stage that have not finished yet
+    unsigned long long* counters;   // [16]  Q_HEAD, Q_TAIL, Q_DONE, then busy-cycle / task statistics (sched.cuh)
+    uint32_t  q_mask;      // q_cap - 1 (power of two)
     int32_t   n_cand;
 };
 
 struct Layout {
     size_t total;
     size_t o_pix_y, o_pix_rc, o_pix_s, o_pix_dist, o_gval, o_cell_start, o_cell_amask, o_cellmap, o_grid_rc, o_grid_tmp, o_cell_list,
-           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_scrH, o_vecs, o_mats, o_items, o_hitems, o_live, o_counters;
-    int64_t C;
+           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_scrH, o_vecs, o_mats, o_q_task, o_q_seq, o_pending, o_counters;
+    int64_t C, q_cap;
     int32_t n_cand;
 };
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
 // P, C, T, V, M: totals of the per-pixel, per-cell, per-table, per-vector and per-matrix arrays of the batch
-inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M, int32_t n_cand)
+// K = upper bound of the number of tasks that can be in flight (sdsm_plan_batch: sum over candidates of the tasks of one stage)
+inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M, int64_t K, int32_t n_cand)
 {
     Layout L{};
     size_t o = 0;
@@ -130,11 +134,14 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_scrH = take(sizeof(double) * SCRH * C);
     L.o_vecs = take(sizeof(double) * V);
     L.o_mats = take(sizeof(double) * M);
-    L.o_items = take(sizeof(uint2) * 2 * C);
-    L.o_hitems = take(sizeof(uint2) * 2 * C);
-    L.o_live = take(sizeof(int32_t) * 2 * (size_t)n_cand);
+    int64_t q_cap = 1024;
+    while (q_cap < K + 1024) q_cap <<= 1;
+    L.o_q_task = take(sizeof(uint2) * q_cap);
+    L.o_q_seq = take(sizeof(uint32_t) * q_cap);
+    L.o_pending = take(sizeof(int32_t) * (size_t)n_cand);
     L.o_counters = take(sizeof(unsigned long long) * 16);
     L.C = C;
+    L.q_cap = q_cap;
     L.n_cand = n_cand;
     L.total = o;
     return L;
@@ -165,11 +172,11 @@ inline WS make_ws(void* base, const Layout& L)
     w.scrH = (double*)(b + L.o_scrH);
     w.vecs = (double*)(b + L.o_vecs);
     w.mats = (double*)(b + L.o_mats);
-    w.items = (uint2*)(b + L.o_items);
-    w.hitems = (uint2*)(b + L.o_hitems);
-    w.live = (int32_t*)(b + L.o_live);
+    w.q_task = (uint2*)(b + L.o_q_task);
+    w.q_seq = (uint32_t*)(b + L.o_q_seq);
+    w.pending = (int32_t*)(b + L.o_pending);
     w.counters = (unsigned long long*)(b + L.o_counters);
-    w.items_cap = L.C;
+    w.q_mask = (uint32_t)(L.q_cap - 1);
     w.n_cand = L.n_cand;
     return w;
 }
@@ -248,6 +255,89 @@ __device__ __forceinline__ bool fp_member(int lab, const int32_t* fp, int n)
     if (lab == 0) return false;
     for (int k = 0; k < n; ++k) if (fp[k] == lab) return true;
     return false;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Device-side task queue (bounded MPMC ring with per-slot sequence numbers).  Tickets are 64-bit counters; slot
+// t & q_mask is free for the producer of ticket t when its sequence number equals (uint32) t, and holds the task for
+// the consumer of ticket t when it equals (uint32) t + 1; the consumer hands it on with t + q_cap.  The ring is sized
+// above the number of tasks that can be in flight (sdsm_plan_batch), so producers only ever wait for a consumer that
+// has claimed its ticket and is about to read the slot.
+
+enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG, Q_CYC_CTRL, Q_CYC_IDLE, Q_N_EVAL, Q_N_HG, Q_N_CTRL, Q_CYC_TOTAL };
+enum { T_CTRL = 0, T_EVAL = 1, T_HG = 2 };
+constexpr uint32_t T_SHIFT = 28, T_CMASK = (1u << T_SHIFT) - 1u;
+
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// one thread: publishes one task under ticket `t` (the ticket was reserved with atomicAdd on Q_TAIL)
+__device__ __forceinline__ void q_put(const WS& ws, unsigned long long t, uint32_t type, uint32_t c, uint32_t first)
+{
+    const uint32_t slot = (uint32_t)t & ws.q_mask;
+    while (ld_acquire_u32(ws.q_seq + slot) != (uint32_t)t) {
+        if (ld_relaxed_u64(ws.counters + Q_ABORT)) return;
+        __nanosleep(32);
+    }
+    ws.q_task[slot] = make_uint2((type << T_SHIFT) | c, first);
+    st_release_u32(ws.q_seq + slot, (uint32_t)t + 1u);
+}
+
+// whole CTA: publishes `count` tasks (type, c, first = k * stride for k < count).  Everything the CTA wrote before the call
+// is visible to the consumers of the tasks.  s_base: one unsigned long long of shared memory.
+template <int BLOCK>
+__device__ __forceinline__ void q_push_range(const WS& ws, uint32_t type, uint32_t c, int count, int stride, unsigned long long* s_base)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) *s_base = atomicAdd(ws.counters + Q_TAIL, (unsigned long long)count);
+    __syncthreads();
+    const unsigned long long base = *s_base;
+    for (int k = threadIdx.x; k < count; k += BLOCK) q_put(ws, base + k, type, c, (uint32_t)(k * stride));
+}
+
+// one thread: publishes a single task
+__device__ __forceinline__ void q_push_one(const WS& ws, uint32_t type, uint32_t c, uint32_t first)
+{
+    const unsigned long long t = atomicAdd(ws.counters + Q_TAIL, 1ull);
+    q_put(ws, t, type, c, first);
+}
+
+// one thread: claims the next ticket and waits for its task.  Returns false when every candidate is finished, or when the
+// watchdog fired: a CTA that has been idle since `timeout_ns` after its start sets Q_ABORT and everybody leaves.
+__device__ __forceinline__ bool q_pop(const WS& ws, unsigned long long n_target, unsigned long long timeout_ns, unsigned long long t_start,
+                                      uint2* task)
+{
+    const unsigned long long t = atomicAdd(ws.counters + Q_HEAD, 1ull);
+    const uint32_t slot = (uint32_t)t & ws.q_mask;
+    unsigned ns = 32, spins = 0;
+    while (ld_acquire_u32(ws.q_seq + slot) != (uint32_t)t + 1u) {
+        if (ld_relaxed_u64(ws.counters + Q_DONE) >= n_target) return false;
+        if (ld_relaxed_u64(ws.counters + Q_ABORT)) return false;
+        if ((++spins & 1023u) == 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+            if (now - t_start > timeout_ns) { atomicExch(ws.counters + Q_ABORT, 1ull); return false; }
+        }
+        __nanosleep(ns);
+        if (ns < 512) ns <<= 1;
+    }
+    *task = ws.q_task[slot];
+    st_release_u32(ws.q_seq + slot, (uint32_t)t + ws.q_mask + 1u);
+    return true;
 }
 
 }  // namespace sdsm

@@ -1,9 +1,9 @@
-// K3b: k_ctrl -- one CTA per live candidate, between two evaluations of F.  It gathers the per-cell results of k_eval into
-// value / gradient / Hessian, advances the candidate's state machine
+// K3b: control tasks -- one CTA advances one candidate between two evaluations of F.  It gathers the per-cell results of the
+// evaluation tasks into value / gradient / Hessian, advances the candidate's state machine
 //   elliptical initialisation (objects.py:321-358) -> DSM solve (objects.py:394-410, dsm.py:431-490) -> result
-// up to the next point where F must be evaluated, files that request (work items for the next k_eval) and returns.
+// up to the next point where F must be evaluated, files that request (evaluation tasks, sched.cuh) and returns.
 // The interior-point iterations restate cvxopt.solvers.cp (oracle/cpsolver.py, which this mirrors line by line); the
-// local variables of that loop live in CState across rounds.
+// local variables of that loop live in CState across tasks.
 #pragma once
 #include "common.cuh"
 #include "eval.cuh"
@@ -14,7 +14,7 @@ constexpr int MAX_RELAXED = 8;
 constexpr double CP_STEP = 0.99, CP_BETA = 0.5, CP_ALPHA = 0.01;
 
 enum { V_X = 0, V_G, V_DX, V_T, V_NX, V_NG, V_SX, V_SDX, V_RD, V_X0, V_E, V_W };
-enum { PC_START = 0, PC_TOP, PC_RESTORED, PC_TRIAL, PC_VAL1, PC_VALINIT, PC_JX, PC_J0, PC_FINAL, PC_DONE };
+enum { PC_START = 0, PC_TOP, PC_RESTORED, PC_TRIAL, PC_VAL1, PC_VALINIT, PC_JX, PC_J0, PC_FINAL, PC_DONE, PC_TRACESTART };
 enum { STG_ELL1 = 0, STG_ELL2, STG_DSM, STG_TRACE };
 
 struct Prob {
@@ -175,94 +175,91 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
         s += P.alpha * (v / sqrt(v * v + P.eps));                             // dsm.py:350
         g[6 + j] = sc * s;
     }
-    // the xi-theta and xi-xi blocks of the Hessian are assembled by k_hgather (one warp per grid point), before k_ctrl runs
+    // the xi-theta and xi-xi blocks of the Hessian are assembled by the T_HG tasks (one warp per grid point), before this task runs
     __syncthreads();
     *psi_out = psi;
     return sc * psi;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// k_hgather: rows 6.. of the Hessian (the xi-theta and xi-xi blocks, dsm.py:369-374) of every candidate that asked for one.
-// One warp per (candidate, grid point j): it visits the <= 25 cells that see j in a fixed order and adds their local
+// T_HG tasks: rows 6.. of the Hessian (the xi-theta and xi-xi blocks, dsm.py:369-374) of a candidate that asked for one.
+// One warp per grid point j: it visits the <= 25 cells that see j in a fixed order and adds their local
 // Hessian rows into 81 + 6 accumulators (the grid points of the 9 x 9 cells around j's cell, and theta), then writes row
 // 6 + j of H = hz * scale_cp * Hess psi (both triangles; entries outside the 9 x 9 neighbourhood stay zero).
 
-constexpr int HG_BLOCK = 256;
+constexpr int HG_BLOCK = SOLVE_BLOCK;
+constexpr int HG_WARPS = HG_BLOCK / 32;
 constexpr int HG_ACC = 96;
 
-__global__ void __launch_bounds__(HG_BLOCK)
-k_hgather(Par par, const sdsm_cand* __restrict__ cands, WS ws, int parity, int unit_scale)
+// task (c, first): the CTA's warps take the grid points first .. first + HG_WARPS of candidate c.  s_acc: HG_WARPS * HG_ACC doubles.
+__device__ __forceinline__ void hg_task(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* s_acc)
 {
-    __shared__ double s_acc[(HG_BLOCK / 32) * HG_ACC];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double* acc = s_acc + warp * HG_ACC;
-    const int n_h = (int)(ws.counters[2 + parity] & 0xffffffffull);
-    const uint2* hitems = ws.hitems + (size_t)parity * ws.items_cap;
     constexpr int SP = 4 * NC + 1;   // 9
-    for (int w = blockIdx.x * (HG_BLOCK / 32) + warp; w < n_h; w += gridDim.x * (HG_BLOCK / 32)) {
-        const uint2 it = hitems[w];
-        const int c = (int)it.x, j = (int)it.y;
-        const sdsm_cand* cd = cands + c;
-        const int64_t cell_off = cd->cell_off;
-        const CInfo ci = ws.cinfo[c];
-        const int cw = ci.cw, ch = ci.ch, N = 6 + ci.m;
-        const double fac = unit_scale ? 1.0 : ws.cstate[c].z * (par.scale / (double)cd->n);
-        const int32_t* cstart = ws.cell_start + cell_off;
-        const uint32_t* amask = ws.cell_amask + cell_off;
-        const int32_t* cellmap = ws.cellmap + cell_off;
-        const double* scrH = ws.scrH + (size_t)cell_off * SCRH;
-        double* H = ws.mats + cd->mat_off;
-        const uint32_t gp = ws.grid_rc[cell_off + j];
-        const int ja = (int)(gp & 0xffffu) / par.sub, jb = (int)(gp >> 16) / par.sub;
-        __syncwarp();
-        for (int t = lane; t < HG_ACC; t += 32) acc[t] = 0.0;
-        __syncwarp();
-        for (int da = -NC; da <= NC; ++da) {
-            const int a = ja - da;                       // cell = j's cell - (da, db): it sees j in slot (da, db)
-            if (a < 0 || a >= ch) continue;
-            for (int db = -NC; db <= NC; ++db) {
-                const int b = jb - db;
-                if (b < 0 || b >= cw) continue;
-                const int cell = a * cw + b;
-                if (cstart[cell + 1] == cstart[cell]) continue;
-                const uint32_t am = amask[cell];
-                const int lj = local_index(am, da, db);
-                if (lj < 0) continue;
-                const int L = 6 + __popc(am);
-                if (lane < L) {
-                    const double v = scrH[(size_t)cell * SCRH + (lane >= lj ? tri(lane, lj) : tri(lj, lane))];
-                    int t;
-                    if (lane < 6) t = SP * SP + lane;
-                    else {
-                        const int s = __fns(am, 0, lane - 6 + 1);           // slot of local entry `lane`
-                        t = (s / 5 - NC - da + 2 * NC) * SP + (s % 5 - NC - db + 2 * NC);
-                    }
-                    acc[t] += v;
+    const sdsm_cand* cd = cands + c;
+    const int64_t cell_off = cd->cell_off;
+    const CInfo ci = ws.cinfo[c];
+    const int j = first + warp;
+    if (j >= ci.m) return;
+    const int cw = ci.cw, ch = ci.ch, N = 6 + ci.m;
+    const EvalReq rq = ws.req[c];
+    const double fac = rq.hfac;
+    const int32_t* cstart = ws.cell_start + cell_off;
+    const uint32_t* amask = ws.cell_amask + cell_off;
+    const int32_t* cellmap = ws.cellmap + cell_off;
+    const double* scrH = ws.scrH + (size_t)cell_off * SCRH;
+    double* H = ws.mats + cd->mat_off;
+    const uint32_t gp = ws.grid_rc[cell_off + j];
+    const int ja = (int)(gp & 0xffffu) / par.sub, jb = (int)(gp >> 16) / par.sub;
+    __syncwarp();
+    for (int t = lane; t < HG_ACC; t += 32) acc[t] = 0.0;
+    __syncwarp();
+    for (int da = -NC; da <= NC; ++da) {
+        const int a = ja - da;                       // cell = j's cell - (da, db): it sees j in slot (da, db)
+        if (a < 0 || a >= ch) continue;
+        for (int db = -NC; db <= NC; ++db) {
+            const int b = jb - db;
+            if (b < 0 || b >= cw) continue;
+            const int cell = a * cw + b;
+            if (cstart[cell + 1] == cstart[cell]) continue;
+            const uint32_t am = amask[cell];
+            const int lj = local_index(am, da, db);
+            if (lj < 0) continue;
+            const int L = 6 + __popc(am);
+            if (lane < L) {
+                const double v = scrH[(size_t)cell * SCRH + (lane >= lj ? tri(lane, lj) : tri(lj, lane))];
+                int t;
+                if (lane < 6) t = SP * SP + lane;
+                else {
+                    const int s = __fns(am, 0, lane - 6 + 1);           // slot of local entry `lane`
+                    t = (s / 5 - NC - da + 2 * NC) * SP + (s % 5 - NC - db + 2 * NC);
                 }
-                __syncwarp();
+                acc[t] += v;
             }
+            __syncwarp();
         }
-        const double* x = ws.req[c].x;
-        for (int t = lane; t < SP * SP; t += 32) {
-            const int ka = ja + t / SP - 2 * NC, kb = jb + t % SP - 2 * NC;
-            if (ka < 0 || ka >= ch || kb < 0 || kb >= cw) continue;
-            const int k = cellmap[ka * cw + kb];
-            if (k < 0) continue;
-            double s = acc[t];
-            if (k == j) {
-                const double v = x[6 + j];
-                const double t3 = v * v, t2 = sqrt(t3 + par.epsilon);
-                double gd = par.alpha * (1.0 / t2 - t3 / (t2 * t2 * t2));      // dsm.py:372-374
-                if (gd < 0) gd = 0;
-                s += gd;
-            }
-            H[(size_t)(6 + j) * N + 6 + k] = s * fac;
+    }
+    const double* x = rq.x;
+    for (int t = lane; t < SP * SP; t += 32) {
+        const int ka = ja + t / SP - 2 * NC, kb = jb + t % SP - 2 * NC;
+        if (ka < 0 || ka >= ch || kb < 0 || kb >= cw) continue;
+        const int k = cellmap[ka * cw + kb];
+        if (k < 0) continue;
+        double s = acc[t];
+        if (k == j) {
+            const double v = x[6 + j];
+            const double t3 = v * v, t2 = sqrt(t3 + par.epsilon);
+            double gd = par.alpha * (1.0 / t2 - t3 / (t2 * t2 * t2));      // dsm.py:372-374
+            if (gd < 0) gd = 0;
+            s += gd;
         }
-        if (lane < 6) {
-            const double s = acc[SP * SP + lane] * fac;
-            H[(size_t)(6 + j) * N + lane] = s;
-            H[(size_t)lane * N + 6 + j] = s;
-        }
+        H[(size_t)(6 + j) * N + 6 + k] = s * fac;
+    }
+    if (lane < 6) {
+        const double s = acc[SP * SP + lane] * fac;
+        H[(size_t)(6 + j) * N + lane] = s;
+        H[(size_t)lane * N + 6 + j] = s;
     }
 }
 
@@ -364,7 +361,7 @@ __device__ __forceinline__ void carve_smem_big(Sm& sm, char* base)
 }
 
 template <int BLOCK>
-__device__ bool cholesky_big(const double* __restrict__ H, int N, double* __restrict__ A, Sm& sb)
+__device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = BLOCK / 32;
@@ -457,7 +454,7 @@ __device__ bool cholesky_big(const double* __restrict__ H, int N, double* __rest
 // v := (A A^T)^-1 v with the factor of cholesky_big; blocked forward / backward substitution, v in global memory.
 // Per 32-block: the diagonal block is staged in shared memory and solved by warp 0, then every thread updates one row.
 template <int BLOCK>
-__device__ void chol_solve_big(const double* __restrict__ A, int N, double* v, Sm& sb)
+__device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     __syncthreads();
@@ -585,10 +582,10 @@ __device__ __forceinline__ void ipm_begin(CState& S)
     S.sv_t = S.sv_s = S.sv_z = S.sv_d = S.sv_lm = S.sv_dt = S.sv_dz = S.sv_ds = S.sv_resx = S.sv_rznl = S.sv_rxt = 0.0;
 }
 
-// Files the evaluation of F at vector `vec` for the next k_eval (work list parity ^ 1).  Returns false, filing nothing,
-// if the point is not finite (the reference's Energy would raise on NaN parameters).
+// Prepares the evaluation of F at vector `vec`: records the request in S (it is published by publish_request when the control
+// task ends).  Returns false, recording nothing, if the point is not finite (the reference's Energy would raise on NaN).
 template <int BLOCK>
-__device__ bool file_request(const Prob& P, Sm& sm, CState& S, const WS& ws, int c, int parity, int vec, int gvec, int want_h)
+__device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int want_h)
 {
     const int tid = threadIdx.x;
     const int N = S.use_xi ? P.N : 6;
@@ -598,32 +595,14 @@ __device__ bool file_request(const Prob& P, Sm& sm, CState& S, const WS& ws, int
     if (__syncthreads_or(bad)) return false;
     S.req_vec = vec; S.req_gvec = gvec; S.req_h = want_h;
     if (want_h) S.nh += 1; else S.nf += 1;                      // evaluation counters (reported in out.info)
-    const int other = parity ^ 1;
-    const bool big = N > SMALL_N_MAX;                           // who advances this candidate next: k_ctrl or k_ctrl_big
-    const int n_h = (want_h && S.use_xi) ? P.m : 0;             // rows of the Hessian k_hgather assembles
-    if (tid == 0) {
-        EvalReq rq; rq.x = x; rq.want_h = want_h; rq.use_xi = S.use_xi;
-        ws.req[c] = rq;
-        const unsigned long long old0 = atomicAdd(&ws.counters[other], ((big ? 0ull : 1ull) << 32) | (unsigned long long)P.n_ne);
-        const unsigned long long old2 = atomicAdd(&ws.counters[2 + other], ((big ? 1ull : 0ull) << 32) | (unsigned long long)n_h);
-        if (big) ws.live[(size_t)other * ws.n_cand + (ws.n_cand - 1 - (int)(old2 >> 32))] = c;
-        else ws.live[(size_t)other * ws.n_cand + (int)(old0 >> 32)] = c;
-        sm.flag[2] = (int)(old0 & 0xffffffffull);
-        sm.flag[3] = (int)(old2 & 0xffffffffull);
-    }
-    __syncthreads();
-    const int start = sm.flag[2], hstart = sm.flag[3];
-    uint2* items = ws.items + (size_t)other * ws.items_cap + start;
-    for (int i = tid; i < P.n_ne; i += BLOCK) items[i] = make_uint2((unsigned)c, (unsigned)P.clist[i]);
-    uint2* hitems = ws.hitems + (size_t)other * ws.items_cap + hstart;
-    for (int i = tid; i < n_h; i += BLOCK) hitems[i] = make_uint2((unsigned)c, (unsigned)i);
-    __syncthreads();
     return true;
 }
 
-// Advances candidate c by one round: consumes the evaluation it asked for, runs up to the next evaluation request.
+// Advances candidate c by one control task: consumes the evaluation it asked for, runs up to the next evaluation request.
+// Returns true if an evaluation was requested (ws.req[c] describes it; the caller schedules it), false if the candidate is
+// finished.  first = false: there is an evaluation to consume (always true except for the task that starts the candidate).
 template <int BLOCK, bool BIG>
-__device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c, int parity,
+__device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
                           Sm& sm, const sdsm_out& out, double* trace)
 {
     const int tid = threadIdx.x;
@@ -637,7 +616,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
     int32_t* info = out.d_info + (size_t)c * 8;
 
     double f0 = 0.0;
-    if (S.pc != PC_START) {
+    if (S.pc != PC_START && S.pc != PC_TRACESTART) {
         double psi = 0.0;
         double* gout = P.V + (size_t)S.req_gvec * ld;
         if (!S.use_xi) f0 = S.req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
@@ -649,10 +628,11 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
     }
     bool hres_alt = false;
     bool yield = false;
+    bool requested = false;
 
 #define REQUEST(vec_, gvec_, h_, next_, onbad_)                                                       \
     do {                                                                                              \
-        if (file_request<BLOCK>(P, sm, S, ws, c, parity, vec_, gvec_, h_)) { S.pc = next_; yield = true; } \
+        if (prepare_request<BLOCK>(P, S, vec_, gvec_, h_)) { S.pc = next_; yield = true; requested = true; } \
         else { onbad_; }                                                                              \
     } while (0)
 
@@ -681,6 +661,7 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
             else S.pc = PC_BEGIN_DSM;
             break;
         }
+        case PC_TRACESTART: { S.pc = PC_IPMSTART; break; }      // diagnostics: one solve from the x the host provided
         case PC_IPMSTART: {
             ipm_begin(S);
             REQUEST(V_X, V_G, 1, PC_TOP, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
@@ -999,56 +980,20 @@ __device__ void ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, c
     }
 #undef REQUEST
     __syncthreads();
-    if (tid == 0) ws.cstate[c] = S;
+    if (tid == 0) {
+        ws.cstate[c] = S;
+        if (requested) {
+            EvalReq rq;
+            rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = S.z * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;
+            ws.req[c] = rq;
+        }
+    }
+    __syncthreads();
+    return requested;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// kernels
-
-// Round 0 (order != nullptr): CTA b starts candidate order[b].  Later rounds: CTA b advances the b-th live candidate of
-// work list `parity` whose current system is small (N <= SMALL_N_MAX).  Requests go to work list parity ^ 1.
-__global__ void __launch_bounds__(CTRL_BLOCK, 4)
-k_ctrl(Img img, Par par, const sdsm_cand* __restrict__ cands, const int32_t* __restrict__ order, int n_first, WS ws, sdsm_out out,
-       int parity, int lcap, double* trace)
-{
-    extern __shared__ __align__(16) char smem_ctrl[];
-    Sm sm;
-    carve_smem(sm, smem_ctrl, lcap);
-    int c;
-    if (order) {
-        if ((int)blockIdx.x >= n_first) return;
-        c = order[blockIdx.x];
-    } else {
-        const int n_live = (int)(ws.counters[parity] >> 32);
-        if ((int)blockIdx.x >= n_live) return;
-        c = ws.live[(size_t)parity * ws.n_cand + blockIdx.x];
-    }
-    const sdsm_cand cd = cands[c];
-    const CInfo ci = ws.cinfo[c];
-    ctrl_step<CTRL_BLOCK, false>(par, img, cd, ci, ws, c, parity, sm, out, trace);
-}
-
-// the live candidates whose current system is large (filed from the back of the live list)
-__global__ void __launch_bounds__(BIG_BLOCK, 1)
-k_ctrl_big(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out out, int parity, double* trace)
-{
-    extern __shared__ __align__(16) char smem_ctrl[];
-    Sm sm;
-    carve_smem_big(sm, smem_ctrl);
-    const int n_live = (int)(ws.counters[2 + parity] >> 32);
-    if ((int)blockIdx.x >= n_live) return;
-    const int c = ws.live[(size_t)parity * ws.n_cand + (ws.n_cand - 1 - blockIdx.x)];
-    const sdsm_cand cd = cands[c];
-    const CInfo ci = ws.cinfo[c];
-    ctrl_step<BIG_BLOCK, true>(par, img, cd, ci, ws, c, parity, sm, out, trace);
-}
-
-// Publishes the size of work list `parity` for the host (pinned memory), after k_ctrl has filled it.
-__global__ void k_publish(WS ws, int parity, unsigned long long* host_flag)
-{
-    host_flag[0] = ws.counters[parity];
-    host_flag[1] = ws.counters[2 + parity];
-}
+// kernels (the persistent solver kernel is in sched.cuh)
 
 // Result rasterisation (objects.py:198-211): foreground inside omega, its bounding box, on_boundary.  One CTA per candidate.
 constexpr int FIN_BLOCK = 256;
@@ -1136,99 +1081,6 @@ k_finish(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS w
             if (s_box[1] >= 0) { out.d_fgbox[c * 4 + 0] = s_box[0]; out.d_fgbox[c * 4 + 1] = s_box[1]; out.d_fgbox[c * 4 + 2] = s_box[2]; out.d_fgbox[c * 4 + 3] = s_box[3]; }
         }
     }
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// diagnostics for the parity tests (single candidate of the last solved batch)
-
-// files the evaluation of F (with Hessian) of candidate c at xin into work list `parity ^ 1`
-__global__ void __launch_bounds__(CTRL_BLOCK)
-k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, const double* __restrict__ xin, int parity, int lcap)
-{
-    extern __shared__ __align__(16) char smem_ctrl[];
-    Sm sm;
-    carve_smem(sm, smem_ctrl, lcap);
-    const int tid = threadIdx.x;
-    const sdsm_cand cd = cands[c];
-    const CInfo ci = ws.cinfo[c];
-    CState S = ws.cstate[c];
-    Prob P;
-    setup_problem(P, par, cd, ci, ws);
-    S.use_xi = P.m > 0 ? 1 : 0;
-    const int N = P.N;
-    double* nx = P.V + (size_t)V_NX * P.ld;
-    for (int i = tid; i < N; i += CTRL_BLOCK) nx[i] = xin[i];
-    for (size_t i = tid; i < (size_t)N * N; i += CTRL_BLOCK) P.H[i] = 0.0;
-    __syncthreads();
-    const bool ok = file_request<CTRL_BLOCK>(P, sm, S, ws, c, parity, V_NX, V_NG, 1);
-    S.pc = ok ? PC_DONE : -1;
-    __syncthreads();
-    if (tid == 0) ws.cstate[c] = S;
-}
-
-__global__ void __launch_bounds__(CTRL_BLOCK)
-k_diag_eval_end(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, double* value, double* grad, double* Hout, int lcap)
-{
-    extern __shared__ __align__(16) char smem_ctrl[];
-    Sm sm;
-    carve_smem(sm, smem_ctrl, lcap);
-    const int tid = threadIdx.x;
-    const sdsm_cand cd = cands[c];
-    const CInfo ci = ws.cinfo[c];
-    Prob P;
-    setup_problem(P, par, cd, ci, ws);
-    P.scale_cp = 1.0;
-    const int N = P.N;
-    double* g = P.V + (size_t)V_NG * P.ld;
-    const double* xe = P.V + (size_t)V_NX * P.ld;
-    double psi = 0;
-    double f;
-    if (ws.cstate[c].pc == -1) f = NAN;
-    else if (P.m > 0) f = gather_cells<CTRL_BLOCK, true>(P, sm, xe, g, 1.0, &psi);
-    else f = gather_poly<CTRL_BLOCK, true>(P, sm, g, 1.0, &psi);
-    __syncthreads();
-    if (tid == 0) *value = f;
-    for (int i = tid; i < N; i += CTRL_BLOCK) grad[i] = g[i];
-    for (size_t i = tid; i < (size_t)N * N; i += CTRL_BLOCK) Hout[i] = P.H[i];
-}
-
-// starts one interior-point solve of candidate c from x0 (STG_TRACE); k_ctrl rounds record the iterates
-__global__ void __launch_bounds__(CTRL_BLOCK)
-k_diag_trace_begin(Par par, const sdsm_cand* __restrict__ cands, int c, int use_xi_, WS ws, const double* __restrict__ x0, int parity, int lcap)
-{
-    extern __shared__ __align__(16) char smem_ctrl[];
-    Sm sm;
-    carve_smem(sm, smem_ctrl, lcap);
-    const int tid = threadIdx.x;
-    const sdsm_cand cd = cands[c];
-    const CInfo ci = ws.cinfo[c];
-    CState S = ws.cstate[c];
-    Prob P;
-    setup_problem(P, par, cd, ci, ws);
-    S.use_xi = (use_xi_ && P.m > 0) ? 1 : 0;
-    S.stage = STG_TRACE;
-    const int N = S.use_xi ? P.N : 6;
-    double* x = P.V + (size_t)V_X * P.ld;
-    for (int i = tid; i < N; i += CTRL_BLOCK) x[i] = x0[i];
-    if (S.use_xi) for (size_t i = tid; i < (size_t)N * N; i += CTRL_BLOCK) P.H[i] = 0.0;
-    __syncthreads();
-    ipm_begin(S);
-    S.r_ipm = 0;
-    if (file_request<CTRL_BLOCK>(P, sm, S, ws, c, parity, V_X, V_G, 1)) S.pc = PC_TOP;
-    else { S.r_ipm = 2; S.pc = PC_DONE; }
-    __syncthreads();
-    if (tid == 0) ws.cstate[c] = S;
-}
-
-__global__ void k_diag_trace_end(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, double* xout, int32_t* status_iters)
-{
-    const sdsm_cand cd = cands[c];
-    const CState* S = ws.cstate + c;
-    const int ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
-    const int N = S->use_xi ? 6 + ws.cinfo[c].m : 6;
-    const double* x = ws.vecs + cd.vec_off + (size_t)V_X * ld;
-    for (int i = threadIdx.x; i < N; i += blockDim.x) xout[i] = x[i];
-    if (threadIdx.x == 0) { status_iters[0] = S->r_ipm; status_iters[1] = S->iters; }
 }
 
 // register-resident FP64 FMA peak (the FP64 roofline denominator; MEASURED_PEAKS.json has none)

@@ -1,11 +1,11 @@
-// K3a: k_eval -- the energy psi, its gradient and (on request) its Hessian (dsm.py:291-385) for EVERY live candidate of a
-// round in one launch.  A work item is one non-empty pixel cell of one candidate; a warp owns an item.
+// K3a: evaluation tasks -- the energy psi, its gradient and (on request) its Hessian (dsm.py:291-385).  A work item is one
+// non-empty pixel cell of one candidate; a warp owns an item, a task (sched.cuh) is EVAL_WARPS consecutive items.
 //
 // All pixels of a subsample x subsample cell see the same <= 25 grid points, so a cell has a dense local parameter vector
 // of length L = 6 + #active slots.  Per chunk of 32 pixels each lane builds its pixel's local row into a shared-memory
 // tile, then the lanes switch roles and own outputs: lane e accumulates local gradient entry e, and 4x4 register blocks
 // of the local Hessian.  Local results go to the cell's scratch (scrG / scrH); k_ctrl gathers them into the candidate's
-// value / gradient / Hessian in a fixed order -- no atomics, bit-reproducible.
+// value / gradient / Hessian in a fixed order -- no floating-point atomics, bit-reproducible whatever the schedule.
 #pragma once
 #include "common.cuh"
 
@@ -40,8 +40,8 @@ __device__ __forceinline__ int nth_set_bit(uint32_t mask, int n)
 
 template <bool HESS>
 __device__ __forceinline__ void eval_cell_poly(const double* __restrict__ py, const uint32_t* __restrict__ prc, int npix,
-                                               const double* __restrict__ xr, const double* __restrict__ xc, const double* __restrict__ x,
-                                               double tol, double* __restrict__ sg, double* __restrict__ sh)
+                                               const double* __restrict__ xr, const double* __restrict__ xc, const double* x,
+                                               double tol, double* sg, double* sh)
 {
     const int lane = threadIdx.x & 31;
     const double a1 = x[0], a2 = x[1], a3 = x[2], b1 = x[3], b2 = x[4], c0 = x[5];
@@ -91,8 +91,8 @@ __device__ __forceinline__ void eval_cell_poly(const double* __restrict__ py, co
 template <bool HESS>
 __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
                                              int npix, uint32_t am, const double* __restrict__ xr, const double* __restrict__ xc,
-                                             const double* __restrict__ x, double tol, double* __restrict__ Tt, const int* __restrict__ slotj,
-                                             double* __restrict__ sg, double* __restrict__ sh)
+                                             const double* x, double tol, double* Tt, const int* slotj,
+                                             double* sg, double* sh)
 {
     const int lane = threadIdx.x & 31;
     double* U = Tt + 32 * TILE_LD;
@@ -233,55 +233,48 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
 
 constexpr size_t EVAL_SMEM = sizeof(double) * EVAL_WARPS * TILE_DOUBLES;
 
-// One launch evaluates every live candidate of the round: items = work list `parity` (built by k_ctrl of the previous
-// round), each item one (candidate, cell).  Also clears the other work list's counter for k_ctrl to refill.
-__global__ void __launch_bounds__(EVAL_BLOCK, 2)
-k_eval(Par par, const sdsm_cand* __restrict__ cands, WS ws, int parity)
+// Evaluation task (c, first): the CTA's warps take the non-empty cells cell_list[first .. first + EVAL_WARPS) of candidate c,
+// one warp per cell, and leave the per-cell value / gradient / Hessian in scrG / scrH.  smem_eval: EVAL_SMEM bytes.
+__device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first,
+                                          double* smem_eval, int* s_slotj)
 {
-    extern __shared__ __align__(16) double smem_eval[];
-    __shared__ int s_slotj[EVAL_WARPS * 32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double* Tt = smem_eval + warp * TILE_DOUBLES;
     int* slotj = s_slotj + warp * 32;
-    const unsigned long long cnt = ws.counters[parity];
-    const int n_items = (int)(cnt & 0xffffffffull);
-    if (blockIdx.x == 0 && threadIdx.x == 0) { ws.counters[parity ^ 1] = 0ull; ws.counters[2 + (parity ^ 1)] = 0ull; }
-    const uint2* items = ws.items + (size_t)parity * ws.items_cap;
-
-    for (int w = blockIdx.x * EVAL_WARPS + warp; w < n_items; w += gridDim.x * EVAL_WARPS) {
-        const uint2 it = items[w];
-        const int c = (int)it.x, cell = (int)it.y;
-        const sdsm_cand* cd = cands + c;
-        const int64_t pix_off = cd->pix_off, cell_off = cd->cell_off, tab_off = cd->tab_off;
-        const int h = cd->h;
-        const EvalReq rq = ws.req[c];
-        const int32_t* cstart = ws.cell_start + cell_off;
-        const int st = cstart[cell], npix = cstart[cell + 1] - st;
-        const double* py = ws.pix_y + pix_off + st;
-        const uint32_t* prc = ws.pix_rc + pix_off + st;
-        const double* xr = ws.xtab + tab_off;
-        const double* xc = xr + h;
-        double* sg = ws.scrG + (size_t)(cell_off + cell) * SCRG;
-        double* sh = ws.scrH + (size_t)(cell_off + cell) * SCRH;
-        if (!rq.use_xi) {
-            if (rq.want_h) eval_cell_poly<true>(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
-            else eval_cell_poly<false>(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
-            continue;
-        }
-        const int cw = ws.cinfo[c].cw;
-        const uint32_t am = ws.cell_amask[cell_off + cell];
-        const int na = __popc(am);
-        const int ca = cell / cw, cb = cell - ca * cw;
-        __syncwarp();
-        if (lane < na) {
-            const int s = nth_set_bit(am, lane);
-            slotj[lane] = ws.cellmap[cell_off + (ca + s / 5 - NC) * cw + (cb + s % 5 - NC)];
-        }
-        __syncwarp();
-        const float* gcell = ws.gval + (size_t)NSLOT * (pix_off + st);
-        if (rq.want_h) eval_cell_xi<true>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, sh);
-        else eval_cell_xi<false>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, sh);
+    const sdsm_cand* cd = cands + c;
+    const int64_t pix_off = cd->pix_off, cell_off = cd->cell_off, tab_off = cd->tab_off;
+    const CInfo ci = ws.cinfo[c];
+    const int idx = first + warp;
+    if (idx >= ci.n_ne) return;
+    const int cell = ws.cell_list[cell_off + idx];
+    const int h = cd->h;
+    const EvalReq rq = ws.req[c];
+    const int32_t* cstart = ws.cell_start + cell_off;
+    const int st = cstart[cell], npix = cstart[cell + 1] - st;
+    const double* py = ws.pix_y + pix_off + st;
+    const uint32_t* prc = ws.pix_rc + pix_off + st;
+    const double* xr = ws.xtab + tab_off;
+    const double* xc = xr + h;
+    double* sg = ws.scrG + (size_t)(cell_off + cell) * SCRG;
+    double* sh = ws.scrH + (size_t)(cell_off + cell) * SCRH;
+    if (!rq.use_xi) {
+        if (rq.want_h) eval_cell_poly<true>(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
+        else eval_cell_poly<false>(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
+        return;
     }
+    const int cw = ci.cw;
+    const uint32_t am = ws.cell_amask[cell_off + cell];
+    const int na = __popc(am);
+    const int ca = cell / cw, cb = cell - ca * cw;
+    __syncwarp();
+    if (lane < na) {
+        const int s = nth_set_bit(am, lane);
+        slotj[lane] = ws.cellmap[cell_off + (ca + s / 5 - NC) * cw + (cb + s % 5 - NC)];
+    }
+    __syncwarp();
+    const float* gcell = ws.gval + (size_t)NSLOT * (pix_off + st);
+    if (rq.want_h) eval_cell_xi<true>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, sh);
+    else eval_cell_xi<false>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, sh);
 }
 
 }  // namespace sdsm

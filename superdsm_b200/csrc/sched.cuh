@@ -1,0 +1,270 @@
+// K3: k_solve -- the persistent solver kernel.  Every candidate's fit is a chain of dependent steps
+//     control task -> evaluation tasks (one per EVAL_WARPS pixel cells) [-> Hessian-row tasks] -> control task -> ...
+// (a few dozen to a few thousand links, objects.py:361-412 around cvxopt's cp), and the chains of a batch differ in length
+// and width by orders of magnitude.  Instead of lock-step launches, the CTAs of one persistent grid pull tasks from a
+// device-side queue (common.cuh): whoever finishes the last evaluation task of a candidate publishes its next control
+// task, so every candidate advances at its own pace and a straggler only occupies the CTAs its own tasks need.
+// Candidates with few cells run their whole chain inside one CTA (no queue hop between the links).
+//
+// Nothing ever blocks on another task: a task only waits for a queue slot whose previous occupant has already been
+// claimed by a consumer.  The kernel ends when every candidate has reported completion (Q_DONE == n_target), or when the
+// watchdog fires (Q_ABORT; sdsm_solver_stats reports it).
+#pragma once
+#include "common.cuh"
+#include "eval.cuh"
+#include "ctrl.cuh"
+
+namespace sdsm {
+
+constexpr size_t SOLVE_SMEM_MIN = EVAL_SMEM > BIG_SMEM ? EVAL_SMEM : BIG_SMEM;
+__host__ __device__ inline size_t solve_smem_bytes(int lcap)
+{
+    const size_t a = ctrl_smem_bytes(lcap);
+    return a > SOLVE_SMEM_MIN ? a : SOLVE_SMEM_MIN;
+}
+
+struct SolveArgs {
+    int n_target;            // candidates that must finish
+    int lcap;                // shared-memory capacity (doubles) for a packed Cholesky factor
+    int solo_cells;          // candidates with at most this many non-empty cells run their chain inside one CTA
+    unsigned long long timeout_ns;   // watchdog: idle CTAs abort the kernel after this long
+    double* trace;           // diagnostics (STG_TRACE) or nullptr
+};
+
+__device__ __forceinline__ unsigned long long globaltimer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Seeds the queue: slot i holds the control task that starts candidate order[i] (most expensive first).
+__global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, int single)
+{
+    const uint32_t q_cap = ws.q_mask + 1u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < q_cap; i += gridDim.x * blockDim.x) {
+        if ((int)i < n_first) {
+            ws.q_task[i] = make_uint2(((uint32_t)T_CTRL << T_SHIFT) | (uint32_t)(order ? order[i] : single), 0u);
+            ws.q_seq[i] = i + 1u;
+        } else ws.q_seq[i] = i;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (int k = 0; k < 16; ++k) ws.counters[k] = 0ull;
+        ws.counters[Q_TAIL] = (unsigned long long)n_first;
+    }
+}
+
+// the CTA that finished a task of candidate c's current stage: the last one to finish starts the next stage
+template <int BLOCK>
+__device__ __forceinline__ void finish_stage_task(const WS& ws, uint32_t type, int c, int* s_flag, unsigned long long* s_base)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const int old = atomicSub(ws.pending + c, 1);
+        __threadfence();
+        int next = 0;                                        // 0: not the last, 1: control task, > 1: that many T_HG tasks
+        if (old == 1) {
+            const EvalReq rq = ws.req[c];
+            next = 1;
+            if (type == T_EVAL && rq.want_h && rq.use_xi) {
+                const int nt = (ws.cinfo[c].m + HG_WARPS - 1) / HG_WARPS;
+                ws.pending[c] = nt;
+                next = 1 + nt;
+            }
+        }
+        *s_flag = next;
+    }
+    __syncthreads();
+    const int next = *s_flag;
+    if (next == 0) return;
+    if (next == 1) { if (threadIdx.x == 0) q_push_one(ws, T_CTRL, (uint32_t)c, 0u); }
+    else q_push_range<BLOCK>(ws, T_HG, (uint32_t)c, next - 1, HG_WARPS, s_base);
+}
+
+__global__ void __launch_bounds__(SOLVE_BLOCK, 2)
+k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out out, SolveArgs args)
+{
+    constexpr int BLOCK = SOLVE_BLOCK;
+    extern __shared__ __align__(16) char smem_solve[];
+    __shared__ int s_slotj[EVAL_WARPS * 32];
+    __shared__ uint2 s_task;
+    __shared__ int s_flag;
+    __shared__ unsigned long long s_base;
+    const int tid = threadIdx.x;
+    const unsigned long long n_target = (unsigned long long)args.n_target;
+    unsigned long long t_start = 0, cyc[4] = {0, 0, 0, 0}, cnt[3] = {0, 0, 0};
+    if (tid == 0) t_start = globaltimer_ns();
+    const long long c_begin = clock64();
+
+    for (;;) {
+        if (tid == 0) {
+            const long long c0 = clock64();
+            uint2 task;
+            const bool ok = q_pop(ws, n_target, args.timeout_ns, t_start, &task);
+            cyc[3] += (unsigned long long)(clock64() - c0);
+            s_task = task;
+            s_flag = ok ? 1 : 0;
+        }
+        __syncthreads();
+        const uint2 task = s_task;
+        const bool ok = s_flag != 0;
+        __syncthreads();
+        if (!ok) break;
+        const uint32_t type = task.x >> T_SHIFT;
+        const int c = (int)(task.x & T_CMASK);
+        const long long c0 = clock64();
+        if (type == T_EVAL) {
+            eval_task(par, cands, ws, c, (int)task.y, (double*)smem_solve, s_slotj);
+            finish_stage_task<BLOCK>(ws, T_EVAL, c, &s_flag, &s_base);
+        } else if (type == T_HG) {
+            hg_task(par, cands, ws, c, (int)task.y, (double*)smem_solve);
+            finish_stage_task<BLOCK>(ws, T_HG, c, &s_flag, &s_base);
+        } else {
+            const sdsm_cand cd = cands[c];
+            const CInfo ci = ws.cinfo[c];
+            const bool solo = ci.n_ne <= args.solo_cells;
+            for (;;) {
+                const bool big = (ws.cstate[c].use_xi ? 6 + ci.m : 6) > SMALL_N_MAX;
+                Sm sm;
+                bool requested;
+                if (big) { carve_smem_big(sm, smem_solve); requested = ctrl_step<BLOCK, true>(par, img, cd, ci, ws, c, sm, out, args.trace); }
+                else { carve_smem(sm, smem_solve, args.lcap); requested = ctrl_step<BLOCK, false>(par, img, cd, ci, ws, c, sm, out, args.trace); }
+                if (!requested) {
+                    if (tid == 0) { __threadfence(); atomicAdd(ws.counters + Q_DONE, 1ull); }
+                    break;
+                }
+                const int n_tasks = (ci.n_ne + EVAL_WARPS - 1) / EVAL_WARPS;
+                if (!solo) {
+                    // publishing is the LAST thing a control task does: the candidate's next control task may start on another
+                    // SM as soon as the evaluations have finished
+                    if (tid == 0) ws.pending[c] = n_tasks;
+                    q_push_range<BLOCK>(ws, T_EVAL, (uint32_t)c, n_tasks, EVAL_WARPS, &s_base);
+                    break;
+                }
+                // the whole chain in this CTA: evaluate here and go on
+                const EvalReq rq = ws.req[c];
+                for (int k = 0; k < n_tasks; ++k) { eval_task(par, cands, ws, c, k * EVAL_WARPS, (double*)smem_solve, s_slotj); __syncthreads(); }
+                if (rq.want_h && rq.use_xi)
+                    for (int j = 0; j < ci.m; j += HG_WARPS) { hg_task(par, cands, ws, c, j, (double*)smem_solve); __syncthreads(); }
+            }
+        }
+        if (tid == 0) { cyc[type] += (unsigned long long)(clock64() - c0); cnt[type] += 1; }
+    }
+    if (tid == 0) {
+        atomicAdd(ws.counters + Q_CYC_CTRL, cyc[T_CTRL]); atomicAdd(ws.counters + Q_CYC_EVAL, cyc[T_EVAL]);
+        atomicAdd(ws.counters + Q_CYC_HG, cyc[T_HG]);     atomicAdd(ws.counters + Q_CYC_IDLE, cyc[3]);
+        atomicAdd(ws.counters + Q_N_CTRL, cnt[T_CTRL]);   atomicAdd(ws.counters + Q_N_EVAL, cnt[T_EVAL]);
+        atomicAdd(ws.counters + Q_N_HG, cnt[T_HG]);       atomicAdd(ws.counters + Q_CYC_TOTAL, (unsigned long long)(clock64() - c_begin));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// diagnostics for the parity tests (single candidate of the last solved batch; plain grid-stride kernels, no queue)
+
+// prepares the evaluation of F (with Hessian, unscaled) of candidate c at xin
+__global__ void __launch_bounds__(SOLVE_BLOCK)
+k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, const double* __restrict__ xin)
+{
+    const int tid = threadIdx.x;
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    Prob P;
+    setup_problem(P, par, cd, ci, ws);
+    const int N = P.N;
+    double* nx = P.V + (size_t)V_NX * P.ld;
+    int bad = 0;
+    for (int i = tid; i < N; i += SOLVE_BLOCK) { nx[i] = xin[i]; bad |= !isfinite(xin[i]); }
+    for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) P.H[i] = 0.0;
+    bad = __syncthreads_or(bad);
+    if (tid == 0) {
+        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = 1; rq.use_xi = P.m > 0 ? 1 : 0;
+        ws.req[c] = rq;
+        ws.cstate[c].pc = bad ? -1 : PC_DONE;
+    }
+}
+
+__global__ void __launch_bounds__(SOLVE_BLOCK)
+k_diag_eval_cells(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws)
+{
+    extern __shared__ __align__(16) char smem_solve[];
+    __shared__ int s_slotj[EVAL_WARPS * 32];
+    const int n_ne = ws.cinfo[c].n_ne;
+    for (int first = blockIdx.x * EVAL_WARPS; first < n_ne; first += gridDim.x * EVAL_WARPS) {
+        eval_task(par, cands, ws, c, first, (double*)smem_solve, s_slotj);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SOLVE_BLOCK)
+k_diag_eval_rows(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws)
+{
+    extern __shared__ __align__(16) char smem_solve[];
+    const int m = ws.cinfo[c].m;
+    for (int first = blockIdx.x * HG_WARPS; first < m; first += gridDim.x * HG_WARPS) {
+        hg_task(par, cands, ws, c, first, (double*)smem_solve);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SOLVE_BLOCK)
+k_diag_eval_end(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, double* value, double* grad, double* Hout, int lcap)
+{
+    extern __shared__ __align__(16) char smem_solve[];
+    Sm sm;
+    carve_smem(sm, smem_solve, lcap);
+    const int tid = threadIdx.x;
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    Prob P;
+    setup_problem(P, par, cd, ci, ws);
+    P.scale_cp = 1.0;
+    const int N = P.N;
+    double* g = P.V + (size_t)V_NG * P.ld;
+    const double* xe = P.V + (size_t)V_NX * P.ld;
+    double psi = 0;
+    double f;
+    if (ws.cstate[c].pc == -1) f = NAN;
+    else if (P.m > 0) f = gather_cells<SOLVE_BLOCK, true>(P, sm, xe, g, 1.0, &psi);
+    else f = gather_poly<SOLVE_BLOCK, true>(P, sm, g, 1.0, &psi);
+    __syncthreads();
+    if (tid == 0) *value = f;
+    for (int i = tid; i < N; i += SOLVE_BLOCK) grad[i] = g[i];
+    for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) Hout[i] = P.H[i];
+}
+
+// prepares one interior-point solve of candidate c from x0 (STG_TRACE): k_solve continues it at PC_IPMSTART and records
+// the iterates
+__global__ void __launch_bounds__(SOLVE_BLOCK)
+k_diag_trace_begin(Par par, const sdsm_cand* __restrict__ cands, int c, int use_xi_, WS ws, const double* __restrict__ x0)
+{
+    const int tid = threadIdx.x;
+    const sdsm_cand cd = cands[c];
+    const CInfo ci = ws.cinfo[c];
+    Prob P;
+    setup_problem(P, par, cd, ci, ws);
+    const int use_xi = (use_xi_ && P.m > 0) ? 1 : 0;
+    const int N = use_xi ? P.N : 6;
+    double* x = P.V + (size_t)V_X * P.ld;
+    for (int i = tid; i < N; i += SOLVE_BLOCK) x[i] = x0[i];
+    if (use_xi) for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) P.H[i] = 0.0;
+    __syncthreads();
+    if (tid == 0) {
+        CState S = ws.cstate[c];
+        S.use_xi = use_xi; S.stage = STG_TRACE; S.r_ipm = 0; S.pc = PC_TRACESTART;
+        ws.cstate[c] = S;
+    }
+}
+
+__global__ void k_diag_trace_end(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, double* xout, int32_t* status_iters)
+{
+    const sdsm_cand cd = cands[c];
+    const CState* S = ws.cstate + c;
+    const int ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
+    const int N = S->use_xi ? 6 + ws.cinfo[c].m : 6;
+    const double* x = ws.vecs + cd.vec_off + (size_t)V_X * ld;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) xout[i] = x[i];
+    if (threadIdx.x == 0) { status_iters[0] = S->r_ipm; status_iters[1] = S->iters; }
+}
+
+}  // namespace sdsm

@@ -1,6 +1,7 @@
 // C ABI of the superdsm_b200 library (see include/superdsm_b200.h).  Host side: argument checks, workspace layout,
 // kernel launches on the caller's stream.  No per-batch allocation, no synchronisation.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -10,6 +11,7 @@
 #include "grid.cuh"
 #include "eval.cuh"
 #include "ctrl.cuh"
+#include "sched.cuh"
 
 using namespace sdsm;
 
@@ -23,10 +25,11 @@ struct sdsm_ctx {
     size_t psf_cap = 0;
     int64_t launches = 0;
     // totals of the last plan (the layout is a pure function of these)
-    int64_t P = 0, C = 0, T = 0, V = 0, M = 0;
-    int32_t n_cand = 0, n_big = 0;
-    unsigned long long* h_flag = nullptr;   // pinned: size of the next work list, published by the device every few rounds
-    int64_t rounds = 0;                      // rounds of the last solve (diagnostics)
+    int64_t P = 0, C = 0, T = 0, V = 0, M = 0, K = 0;
+    int32_t n_cand = 0;
+    int solve_ctas_per_sm = 1;               // resident CTAs of k_solve per SM (occupancy query)
+    int solo_cells = 16;                     // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
+    double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
     std::string err;
 };
 
@@ -53,14 +56,15 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     CUDA_TRY(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     if (prop.major < 10) { ctx->err = "superdsm_b200 is built for sm_100a (B200) only"; return SDSM_E_UNSUPPORTED; }
-    const int ctrl_max = (int)ctrl_smem_bytes(SMEM_L_CAP);
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_eval, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EVAL_SMEM));
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_ctrl, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_ctrl_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BIG_SMEM));
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_begin, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_end, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
-    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_trace_begin, cudaFuncAttributeMaxDynamicSharedMemorySize, ctrl_max));
-    CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->h_flag, 64, cudaHostAllocDefault));
+    const int smem_max = (int)solve_smem_bytes(SMEM_L_CAP);
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_end, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->solve_ctas_per_sm, k_solve, SOLVE_BLOCK, (size_t)smem_max));
+    if (ctx->solve_ctas_per_sm < 1) { ctx->err = "k_solve does not fit on an SM"; return SDSM_E_UNSUPPORTED; }
+    if (const char* e = getenv("SDSM_SOLO_CELLS")) ctx->solo_cells = atoi(e);
+    if (const char* e = getenv("SDSM_TIMEOUT_S")) ctx->timeout_s = atof(e);
     return SDSM_OK;
 }
 
@@ -69,14 +73,12 @@ extern "C" void sdsm_destroy(sdsm_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->d_psf) cudaFree(ctx->d_psf);
-    if (ctx->h_flag) cudaFreeHost(ctx->h_flag);
     delete ctx;
 }
 
 extern "C" const char* sdsm_last_error(const sdsm_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
 extern "C" int64_t sdsm_launch_count(const sdsm_ctx* ctx) { return ctx ? ctx->launches : 0; }
-extern "C" int64_t sdsm_round_count(const sdsm_ctx* ctx) { return ctx ? ctx->rounds : 0; }
 
 extern "C" int sdsm_set_image(sdsm_ctx* ctx, const double* d_y, const int32_t* d_atoms, int32_t H, int32_t W)
 {
@@ -133,8 +135,8 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
     if (!ctx || !cands || !plan || n_cand < 1) return SDSM_E_ARG;
     if (!ctx->have_par || !ctx->img.y) { ctx->err = "sdsm_set_image / sdsm_set_params must precede sdsm_plan_batch"; return SDSM_E_ARG; }
     const int sub = ctx->par.sub;
-    int64_t P = 0, C = 0, T = 0, V = 0, M = 0, PAR = 0, FG = 0;
-    int32_t n_max = 6, cells_max = 1, n_big = 0;
+    int64_t P = 0, C = 0, T = 0, V = 0, M = 0, PAR = 0, FG = 0, K = 0;
+    int32_t n_max = 6, cells_max = 1;
     for (int32_t i = 0; i < n_cand; ++i) {
         sdsm_cand& c = cands[i];
         if (c.h < 1 || c.w < 1 || c.n < 1 || c.r0 < 0 || c.c0 < 0 || c.r0 + c.h > ctx->img.H || c.c0 + c.w > ctx->img.W || c.fp_len < 1) {
@@ -151,82 +153,46 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
         c.fg_off = FG;  FG += (int64_t)c.h * c.w;
         c.vec_off = V;  V += (int64_t)NVEC * ld;
         c.mat_off = M;  M += 3 * ld * ld;
-        if (ld > SMALL_N_MAX) ++n_big;
+        K += 1 + (cap + EVAL_WARPS - 1) / EVAL_WARPS;     // tasks of the candidate that can be queued at the same time
         if (ld > n_max) n_max = (int32_t)ld;
         if (cap > cells_max) cells_max = cap;
     }
-    const Layout L = make_layout(P, C, T, V, M, n_cand);
+    const Layout L = make_layout(P, C, T, V, M, K, n_cand);
     plan->workspace_bytes = L.total;
     plan->params_len = PAR;
     plan->fgmask_len = FG;
     plan->n_max = n_max;
     plan->cells_max = cells_max;
-    plan->reserved0 = n_big;
+    plan->reserved0 = 0;
     plan->reserved1 = 0;
-    ctx->n_big = n_big;
-    ctx->P = P; ctx->C = C; ctx->T = T; ctx->V = V; ctx->M = M; ctx->n_cand = n_cand;
+    ctx->P = P; ctx->C = C; ctx->T = T; ctx->V = V; ctx->M = M; ctx->K = K; ctx->n_cand = n_cand;
     return SDSM_OK;
 }
 
 static int check_plan(sdsm_ctx* ctx, int32_t n_cand, size_t workspace_bytes, Layout* L)
 {
     if (n_cand != ctx->n_cand) { ctx->err = "batch does not match the last sdsm_plan_batch"; return SDSM_E_ARG; }
-    *L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, n_cand);
+    *L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, n_cand);
     if (L->total > workspace_bytes) { ctx->err = "workspace too small"; return SDSM_E_WORKSPACE; }
     return SDSM_OK;
 }
 
-// Drives the lock-step rounds k_eval -> k_hgather -> k_ctrl / k_ctrl_big until no candidate is live.  `parity` names the
-// work list that is ready.  The sizes of the next work lists are published to pinned memory every few rounds; the host
-// only waits on that.
-struct Bounds { int64_t live_small, live_big, items, hitems; };
-
-static int run_rounds(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_cands, const WS& ws, const sdsm_out& out, int lcap,
-                      Bounds bd, int parity, double* trace, int unit_scale)
+// Seeds the task queue with the control tasks that start `n_first` candidates (order, or the single candidate `single`)
+// and launches the persistent solver: one grid of resident CTAs that runs until every seeded candidate has finished.
+static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_cands, const WS& ws, const sdsm_out& out, int lcap,
+                      const int32_t* d_order, int n_first, int single, double* trace)
 {
-    const size_t csmem = ctrl_smem_bytes(lcap);
-    const int max_rounds = 64 * (ctx->par.maxiters + 2) * 3;
-    const int64_t g_max = (int64_t)ctx->sm_count * 16;
-    int round = 0;
-    int burst = 4;
-    while (true) {
-        for (int b = 0; b < burst; ++b, ++round) {
-            int64_t ge = (bd.items + EVAL_WARPS - 1) / EVAL_WARPS;
-            if (ge > g_max) ge = g_max;
-            if (ge < 1) ge = 1;
-            k_eval<<<(unsigned)ge, EVAL_BLOCK, EVAL_SMEM, stream>>>(ctx->par, d_cands, ws, parity);
-            ctx->launches++;
-            if (bd.hitems > 0) {
-                int64_t gh = (bd.hitems + HG_BLOCK / 32 - 1) / (HG_BLOCK / 32);
-                if (gh > g_max) gh = g_max;
-                k_hgather<<<(unsigned)gh, HG_BLOCK, 0, stream>>>(ctx->par, d_cands, ws, parity, unit_scale);
-                ctx->launches++;
-            }
-            if (bd.live_big > 0) {
-                k_ctrl_big<<<(unsigned)bd.live_big, BIG_BLOCK, BIG_SMEM, stream>>>(ctx->img, ctx->par, d_cands, ws, out, parity, trace);
-                ctx->launches++;
-            }
-            if (bd.live_small > 0) {
-                k_ctrl<<<(unsigned)bd.live_small, CTRL_BLOCK, csmem, stream>>>(ctx->img, ctx->par, d_cands, nullptr, 0, ws, out, parity, lcap, trace);
-                ctx->launches++;
-            }
-            parity ^= 1;
-        }
-        k_publish<<<1, 1, 0, stream>>>(ws, parity, ctx->h_flag);
-        ctx->launches++;
-        CUDA_TRY(ctx, cudaStreamSynchronize(stream));
-        const unsigned long long f0 = ((volatile unsigned long long*)ctx->h_flag)[0], f2 = ((volatile unsigned long long*)ctx->h_flag)[1];
-        Bounds nb{(int64_t)(f0 >> 32), (int64_t)(f2 >> 32), (int64_t)(f0 & 0xffffffffull), (int64_t)(f2 & 0xffffffffull)};
-        if (nb.live_small + nb.live_big == 0) break;
-        // the live set only shrinks; a candidate can change class (small -> big) once, when its DSM stage begins
-        if (nb.live_small > bd.live_small || nb.items > bd.items) { ctx->err = "work list grew: internal error"; return SDSM_E_CUDA; }
-        bd.live_big = nb.live_small + nb.live_big < bd.live_big ? nb.live_small + nb.live_big : bd.live_big;
-        bd.live_small = nb.live_small;
-        bd.items = nb.items;
-        if (round > max_rounds) { ctx->err = "solver did not terminate within the round limit"; return SDSM_E_CUDA; }
-        if (burst < 8) burst *= 2;
-    }
-    ctx->rounds = round;
+    k_seed<<<64, 256, 0, stream>>>(ws, d_order, n_first, single);
+    SolveArgs args{};
+    args.n_target = n_first;
+    args.lcap = lcap;
+    args.solo_cells = ctx->solo_cells;
+    args.timeout_ns = (unsigned long long)(ctx->timeout_s * 1e9);
+    args.trace = trace;
+    const int grid = ctx->sm_count * ctx->solve_ctas_per_sm;
+    k_solve<<<grid, SOLVE_BLOCK, solve_smem_bytes(lcap), stream>>>(ctx->img, ctx->par, d_cands, ws, out, args);
+    ctx->launches += 2;
+    CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
 }
 
@@ -242,7 +208,6 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     WS ws = make_ws(d_workspace, L);
-    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
     CUDA_TRY(ctx, cudaMemsetAsync(ws.cstate, 0, sizeof(CState) * (size_t)n_cand, stream));
     CUDA_TRY(ctx, cudaMemsetAsync(out->d_fgmask, 0, (size_t)plan->fgmask_len, stream));
 
@@ -257,14 +222,7 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
         ctx->launches++;
     }
     const int lcap = ctrl_lcap(plan->n_max);
-    // round 0: every candidate starts (work list 0 receives the first requests)
-    k_ctrl<<<n_cand, CTRL_BLOCK, ctrl_smem_bytes(lcap), stream>>>(ctx->img, ctx->par, d_cands, d_order, n_cand, ws, *out, 1, lcap, nullptr);
-    ctx->launches++;
-    CUDA_TRY(ctx, cudaGetLastError());
-    {
-        const Bounds bd{n_cand, ctx->n_big, ctx->C, ctx->par.has_smooth ? ctx->C : 0};
-        rc = run_rounds(ctx, stream, d_cands, ws, *out, lcap, bd, 0, nullptr, 0);
-    }
+    rc = run_solver(ctx, stream, d_cands, ws, *out, lcap, d_order, n_cand, 0, nullptr);
     if (rc) return rc;
     const int fin_grid = n_cand < 16 * ctx->sm_count ? n_cand : 16 * ctx->sm_count;
     k_finish<<<fin_grid, FIN_BLOCK, 0, stream>>>(ctx->img, ctx->par, d_cands, n_cand, ws, *out);
@@ -277,17 +235,16 @@ extern "C" int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const s
                                    double* d_value, double* d_grad, double* d_H, void* d_workspace, void* stream_)
 {
     if (!ctx || !plan || !d_cands || !d_x || !d_value || !d_grad || !d_H || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->n_cand);
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
     WS ws = make_ws(d_workspace, L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const int lcap = ctrl_lcap(plan->n_max);
-    const size_t csmem = ctrl_smem_bytes(lcap);
-    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
-    k_diag_eval_begin<<<1, CTRL_BLOCK, csmem, stream>>>(ctx->par, d_cands, c, ws, d_x, 1, lcap);
-    k_eval<<<ctx->sm_count, EVAL_BLOCK, EVAL_SMEM, stream>>>(ctx->par, d_cands, ws, 0);
-    if (ctx->par.has_smooth) { k_hgather<<<ctx->sm_count, HG_BLOCK, 0, stream>>>(ctx->par, d_cands, ws, 0, 1); ctx->launches++; }
-    k_diag_eval_end<<<1, CTRL_BLOCK, csmem, stream>>>(ctx->par, d_cands, c, ws, d_value, d_grad, d_H, lcap);
+    const size_t smem = solve_smem_bytes(lcap);
+    k_diag_eval_begin<<<1, SOLVE_BLOCK, 0, stream>>>(ctx->par, d_cands, c, ws, d_x);
+    k_diag_eval_cells<<<ctx->sm_count, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, c, ws);
+    if (ctx->par.has_smooth) { k_diag_eval_rows<<<ctx->sm_count, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, c, ws); ctx->launches++; }
+    k_diag_eval_end<<<1, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, c, ws, d_value, d_grad, d_H, lcap);
     ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
@@ -297,7 +254,7 @@ extern "C" int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sd
                                   int32_t* d_cols, float* d_vals, uint32_t* d_grid, void* d_workspace, void* stream_)
 {
     if (!ctx || !plan || !d_cands || !d_rc || !d_cols || !d_vals || !d_grid || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->n_cand);
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
     WS ws = make_ws(d_workspace, L);
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     k_export<<<64, 128, 0, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, ws, d_rc, d_cols, d_vals, d_grid);
@@ -310,17 +267,15 @@ extern "C" int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
                                 const double* d_x0, double* d_trace, double* d_xout, int32_t* d_status_iters, void* d_workspace, void* stream_)
 {
     if (!ctx || !plan || !d_cands || !d_x0 || !d_trace || !d_xout || !d_status_iters || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->n_cand);
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
     WS ws = make_ws(d_workspace, L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const int lcap = ctrl_lcap(plan->n_max);
-    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
-    k_diag_trace_begin<<<1, CTRL_BLOCK, ctrl_smem_bytes(lcap), stream>>>(ctx->par, d_cands, c, use_xi, ws, d_x0, 1, lcap);
+    k_diag_trace_begin<<<1, SOLVE_BLOCK, 0, stream>>>(ctx->par, d_cands, c, use_xi, ws, d_x0);
     ctx->launches++;
     sdsm_out none{};   // STG_TRACE never writes results
-    const Bounds bd{1, 1, ctx->C, ctx->par.has_smooth ? ctx->C : 0};
-    int rc = run_rounds(ctx, stream, d_cands, ws, none, lcap, bd, 0, d_trace, 0);
+    int rc = run_solver(ctx, stream, d_cands, ws, none, lcap, nullptr, 1, c, d_trace);
     if (rc) return rc;
     k_diag_trace_end<<<1, 128, 0, stream>>>(ctx->par, d_cands, c, ws, d_xout, d_status_iters);
     ctx->launches++;
@@ -337,5 +292,17 @@ extern "C" int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, i
     ctx->launches++;
     *flops = (int64_t)blocks * 256 * 8 * 2 * (int64_t)iters;
     CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_t* h_stats, void* stream_)
+{
+    if (!ctx || !d_workspace || !h_stats) return SDSM_E_ARG;
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    WS ws = make_ws(const_cast<void*>(d_workspace), L);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_stats, ws.counters, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(stream));
     return SDSM_OK;
 }

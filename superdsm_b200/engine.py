@@ -158,9 +158,21 @@ class Engine(object):
     def launch_count(self):
         return int(self.lib.sdsm_launch_count(self.ctx))
 
-    @property
-    def round_count(self):
-        return int(self.lib.sdsm_round_count(self.ctx))
+    STAT_NAMES = ('q_head', 'q_tail', 'done', 'abort', 'cyc_eval', 'cyc_hrows', 'cyc_ctrl', 'cyc_idle', 'n_eval', 'n_hrows',
+                  'n_ctrl', 'cyc_total')
+
+    def solver_stats(self, ws=None):
+        """Counters of the persistent solver kernel of the last batch (synchronises): see ``sdsm_solver_stats``."""
+        if ws is None: ws = self._last[2]
+        st = np.zeros(16, dtype=np.uint64)
+        self._check(self.lib.sdsm_solver_stats(self.ctx, ws.data_ptr(), st.ctypes.data, self.stream.cuda_stream))
+        return {k: int(st[i]) for i, k in enumerate(self.STAT_NAMES)}
+
+    def _check_solved(self, ws, n):
+        """Raises if the watchdog of the persistent solver fired or a candidate did not finish."""
+        st = self.solver_stats(ws)
+        if st['abort'] or st['done'] != n:
+            raise SolverError(f"persistent solver did not finish: {st['done']} of {n} candidates done, abort={st['abort']}")
 
     # -- buffers -------------------------------------------------------------------------------------------------
 
@@ -263,7 +275,7 @@ class Engine(object):
                 h[:v].copy_(dev[k][:v], non_blocking=True)
                 host[k] = h
                 self.d2h_bytes += v
-        self.stream.synchronize()
+        self._check_solved(ws, n)
         res = BatchResult(cands,
                           host['energy'][:sizes['energy']].numpy().view(np.float64).copy(),
                           host['status'][:sizes['status']].numpy().view(np.int32).copy(),
