@@ -124,7 +124,8 @@ int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_ca
                      void* d_workspace, size_t workspace_bytes, const sdsm_out* out, void* stream);
 
 /* Diagnostics for the parity tests: evaluates psi, grad psi and the lower triangle of the Hessian of candidate c of the
- * LAST solved batch (same workspace, still intact) at the given parameters; d_H is N x N row-major, N = 6 + m. */
+ * LAST solved batch (same workspace, still intact) at the given parameters; d_H is N x N row-major, N = 6 + m.
+ * d_H = NULL evaluates value and gradient only (the evaluation the line searches use). */
 int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, const double* d_x,
                         double* d_value, double* d_grad, double* d_H, void* d_workspace, void* stream);
 
@@ -142,6 +143,12 @@ int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_ca
 /* Measurement aid: enqueues a register-resident FP64 FMA loop on every SM (8 CTAs of 256 threads per SM, 8 independent
  * chains per thread); *flops receives the floating-point operations of the launch.  Time it with CUDA events. */
 int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flops, void* stream);
+
+/* Measurement aid: `repeats` sweeps of the evaluation tasks (rows = 0; value + gradient, plus the per-cell Hessians if
+ * want_h) or of the Hessian-row tasks (rows = 1) over EVERY candidate of the last solved batch at its solution, outside
+ * the solver: the streaming pass the HBM / FP64 roofline of the energy kernels is quoted on.  Time it with CUDA events. */
+int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t n_cand, int32_t want_h,
+                    int32_t rows, int32_t repeats, void* d_workspace, void* stream);
 
 /* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
 int64_t sdsm_launch_count(const sdsm_ctx* ctx);

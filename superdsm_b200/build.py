@@ -15,10 +15,13 @@ def needs_build():
     return any(os.path.getmtime(src) > built for src in SOURCES + [HEADER])
 
 
+# -fmad=false: floating-point contraction is never left to the compiler (multiply-adds that should fuse are written as
+# fma()): two evaluations of the energy at the same point are then bit-identical whatever code surrounds them, which the
+# line searches of the solver rely on (csrc/eval.cuh).
 def build(force=False, verbose=False):
     if not force and not needs_build(): return LIB_PATH
     nvcc = os.environ.get('NVCC', 'nvcc')
-    cmd = [nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
+    cmd = [nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-fmad=false',
            '-Xcompiler', '-fPIC', '-shared', '-o', LIB_PATH, SOURCES[0]]
     if verbose: cmd[1:1] = ['-Xptxas', '-v']
     res = subprocess.run(cmd, capture_output=True, text=True)

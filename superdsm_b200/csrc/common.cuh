@@ -12,11 +12,13 @@ constexpr int NC         = 2;
 constexpr int LOCAL_MAX  = 32;    // 6 polynomial + 25 slots, padded
 constexpr int SCRH       = 496;   // packed lower triangle of a 31 x 31 local Hessian
 constexpr int SCRG       = 32;    // local gradient (31) + value
-constexpr int TILE_LD    = 34;    // row stride (doubles) of the per-warp pixel tile: conflict-free 128-bit rows
+constexpr int TILE_LD    = 36;    // row stride (doubles) of the per-warp tile T[local parameter][pixel of the chunk]: = 4 mod 16, so that
+                                  // both the column writes (lane = pixel) and the DMMA fragment reads are bank-conflict free
 constexpr int SOLVE_BLOCK = 256;  // k_solve: persistent CTAs, every task is executed by one CTA
 constexpr int EVAL_BLOCK = SOLVE_BLOCK;   // evaluation task: one warp per pixel cell
 constexpr int EVAL_WARPS = EVAL_BLOCK / 32;
-constexpr int TILE_DOUBLES = 32 * TILE_LD + 64;                 // tile + u[32] + dd[32]
+constexpr int EVAL_CELLS = 32;    // non-empty pixel cells per evaluation task: the CTA's warps take them one by one
+constexpr int TILE_DOUBLES = 32 * TILE_LD + 64;                 // tile + dd[32] + xi[32]
 constexpr int CTRL_BLOCK = SOLVE_BLOCK;   // control task: one CTA advances one candidate's state machine
 constexpr int CTRL_WARPS = CTRL_BLOCK / 32;
 constexpr int SMEM_L_CAP = 5504;  // doubles of shared memory for the packed Cholesky factor (N <= 104)

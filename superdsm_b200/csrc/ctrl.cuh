@@ -11,6 +11,7 @@
 namespace sdsm {
 
 constexpr int MAX_RELAXED = 8;
+constexpr int EVAL_BUDGET = 50000;   // evaluations of F per candidate (a regular solve needs < 4000: 100 iterations, few trials each)
 constexpr double CP_STEP = 0.99, CP_BETA = 0.5, CP_ALPHA = 0.01;
 
 enum { V_X = 0, V_G, V_DX, V_T, V_NX, V_NG, V_SX, V_SDX, V_RD, V_X0, V_E, V_W };
@@ -292,7 +293,7 @@ __device__ bool cholesky(const double* H, int N, double* L, Sm& sm)
         for (int i = k + 1 + warp; i < N; i += NW) {
             const double lik = L[tri(i, k)];
             double* row = L + tri(i, 0);
-            for (int j = k + 1 + lane; j <= i; j += 32) row[j] -= lik * L[tri(j, k)];
+            for (int j = k + 1 + lane; j <= i; j += 32) row[j] = fma(-lik, L[tri(j, k)], row[j]);
         }
         __syncthreads();
     }
@@ -306,7 +307,7 @@ __device__ void chol_solve_warp(const double* L, int N, double* b)
     for (int k = 0; k < N; ++k) {
         const double yk = b[k] * L[tri(k, k)];
         __syncwarp();
-        for (int i = k + 1 + lane; i < N; i += 32) b[i] -= L[tri(i, k)] * yk;
+        for (int i = k + 1 + lane; i < N; i += 32) b[i] = fma(-L[tri(i, k)], yk, b[i]);
         if (lane == 0) b[k] = yk;
         __syncwarp();
     }
@@ -314,7 +315,7 @@ __device__ void chol_solve_warp(const double* L, int N, double* b)
         const double xk = b[k] * L[tri(k, k)];
         __syncwarp();
         const double* row = L + tri(k, 0);
-        for (int i = lane; i < k; i += 32) b[i] -= row[i] * xk;
+        for (int i = lane; i < k; i += 32) b[i] = fma(-row[i], xk, b[i]);
         if (lane == 0) b[k] = xk;
         __syncwarp();
     }
@@ -389,7 +390,7 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
                 __syncwarp();
                 if (lane > cc && lane < kw) {
                     const double l = sb.D[lane * CB_LD + cc];
-                    for (int j = cc + 1; j <= lane; ++j) sb.D[lane * CB_LD + j] -= l * sb.D[j * CB_LD + cc];
+                    for (int j = cc + 1; j <= lane; ++j) sb.D[lane * CB_LD + j] = fma(-l, sb.D[j * CB_LD + cc], sb.D[lane * CB_LD + j]);
                 }
                 __syncwarp();
             }
@@ -410,7 +411,7 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
                 if (q < kw) {
                     double v = r[q];
 #pragma unroll
-                    for (int p = 0; p < q; ++p) v -= r[p] * sb.D[q * CB_LD + p];
+                    for (int p = 0; p < q; ++p) v = fma(-r[p], sb.D[q * CB_LD + p], v);
                     r[q] = v * sb.D[q * CB_LD + q];
                 }
             }
@@ -441,7 +442,7 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
                 for (int cc = 0; cc < cmax; ++cc) {
                     double a = 0;
 #pragma unroll
-                    for (int q = 0; q < CB; ++q) a += xv[q] * sb.Xj[cc * CB_LD + q];
+                    for (int q = 0; q < CB; ++q) a = fma(xv[q], sb.Xj[cc * CB_LD + q], a);
                     out[cc] -= a;
                 }
             }
@@ -468,7 +469,7 @@ __device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
             for (int cc = 0; cc < kw; ++cc) {
                 const double yk = __shfl_sync(0xffffffffu, b, cc) * sb.D[cc * CB_LD + cc];
                 if (lane == cc) b = yk;
-                else if (lane > cc && lane < kw) b -= sb.D[lane * CB_LD + cc] * yk;
+                else if (lane > cc && lane < kw) b = fma(-sb.D[lane * CB_LD + cc], yk, b);
             }
             if (lane < kw) { v[k0 + lane] = b; sb.yv[lane] = b; }
         }
@@ -476,7 +477,7 @@ __device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
         for (int i = k0 + kw + tid; i < N; i += BLOCK) {
             const double* ar = A + (size_t)i * N + k0;
             double a = 0;
-            for (int q = 0; q < kw; ++q) a += ar[q] * sb.yv[q];
+            for (int q = 0; q < kw; ++q) a = fma(ar[q], sb.yv[q], a);
             v[i] -= a;
         }
         __syncthreads();
@@ -491,14 +492,14 @@ __device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
             for (int cc = kw - 1; cc >= 0; --cc) {
                 const double xk = __shfl_sync(0xffffffffu, b, cc) * sb.D[cc * CB_LD + cc];
                 if (lane == cc) b = xk;
-                else if (lane < cc) b -= sb.D[cc * CB_LD + lane] * xk;
+                else if (lane < cc) b = fma(-sb.D[cc * CB_LD + lane], xk, b);
             }
             if (lane < kw) { v[k0 + lane] = b; sb.yv[lane] = b; }
         }
         __syncthreads();
         for (int i = tid; i < k0; i += BLOCK) {
             double a = 0;
-            for (int q = 0; q < kw; ++q) a += A[(size_t)(k0 + q) * N + i] * sb.yv[q];
+            for (int q = 0; q < kw; ++q) a = fma(A[(size_t)(k0 + q) * N + i], sb.yv[q], a);
             v[i] -= a;
         }
         __syncthreads();
@@ -509,7 +510,7 @@ template <int BLOCK>
 __device__ double bdot(const double* a, const double* b, int N, Sm& sm)
 {
     double s = 0;
-    for (int i = threadIdx.x; i < N; i += BLOCK) s += a[i] * b[i];
+    for (int i = threadIdx.x; i < N; i += BLOCK) s = fma(a[i], b[i], s);
     return block_sum1<BLOCK>(s, sm.red_part, sm.red_out);
 }
 
@@ -585,7 +586,7 @@ __device__ __forceinline__ void ipm_begin(CState& S)
 // Prepares the evaluation of F at vector `vec`: records the request in S (it is published by publish_request when the control
 // task ends).  Returns false, recording nothing, if the point is not finite (the reference's Energy would raise on NaN).
 template <int BLOCK>
-__device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int want_h)
+__device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int want_h, bool budgeted)
 {
     const int tid = threadIdx.x;
     const int N = S.use_xi ? P.N : 6;
@@ -593,6 +594,9 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
     int bad = 0;
     for (int i = tid; i < N; i += BLOCK) bad |= !isfinite(x[i]);
     if (__syncthreads_or(bad)) return false;
+    // A solve whose line search never terminates (NaN merit values) runs into the reference's SIGALRM time-out
+    // (dsm.py:483-489, cp_timeout = 300 s) and raises; here the evaluation budget plays that role.
+    if (budgeted && S.nf + S.nh >= EVAL_BUDGET) return false;
     S.req_vec = vec; S.req_gvec = gvec; S.req_h = want_h;
     if (want_h) S.nh += 1; else S.nf += 1;                      // evaluation counters (reported in out.info)
     return true;
@@ -632,7 +636,7 @@ __device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sds
 
 #define REQUEST(vec_, gvec_, h_, next_, onbad_)                                                       \
     do {                                                                                              \
-        if (prepare_request<BLOCK>(P, S, vec_, gvec_, h_)) { S.pc = next_; yield = true; requested = true; } \
+        if (prepare_request<BLOCK>(P, S, vec_, gvec_, h_, (next_) == PC_TOP || (next_) == PC_TRIAL || (next_) == PC_RESTORED)) { S.pc = next_; yield = true; requested = true; } \
         else { onbad_; }                                                                              \
     } while (0)
 
@@ -747,7 +751,7 @@ __device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sds
                 for (int i = warp; i < Nc; i += NW) {
                     double a = 0;
                     const double* hr = Hres + (size_t)i * Nc;
-                    for (int j = lane; j < Nc; j += 32) a += hr[j] * tv[j];
+                    for (int j = lane; j < Nc; j += 32) a = fma(hr[j], tv[j], a);
                     a = warp_sum(a);
                     if (lane == 0) { const double vx = -(z * g[i]) - a - gres[i] * wz3; ev[i] = vx + g[i] * vt; }
                 }

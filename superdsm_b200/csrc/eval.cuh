@@ -2,10 +2,10 @@
 // non-empty pixel cell of one candidate; a warp owns an item, a task (sched.cuh) is EVAL_WARPS consecutive items.
 //
 // All pixels of a subsample x subsample cell see the same <= 25 grid points, so a cell has a dense local parameter vector
-// of length L = 6 + #active slots.  Per chunk of 32 pixels each lane builds its pixel's local row into a shared-memory
-// tile, then the lanes switch roles and own outputs: lane e accumulates local gradient entry e, and 4x4 register blocks
-// of the local Hessian.  Local results go to the cell's scratch (scrG / scrH); k_ctrl gathers them into the candidate's
-// value / gradient / Hessian in a fixed order -- no floating-point atomics, bit-reproducible whatever the schedule.
+// of length L = 6 + #active slots (<= 31).  A warp owns a cell, a lane a pixel: value and local gradient accumulate in
+// registers; the local Hessian (a 32-pixel rank update per chunk) runs on the FP64 tensor cores (DMMA.8x8x4) from a
+// shared-memory tile.  Local results go to the cell's scratch (scrG / scrH); the control task gathers them into the
+// candidate's value / gradient / Hessian in a fixed order -- no floating-point atomics, bit-reproducible whatever the schedule.
 #pragma once
 #include "common.cuh"
 
@@ -34,6 +34,50 @@ __device__ __forceinline__ int nth_set_bit(uint32_t mask, int n)
     return __ffs(mask) - 1;
 }
 
+// Sum over the warp of 32 per-lane values at once: on return lane l holds (in the return value) the warp total of v[l].
+// 31 shuffles instead of 160; fixed order, so results do not depend on scheduling.  (Template recursion: every index is a
+// compile-time constant, so v stays in registers.)
+template <int O>
+__device__ __forceinline__ void warp_sum_transposed_step(double (&v)[32], int lane)
+{
+    const bool up = (lane & O) != 0;
+#pragma unroll
+    for (int k = 0; k < O; ++k) {
+        const double send = up ? v[k] : v[k + O];
+        const double recv = __shfl_xor_sync(0xffffffffu, send, O);
+        v[k] = (up ? v[k + O] : v[k]) + recv;
+    }
+    if constexpr (O > 1) warp_sum_transposed_step<O / 2>(v, lane);
+}
+
+__device__ __forceinline__ double warp_sum_transposed(double (&v)[32])
+{
+    warp_sum_transposed_step<16>(v, threadIdx.x & 31);
+    return v[0];
+}
+
+// D (8 x 8) += A (8 x 4) B (4 x 8) in fp64 on the tensor cores: DMMA.8x8x4.  Fragments: a = A[lane / 4][lane % 4],
+// b = B[lane % 4][lane / 4], c0 / c1 = C[lane / 4][2 (lane % 4) + 0 / 1].
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// a load the compiler may not merge with an earlier load of the same address
+__device__ __forceinline__ float ldg_again(const float* p)
+{
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ double cell_S(const double (&th)[6], double x1, double x2)
+{
+    // explicit fma: the value must not depend on how the compiler contracts the expression in a given context
+    const double r1 = fma(x1, th[0], x2 * th[2]), r2 = fma(x1, th[2], x2 * th[1]), r3 = fma(x1, th[3], x2 * th[4]);
+    return fma(r1, x1, fma(r2, x2, fma(2.0, r3, th[5])));
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // polynomial-only model (6 parameters): each lane keeps its pixels' sums in registers, one warp reduction per cell.
 // scrG[0..5] = gradient, scrG[31] = value, scrH[0..20] = packed lower triangle of the 6 x 6 block.
@@ -44,22 +88,21 @@ __device__ __forceinline__ void eval_cell_poly(const double* __restrict__ py, co
                                                double tol, double* sg, double* sh)
 {
     const int lane = threadIdx.x & 31;
-    const double a1 = x[0], a2 = x[1], a3 = x[2], b1 = x[3], b2 = x[4], c0 = x[5];
-    constexpr int K = HESS ? 28 : 7;
-    double acc[K];
+    const double th[6] = {x[0], x[1], x[2], x[3], x[4], x[5]};
+    double acc[32];
 #pragma unroll
-    for (int k = 0; k < K; ++k) acc[k] = 0;
+    for (int k = 0; k < 32; ++k) acc[k] = 0;
     for (int i = lane; i < npix; i += 32) {
         const uint32_t rc = prc[i];
         const double x1 = xr[rc & 0xffffu], x2 = xc[rc >> 16], y = py[i];
-        const double S = (x1 * a1 + x2 * a3) * x1 + (x1 * a3 + x2 * a2) * x2 + 2 * (x1 * b1 + x2 * b2) + c0;
+        const double S = cell_S(th, x1, x2);
         double phi, theta;
         logistic(y, S, phi, theta);
         const double u = -y * theta;
         const double q[6] = {x1 * x1, x2 * x2, 2 * (x1 * x2), 2 * x1, 2 * x2, 1.0};
-        acc[0] += phi;
+        acc[31] += phi;
 #pragma unroll
-        for (int k = 0; k < 6; ++k) acc[1 + k] += u * q[k];
+        for (int k = 0; k < 6; ++k) acc[k] = fma(u, q[k], acc[k]);
         if (HESS) {
             double kappa = theta - theta * theta;
             if (kappa < tol) kappa = 0;
@@ -68,25 +111,145 @@ __device__ __forceinline__ void eval_cell_poly(const double* __restrict__ py, co
             for (int a = 0; a < 6; ++a) {
                 const double da = dd * q[a];
 #pragma unroll
-                for (int b = 0; b <= a; ++b) acc[7 + a * (a + 1) / 2 + b] += da * q[b];
+                for (int b = 0; b <= a; ++b) acc[6 + a * (a + 1) / 2 + b] = fma(da, q[b], acc[6 + a * (a + 1) / 2 + b]);
             }
         }
     }
-#pragma unroll
-    for (int k = 0; k < K; ++k) acc[k] = warp_sum(acc[k]);
-    if (lane == 0) {
-        sg[31] = acc[0];
-#pragma unroll
-        for (int k = 0; k < 6; ++k) sg[k] = acc[1 + k];
-        if (HESS) {
-#pragma unroll
-            for (int k = 0; k < 21; ++k) sh[k] = acc[7 + k];
-        }
-    }
+    const double tot = warp_sum_transposed(acc);     // lane: 0..5 gradient, 6..26 Hessian, 31 value
+    if (lane < 6 || lane == 31) sg[lane] = tot;
+    if (HESS && lane >= 6 && lane < 27) sh[lane - 6] = tot;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// deformable model: warp per cell, shared-memory tile of local rows
+// deformable model: warp per cell, lane per pixel.
+//
+// cell_value_grad: value and local gradient accumulate in registers, one transposed warp reduction per cell.  The line
+// searches of cp compare merit values of evaluations WITH and WITHOUT Hessian at (eventually) the same point and only
+// terminate when they are equal, as they are in the reference where both come from the same numpy code; so both kinds of
+// evaluation call this one function, and every multiply-add in it is an explicit fma (no context-dependent contraction).
+//
+// cell_hessian: the local Hessian  sum_p dd_p row_p row_p^T: the lanes stage their rows in a shared-memory tile
+// T[parameter][pixel] and the warp multiplies the 8 x 8 output tiles of the lower triangle on the FP64 tensor cores.
+
+__device__ __forceinline__ void cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
+                                             int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
+                                             const double* x, double tol, const double* XI, double* sg)
+{
+    const int lane = threadIdx.x & 31;
+    const double th[6] = {x[0], x[1], x[2], x[3], x[4], x[5]};
+    const int L = 6 + na;
+    double acc[32];                                   // acc[e] = local gradient entry e, acc[31] = value
+#pragma unroll
+    for (int k = 0; k < 32; ++k) acc[k] = 0;
+    for (int p0 = 0; p0 < npix; p0 += 32) {
+        const int p = p0 + lane;
+        const bool act = p < npix;
+        // The row of G~ is read twice (second time from L1) instead of being kept in 25 registers across the logistic
+        // function: with the 32 accumulators that would not fit the 128 registers two resident CTAs per SM allow.
+        const float* gp = gcell + (act ? p : 0);
+        double y = 0, x1 = 0, x2 = 0;
+        if (act) {
+            const uint32_t rc = prc[p];
+            x1 = xr[rc & 0xffffu];
+            x2 = xc[rc >> 16];
+            y = py[p];
+        }
+        double S = cell_S(th, x1, x2);
+        double sx0 = 0, sx1 = 0;
+#pragma unroll
+        for (int a = 0; a < NSLOT; a += 2) {
+            if (a < na) sx0 = fma((double)gp[(size_t)a * npix], XI[a], sx0);
+            if (a + 1 < NSLOT && a + 1 < na) sx1 = fma((double)gp[(size_t)(a + 1) * npix], XI[a + 1], sx1);
+        }
+        S += sx0 + sx1;
+        double phi = 0, theta = 0;
+        if (act) logistic(y, S, phi, theta);
+        const double u = -y * theta;                  // 0 for the lanes beyond the cell's last pixel (y = 0)
+        const double q[6] = {x1 * x1, x2 * x2, 2 * (x1 * x2), 2 * x1, 2 * x2, act ? 1.0 : 0.0};
+        acc[31] += phi;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) acc[k] = fma(u, q[k], acc[k]);
+        // the xi part of the gradient drops |u| < sparsity_tol (dsm.py:346); the theta part does not
+        const double ux = (tol > 0 && fabs(u) < tol) ? 0.0 : u;
+#pragma unroll
+        for (int a = 0; a < NSLOT; ++a) if (a < na) acc[6 + a] = fma(ux, (double)ldg_again(gp + (size_t)a * npix), acc[6 + a]);
+    }
+    const double tot = warp_sum_transposed(acc);     // lane: local gradient entry, 31: value
+    sg[lane] = (lane == 31 || lane < L) ? tot : 0.0;
+}
+
+__device__ __forceinline__ void cell_hessian(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
+                                             int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
+                                             const double* x, double tol, double* Tt, const double* XI, double* sh)
+{
+    const int lane = threadIdx.x & 31;
+    double* DD = Tt + 32 * TILE_LD;
+    const double th[6] = {x[0], x[1], x[2], x[3], x[4], x[5]};
+    const int L = 6 + na;
+    const int nt = (L + 7) >> 3;                      // 8 x 8 tiles per side of the local Hessian
+    double hc[10][2];
+#pragma unroll
+    for (int k = 0; k < 10; ++k) { hc[k][0] = 0; hc[k][1] = 0; }
+    const int fr = lane >> 2, fk = lane & 3;          // DMMA fragment coordinates
+
+    for (int p0 = 0; p0 < npix; p0 += 32) {
+        const int p = p0 + lane;
+        const bool act = p < npix;
+        double y = 0, x1 = 0, x2 = 0;
+        if (act) {
+            const uint32_t rc = prc[p];
+            x1 = xr[rc & 0xffffu];
+            x2 = xc[rc >> 16];
+            y = py[p];
+        }
+        double S = cell_S(th, x1, x2);
+        double* col = Tt + lane;
+        double sx0 = 0, sx1 = 0;
+#pragma unroll
+        for (int a = 0; a < NSLOT; a += 2) {
+            if (a < na) { const double g = act ? (double)gcell[(size_t)a * npix + p] : 0.0; col[(6 + a) * TILE_LD] = g; sx0 = fma(g, XI[a], sx0); }
+            if (a + 1 < NSLOT && a + 1 < na) { const double g = act ? (double)gcell[(size_t)(a + 1) * npix + p] : 0.0; col[(7 + a) * TILE_LD] = g; sx1 = fma(g, XI[a + 1], sx1); }
+        }
+        S += sx0 + sx1;
+        double phi = 0, theta = 0;
+        if (act) logistic(y, S, phi, theta);
+        double kappa = theta - theta * theta;
+        if (kappa < tol) kappa = 0;
+        col[0] = x1 * x1; col[TILE_LD] = x2 * x2; col[2 * TILE_LD] = 2 * (x1 * x2); col[3 * TILE_LD] = 2 * x1; col[4 * TILE_LD] = 2 * x2;
+        col[5 * TILE_LD] = act ? 1.0 : 0.0;
+        for (int e = L; e < 8 * nt; ++e) col[e * TILE_LD] = 0.0;
+        DD[lane] = act ? kappa * y * y : 0.0;
+        __syncwarp();
+        const double* frag = Tt + fr * TILE_LD + fk;
+#pragma unroll 2
+        for (int kk = 0; kk < 8; ++kk) {
+            const double ddk = DD[4 * kk + fk];
+            double f[4], fs[4];
+#pragma unroll
+            for (int X = 0; X < 4; ++X) {
+                f[X] = (X < nt) ? frag[X * 8 * TILE_LD + 4 * kk] : 0.0;
+                fs[X] = f[X] * ddk;
+            }
+#pragma unroll
+            for (int I = 0; I < 4; ++I)
+#pragma unroll
+                for (int J = 0; J <= I; ++J)
+                    if (I < nt) dmma884(hc[I * (I + 1) / 2 + J][0], hc[I * (I + 1) / 2 + J][1], fs[I], f[J]);
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int I = 0; I < 4; ++I)
+#pragma unroll
+        for (int J = 0; J <= I; ++J) {
+            if (I < nt) {
+                const int r = 8 * I + fr, q0 = 8 * J + 2 * fk;
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+                    if (q0 + i <= r && r < L) sh[tri(r, q0 + i)] = hc[I * (I + 1) / 2 + J][i];
+            }
+        }
+}
 
 template <bool HESS>
 __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
@@ -95,157 +258,47 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
                                              double* sg, double* sh)
 {
     const int lane = threadIdx.x & 31;
-    double* U = Tt + 32 * TILE_LD;
-    double* DD = U + 32;
-    const double a1 = x[0], a2 = x[1], a3 = x[2], b1 = x[3], b2 = x[4], c0 = x[5];
-    const double* xi = x + 6;
-    const int na = __popc(am), L = 6 + na;
-    const int Lpad = (L + 3) & ~3;
-    // Hessian block ownership: 4x4 blocks (A, B), B <= A, of the Lpad x Lpad local matrix
-    const int nb = Lpad >> 2, nblk = nb * (nb + 1) / 2;
-    int A0 = 0, B0 = 0, A1 = 0, B1 = 0;
-    if (HESS) {
-        int t = lane;
-        while (t >= A0 + 1) { t -= A0 + 1; ++A0; }
-        B0 = t;
-        t = lane + 32;
-        while (t >= A1 + 1) { t -= A1 + 1; ++A1; }
-        B1 = t;
-    }
-    double h0[16], h1[16];
-    if (HESS) {
-#pragma unroll
-        for (int k = 0; k < 16; ++k) { h0[k] = 0; h1[k] = 0; }
-    }
-    double acc_g = 0, acc_v = 0;
-    // the xi values this cell sees, one per lane
-    const double xi_l = lane < na ? xi[slotj[lane]] : 0.0;
-
-    for (int p0 = 0; p0 < npix; p0 += 32) {
-        const int p = p0 + lane;
-        const bool act = p < npix;
-        double* row = Tt + lane * TILE_LD;
-        double y = 0, S = 0, x1 = 0, x2 = 0;
-        if (act) {
-            const uint32_t rc = prc[p];
-            x1 = xr[rc & 0xffffu];
-            x2 = xc[rc >> 16];
-            y = py[p];
-            S = (x1 * a1 + x2 * a3) * x1 + (x1 * a3 + x2 * a2) * x2 + 2 * (x1 * b1 + x2 * b2) + c0;
-        }
-        row[0] = x1 * x1; row[1] = x2 * x2; row[2] = 2 * (x1 * x2); row[3] = 2 * x1; row[4] = 2 * x2; row[5] = act ? 1.0 : 0.0;
-        double sx = 0;
-        for (int a = 0; a < na; ++a) {
-            const double g = act ? (double)gcell[(size_t)a * npix + p] : 0.0;
-            sx += g * __shfl_sync(0xffffffffu, xi_l, a);
-            row[6 + a] = g;
-        }
-        for (int e = L; e < Lpad; ++e) row[e] = 0;
-        S += sx;
-        double phi = 0, theta = 0;
-        if (act) logistic(y, S, phi, theta);
-        acc_v += phi;
-        const double u = -y * theta;
-        U[lane] = u;
-        if (HESS) {
-            double kappa = theta - theta * theta;
-            if (kappa < tol) kappa = 0;
-            DD[lane] = act ? kappa * y * y : 0.0;
-        }
-        __syncwarp();
-        if (lane < L) {
-            double s = 0;
-            if (lane < 6 || tol == 0) {
-#pragma unroll 8
-                for (int pp = 0; pp < 32; ++pp) s += Tt[pp * TILE_LD + lane] * U[pp];
-            } else {
-                // the xi part of the gradient drops |u| < sparsity_tol (dsm.py:346); the theta part does not
-                for (int pp = 0; pp < 32; ++pp) { const double uu = U[pp]; s += Tt[pp * TILE_LD + lane] * (fabs(uu) < tol ? 0.0 : uu); }
-            }
-            acc_g += s;
-        }
-        if (HESS) {
-            if (lane < nblk) {
-                const double* ra = Tt + 4 * A0;
-                const double* rb = Tt + 4 * B0;
-#pragma unroll 4
-                for (int pp = 0; pp < 32; ++pp) {
-                    const double dd = DD[pp];
-                    const double2 a01 = *reinterpret_cast<const double2*>(ra + pp * TILE_LD);
-                    const double2 a23 = *reinterpret_cast<const double2*>(ra + pp * TILE_LD + 2);
-                    const double2 b01 = *reinterpret_cast<const double2*>(rb + pp * TILE_LD);
-                    const double2 b23 = *reinterpret_cast<const double2*>(rb + pp * TILE_LD + 2);
-                    const double av[4] = {a01.x * dd, a01.y * dd, a23.x * dd, a23.y * dd};
-                    const double bv[4] = {b01.x, b01.y, b23.x, b23.y};
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) h0[i * 4 + j] += av[i] * bv[j];
-                }
-            }
-            if (lane + 32 < nblk) {
-                const double* ra = Tt + 4 * A1;
-                const double* rb = Tt + 4 * B1;
-#pragma unroll 4
-                for (int pp = 0; pp < 32; ++pp) {
-                    const double dd = DD[pp];
-                    const double2 a01 = *reinterpret_cast<const double2*>(ra + pp * TILE_LD);
-                    const double2 a23 = *reinterpret_cast<const double2*>(ra + pp * TILE_LD + 2);
-                    const double2 b01 = *reinterpret_cast<const double2*>(rb + pp * TILE_LD);
-                    const double2 b23 = *reinterpret_cast<const double2*>(rb + pp * TILE_LD + 2);
-                    const double av[4] = {a01.x * dd, a01.y * dd, a23.x * dd, a23.y * dd};
-                    const double bv[4] = {b01.x, b01.y, b23.x, b23.y};
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) h1[i * 4 + j] += av[i] * bv[j];
-                }
-            }
-        }
-        __syncwarp();
-    }
-    // local results -> per-cell scratch
-    acc_v = warp_sum(acc_v);
-    sg[lane] = (lane == 31) ? acc_v : (lane < L ? acc_g : 0.0);
-    if (HESS) {
-        if (lane < nblk) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int r = 4 * A0 + i, q = 4 * B0 + j;
-                    if (q <= r && r < L) sh[tri(r, q)] = h0[i * 4 + j];
-                }
-        }
-        if (lane + 32 < nblk) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int r = 4 * A1 + i, q = 4 * B1 + j;
-                    if (q <= r && r < L) sh[tri(r, q)] = h1[i * 4 + j];
-                }
-        }
-    }
+    double* XI = Tt + 32 * TILE_LD + 32;
+    const int na = __popc(am);
+    __syncwarp();
+    if (lane < na) XI[lane] = x[6 + slotj[lane]];     // the xi values this cell sees
+    __syncwarp();
+    cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, XI, sg);
+    if (HESS) cell_hessian(py, prc, gcell, npix, na, xr, xc, x, tol, Tt, XI, sh);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 
 constexpr size_t EVAL_SMEM = sizeof(double) * EVAL_WARPS * TILE_DOUBLES;
 
-// Evaluation task (c, first): the CTA's warps take the non-empty cells cell_list[first .. first + EVAL_WARPS) of candidate c,
-// one warp per cell, and leave the per-cell value / gradient / Hessian in scrG / scrH.  smem_eval: EVAL_SMEM bytes.
+// Evaluation task (c, first): the CTA's warps share the non-empty cells cell_list[first .. first + EVAL_CELLS) of candidate c
+// -- a warp takes the next cell when it is done with its last one (cells differ in their pixel counts) -- and leave the
+// per-cell value / gradient / Hessian in scrG / scrH.  smem_eval: EVAL_SMEM bytes; *s_next == 0 on entry (all threads
+// synchronised after it was set), and the caller synchronises the CTA after the call.
+__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, const CInfo& ci, int idx,
+                                          double* Tt, int* slotj);
+
 __device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first,
-                                          double* smem_eval, int* s_slotj)
+                                          double* smem_eval, int* s_slotj, int* s_next)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double* Tt = smem_eval + warp * TILE_DOUBLES;
-    int* slotj = s_slotj + warp * 32;
+    const CInfo ci = ws.cinfo[c];
+    const int count = min(EVAL_CELLS, ci.n_ne - first);
+    for (;;) {
+        int i = 0;
+        if (lane == 0) i = atomicAdd(s_next, 1);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= count) break;
+        eval_cell(par, cands, ws, c, ci, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * 32);
+    }
+}
+
+__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, const CInfo& ci, int idx,
+                                          double* Tt, int* slotj)
+{
+    const int lane = threadIdx.x & 31;
     const sdsm_cand* cd = cands + c;
     const int64_t pix_off = cd->pix_off, cell_off = cd->cell_off, tab_off = cd->tab_off;
-    const CInfo ci = ws.cinfo[c];
-    const int idx = first + warp;
-    if (idx >= ci.n_ne) return;
     const int cell = ws.cell_list[cell_off + idx];
     const int h = cd->h;
     const EvalReq rq = ws.req[c];

@@ -1,5 +1,5 @@
 // K3: k_solve -- the persistent solver kernel.  Every candidate's fit is a chain of dependent steps
-//     control task -> evaluation tasks (one per EVAL_WARPS pixel cells) [-> Hessian-row tasks] -> control task -> ...
+//     control task -> evaluation tasks (one per EVAL_CELLS pixel cells) [-> Hessian-row tasks] -> control task -> ...
 // (a few dozen to a few thousand links, objects.py:361-412 around cvxopt's cp), and the chains of a batch differ in length
 // and width by orders of magnitude.  Instead of lock-step launches, the CTAs of one persistent grid pull tasks from a
 // device-side queue (common.cuh): whoever finishes the last evaluation task of a candidate publishes its next control
@@ -77,6 +77,7 @@ __device__ __forceinline__ void finish_stage_task(const WS& ws, uint32_t type, i
     }
     __syncthreads();
     const int next = *s_flag;
+    __syncthreads();                                         // thread 0 reuses s_flag as soon as it is back in the task loop
     if (next == 0) return;
     if (next == 1) { if (threadIdx.x == 0) q_push_one(ws, T_CTRL, (uint32_t)c, 0u); }
     else q_push_range<BLOCK>(ws, T_HG, (uint32_t)c, next - 1, HG_WARPS, s_base);
@@ -89,7 +90,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     extern __shared__ __align__(16) char smem_solve[];
     __shared__ int s_slotj[EVAL_WARPS * 32];
     __shared__ uint2 s_task;
-    __shared__ int s_flag;
+    __shared__ int s_flag, s_next;
     __shared__ unsigned long long s_base;
     const int tid = threadIdx.x;
     const unsigned long long n_target = (unsigned long long)args.n_target;
@@ -97,14 +98,17 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     if (tid == 0) t_start = globaltimer_ns();
     const long long c_begin = clock64();
 
+    unsigned n_popped = 0;
     for (;;) {
         if (tid == 0) {
             const long long c0 = clock64();
             uint2 task;
+            if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) atomicExch(ws.counters + Q_ABORT, 1ull);
             const bool ok = q_pop(ws, n_target, args.timeout_ns, t_start, &task);
             cyc[3] += (unsigned long long)(clock64() - c0);
             s_task = task;
             s_flag = ok ? 1 : 0;
+            s_next = 0;
         }
         __syncthreads();
         const uint2 task = s_task;
@@ -115,7 +119,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         const int c = (int)(task.x & T_CMASK);
         const long long c0 = clock64();
         if (type == T_EVAL) {
-            eval_task(par, cands, ws, c, (int)task.y, (double*)smem_solve, s_slotj);
+            eval_task(par, cands, ws, c, (int)task.y, (double*)smem_solve, s_slotj, &s_next);
             finish_stage_task<BLOCK>(ws, T_EVAL, c, &s_flag, &s_base);
         } else if (type == T_HG) {
             hg_task(par, cands, ws, c, (int)task.y, (double*)smem_solve);
@@ -124,7 +128,14 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
             const sdsm_cand cd = cands[c];
             const CInfo ci = ws.cinfo[c];
             const bool solo = ci.n_ne <= args.solo_cells;
-            for (;;) {
+            for (unsigned link = 1;; ++link) {
+                if ((link & 63u) == 0) {                    // watchdog of a chain that never leaves this CTA
+                    if (tid == 0) s_flag = (globaltimer_ns() - t_start > args.timeout_ns || ld_relaxed_u64(ws.counters + Q_ABORT)) ? 1 : 0;
+                    __syncthreads();
+                    const bool stop = s_flag != 0;
+                    __syncthreads();
+                    if (stop) { if (tid == 0) atomicExch(ws.counters + Q_ABORT, 1ull); break; }
+                }
                 const bool big = (ws.cstate[c].use_xi ? 6 + ci.m : 6) > SMALL_N_MAX;
                 Sm sm;
                 bool requested;
@@ -134,17 +145,22 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     if (tid == 0) { __threadfence(); atomicAdd(ws.counters + Q_DONE, 1ull); }
                     break;
                 }
-                const int n_tasks = (ci.n_ne + EVAL_WARPS - 1) / EVAL_WARPS;
+                const int n_tasks = (ci.n_ne + EVAL_CELLS - 1) / EVAL_CELLS;
                 if (!solo) {
                     // publishing is the LAST thing a control task does: the candidate's next control task may start on another
                     // SM as soon as the evaluations have finished
                     if (tid == 0) ws.pending[c] = n_tasks;
-                    q_push_range<BLOCK>(ws, T_EVAL, (uint32_t)c, n_tasks, EVAL_WARPS, &s_base);
+                    q_push_range<BLOCK>(ws, T_EVAL, (uint32_t)c, n_tasks, EVAL_CELLS, &s_base);
                     break;
                 }
                 // the whole chain in this CTA: evaluate here and go on
                 const EvalReq rq = ws.req[c];
-                for (int k = 0; k < n_tasks; ++k) { eval_task(par, cands, ws, c, k * EVAL_WARPS, (double*)smem_solve, s_slotj); __syncthreads(); }
+                for (int k = 0; k < n_tasks; ++k) {
+                    if (tid == 0) s_next = 0;
+                    __syncthreads();
+                    eval_task(par, cands, ws, c, k * EVAL_CELLS, (double*)smem_solve, s_slotj, &s_next);
+                    __syncthreads();
+                }
                 if (rq.want_h && rq.use_xi)
                     for (int j = 0; j < ci.m; j += HG_WARPS) { hg_task(par, cands, ws, c, j, (double*)smem_solve); __syncthreads(); }
             }
@@ -164,7 +180,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
 
 // prepares the evaluation of F (with Hessian, unscaled) of candidate c at xin
 __global__ void __launch_bounds__(SOLVE_BLOCK)
-k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, const double* __restrict__ xin)
+k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, const double* __restrict__ xin, int want_h)
 {
     const int tid = threadIdx.x;
     const sdsm_cand cd = cands[c];
@@ -178,7 +194,7 @@ k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, co
     for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) P.H[i] = 0.0;
     bad = __syncthreads_or(bad);
     if (tid == 0) {
-        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = 1; rq.use_xi = P.m > 0 ? 1 : 0;
+        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = P.m > 0 ? 1 : 0;
         ws.req[c] = rq;
         ws.cstate[c].pc = bad ? -1 : PC_DONE;
     }
@@ -189,9 +205,12 @@ k_diag_eval_cells(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws)
 {
     extern __shared__ __align__(16) char smem_solve[];
     __shared__ int s_slotj[EVAL_WARPS * 32];
+    __shared__ int s_next;
     const int n_ne = ws.cinfo[c].n_ne;
-    for (int first = blockIdx.x * EVAL_WARPS; first < n_ne; first += gridDim.x * EVAL_WARPS) {
-        eval_task(par, cands, ws, c, first, (double*)smem_solve, s_slotj);
+    for (int first = blockIdx.x * EVAL_CELLS; first < n_ne; first += gridDim.x * EVAL_CELLS) {
+        if (threadIdx.x == 0) s_next = 0;
+        __syncthreads();
+        eval_task(par, cands, ws, c, first, (double*)smem_solve, s_slotj, &s_next);
         __syncthreads();
     }
 }
@@ -225,12 +244,12 @@ k_diag_eval_end(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, doub
     double psi = 0;
     double f;
     if (ws.cstate[c].pc == -1) f = NAN;
-    else if (P.m > 0) f = gather_cells<SOLVE_BLOCK, true>(P, sm, xe, g, 1.0, &psi);
-    else f = gather_poly<SOLVE_BLOCK, true>(P, sm, g, 1.0, &psi);
+    else if (P.m > 0) f = Hout ? gather_cells<SOLVE_BLOCK, true>(P, sm, xe, g, 1.0, &psi) : gather_cells<SOLVE_BLOCK, false>(P, sm, xe, g, 1.0, &psi);
+    else f = Hout ? gather_poly<SOLVE_BLOCK, true>(P, sm, g, 1.0, &psi) : gather_poly<SOLVE_BLOCK, false>(P, sm, g, 1.0, &psi);
     __syncthreads();
     if (tid == 0) *value = f;
     for (int i = tid; i < N; i += SOLVE_BLOCK) grad[i] = g[i];
-    for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) Hout[i] = P.H[i];
+    if (Hout) for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) Hout[i] = P.H[i];
 }
 
 // prepares one interior-point solve of candidate c from x0 (STG_TRACE): k_solve continues it at PC_IPMSTART and records
@@ -265,6 +284,50 @@ __global__ void k_diag_trace_end(Par par, const sdsm_cand* __restrict__ cands, i
     const double* x = ws.vecs + cd.vec_off + (size_t)V_X * ld;
     for (int i = threadIdx.x; i < N; i += blockDim.x) xout[i] = x[i];
     if (threadIdx.x == 0) { status_iters[0] = S->r_ipm; status_iters[1] = S->iters; }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// measurement aid (bench.py, roofline of the evaluation tasks): one sweep of the evaluation tasks over EVERY candidate of
+// the last solved batch at its solution, outside the solver.  k_sweep_prep lists the tasks, k_sweep runs them.
+
+__global__ void __launch_bounds__(SOLVE_BLOCK)
+k_sweep_prep(Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, int want_h, int rows)
+{
+    __shared__ unsigned long long s_base;
+    for (int c = blockIdx.x; c < n_cand; c += gridDim.x) {
+        const sdsm_cand cd = cands[c];
+        const CInfo ci = ws.cinfo[c];
+        const bool live = !ci.flags && ci.n_fg != 1 && ws.cstate[c].pc == PC_DONE;
+        const int count = !live ? 0 : (rows ? (ci.m + HG_WARPS - 1) / HG_WARPS : (ci.n_ne + EVAL_CELLS - 1) / EVAL_CELLS);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const int ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
+            EvalReq rq; rq.x = ws.vecs + cd.vec_off + (size_t)V_X * ld; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = ci.m > 0 ? 1 : 0;
+            ws.req[c] = rq;
+            s_base = atomicAdd(ws.counters + Q_TAIL, (unsigned long long)count);
+        }
+        __syncthreads();
+        const unsigned long long base = s_base;
+        for (int k = threadIdx.x; k < count; k += SOLVE_BLOCK)
+            ws.q_task[base + k] = make_uint2((uint32_t)c, (uint32_t)(k * (rows ? HG_WARPS : EVAL_CELLS)));
+    }
+}
+
+__global__ void __launch_bounds__(SOLVE_BLOCK, 2)
+k_sweep(Par par, const sdsm_cand* __restrict__ cands, WS ws, int rows)
+{
+    extern __shared__ __align__(16) char smem_solve[];
+    __shared__ int s_slotj[EVAL_WARPS * 32];
+    __shared__ int s_next;
+    const unsigned long long n_tasks = ws.counters[Q_TAIL];
+    for (unsigned long long i = blockIdx.x; i < n_tasks; i += gridDim.x) {
+        const uint2 task = ws.q_task[i];
+        if (threadIdx.x == 0) s_next = 0;
+        __syncthreads();
+        if (rows) hg_task(par, cands, ws, (int)task.x, (int)task.y, (double*)smem_solve);
+        else eval_task(par, cands, ws, (int)task.x, (int)task.y, (double*)smem_solve, s_slotj, &s_next);
+        __syncthreads();
+    }
 }
 
 }  // namespace sdsm

@@ -58,6 +58,7 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     if (prop.major < 10) { ctx->err = "superdsm_b200 is built for sm_100a (B200) only"; return SDSM_E_UNSUPPORTED; }
     const int smem_max = (int)solve_smem_bytes(SMEM_L_CAP);
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    CUDA_TRY(ctx, cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_end, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
@@ -234,16 +235,16 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
 extern "C" int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, const double* d_x,
                                    double* d_value, double* d_grad, double* d_H, void* d_workspace, void* stream_)
 {
-    if (!ctx || !plan || !d_cands || !d_x || !d_value || !d_grad || !d_H || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
+    if (!ctx || !plan || !d_cands || !d_x || !d_value || !d_grad || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
     const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
     WS ws = make_ws(d_workspace, L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const int lcap = ctrl_lcap(plan->n_max);
     const size_t smem = solve_smem_bytes(lcap);
-    k_diag_eval_begin<<<1, SOLVE_BLOCK, 0, stream>>>(ctx->par, d_cands, c, ws, d_x);
+    k_diag_eval_begin<<<1, SOLVE_BLOCK, 0, stream>>>(ctx->par, d_cands, c, ws, d_x, d_H ? 1 : 0);
     k_diag_eval_cells<<<ctx->sm_count, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, c, ws);
-    if (ctx->par.has_smooth) { k_diag_eval_rows<<<ctx->sm_count, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, c, ws); ctx->launches++; }
+    if (ctx->par.has_smooth && d_H) { k_diag_eval_rows<<<ctx->sm_count, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, c, ws); ctx->launches++; }
     k_diag_eval_end<<<1, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, c, ws, d_value, d_grad, d_H, lcap);
     ctx->launches += 3;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -304,5 +305,24 @@ extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     CUDA_TRY(ctx, cudaMemcpyAsync(h_stats, ws.counters, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t n_cand, int32_t want_h,
+                               int32_t rows, int32_t repeats, void* d_workspace, void* stream_)
+{
+    if (!ctx || !plan || !d_cands || !d_workspace || n_cand != ctx->n_cand || repeats < 1) return SDSM_E_ARG;
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    WS ws = make_ws(d_workspace, L);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
+    const int prep_grid = n_cand < 8 * ctx->sm_count ? n_cand : 8 * ctx->sm_count;
+    k_sweep_prep<<<prep_grid, SOLVE_BLOCK, 0, stream>>>(ctx->par, d_cands, n_cand, ws, want_h, rows);
+    const size_t smem = solve_smem_bytes(ctrl_lcap(plan->n_max));
+    for (int r = 0; r < repeats; ++r)
+        k_sweep<<<ctx->sm_count * ctx->solve_ctas_per_sm, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, ws, rows);
+    ctx->launches += 1 + repeats;
+    CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
 }

