@@ -19,8 +19,9 @@
  * stream; nothing synchronises.  Errors are integer codes (0 = ok), solver trouble is per-candidate data
  * (status word), never a C++ exception.  One context per device; a context is not thread-safe.
  *
- * Environment (read by sdsm_create): SDSM_SOLO_CELLS (default 16) -- candidates with at most this many pixel cells run
- * their whole chain of solver steps inside one CTA; SDSM_TIMEOUT_S (default 60) -- watchdog of the persistent solver kernel.
+ * Environment (read by sdsm_create): SDSM_SOLO_CELLS (default 8) -- candidates with at most this many pixel cells run
+ * their whole chain of solver steps inside one CTA; SDSM_TASK_SMALL_CELLS (default 512) -- candidates with at most this many
+ * cells get evaluation tasks of one cell per warp (more CTAs per evaluation, shorter links); SDSM_TIMEOUT_S (default 60) -- watchdog of the persistent solver kernel.
  */
 #ifndef SUPERDSM_B200_H
 #define SUPERDSM_B200_H
@@ -144,6 +145,10 @@ int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_ca
  * chains per thread); *flops receives the floating-point operations of the launch.  Time it with CUDA events. */
 int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flops, void* stream);
 
+/* Diagnostics: h_us[n_cand] receives, for every candidate of the last sdsm_solve_batch() on this workspace, the time (in
+ * microseconds after the solver kernel started) at which its fit finished; SYNCHRONISES the stream. */
+int sdsm_finish_times(sdsm_ctx* ctx, const void* d_workspace, int32_t* h_us, void* stream);
+
 /* Measurement aid: `repeats` sweeps of the evaluation tasks (rows = 0; value + gradient, plus the per-cell Hessians if
  * want_h) or of the Hessian-row tasks (rows = 1) over EVERY candidate of the last solved batch at its solution, outside
  * the solver: the streaming pass the HBM / FP64 roofline of the energy kernels is quoted on.  Time it with CUDA events. */
@@ -153,10 +158,11 @@ int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_can
 /* number of kernel launches this context has enqueued so far (bench.py's gpu_launches) */
 int64_t sdsm_launch_count(const sdsm_ctx* ctx);
 
-/* Diagnostics / watchdog: copies the 16 counters of the persistent solver of the last sdsm_solve_batch() on this workspace to
+/* Diagnostics / watchdog: copies the 32 counters of the persistent solver of the last sdsm_solve_batch() on this workspace to
  * h_stats and SYNCHRONISES the stream.  [2] candidates finished, [3] != 0: the watchdog aborted the solve (results invalid),
  * [4..7] busy clock cycles summed over CTAs in evaluation / Hessian-row / control tasks and idle, [8..10] number of
- * evaluation / Hessian-row / control tasks, [11] CTA lifetime cycles summed over CTAs. */
+ * evaluation / Hessian-row / control tasks, [11] CTA lifetime cycles summed over CTAs, [16..19] / [20..23] cycles / number of
+ * the queued evaluation tasks by kind (polynomial model: value+gradient, +Hessian; deformable model: value+gradient, +Hessian). */
 int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_t* h_stats, void* stream);
 
 #ifdef __cplusplus

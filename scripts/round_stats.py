@@ -21,12 +21,14 @@ print('solver stats', st)
 tot = max(st['cyc_total'], 1)
 print('CTA time share: eval %.3f hrows %.3f ctrl %.3f idle %.3f' % tuple(st[k] / tot for k in ('cyc_eval', 'cyc_hrows', 'cyc_ctrl', 'cyc_idle')))
 info = res.info
+ft = eng.finish_times_us()
+print('finish time (us) percentiles 50/90/99/100', np.percentile(ft, [50, 90, 99, 100]))
 n = res.cands['n']
 ev = info[:, 6] + info[:, 7]
 print('status counts', np.bincount(res.status))
 print('evals per candidate: percentiles 0/50/90/99/100', np.percentile(ev, [0, 50, 90, 99, 100]))
 print('n percentiles', np.percentile(n, [0, 50, 90, 99, 100]), 'm percentiles', np.percentile(info[:, 0], [0, 50, 90, 99, 100]))
-order = np.argsort(-ev)[:20]
+order = np.argsort(-ft)[:25]
 for k in order:
-    print('cand', k, 'n', n[k], 'm', info[k, 0], 'it', info[k, 1:4], 'n_fg', info[k, 4], 'bits', info[k, 5], 'nf', info[k, 6], 'nh', info[k, 7], 'status', res.status[k], 'E', res.energy[k])
+    print('cand', k, 'n', n[k], 'm', info[k, 0], 'it', info[k, 1:4], 'n_fg', info[k, 4], 'bits', info[k, 5], 'nf', info[k, 6], 'nh', info[k, 7], 'status', res.status[k], 'E', res.energy[k], 'done_us', ft[k])
 np.savez('gpurun_out/round_stats.npz', info=info, n=n, status=res.status, energy=res.energy, cell_cap=res.cands['cell_cap'])

@@ -40,7 +40,7 @@ class Out(ctypes.Structure):
 
 EXPORTS = ('sdsm_abi_version', 'sdsm_create', 'sdsm_destroy', 'sdsm_last_error', 'sdsm_set_image', 'sdsm_set_params',
            'sdsm_plan_batch', 'sdsm_solve_batch', 'sdsm_eval_candidate', 'sdsm_export_smooth', 'sdsm_trace_solve',
-           'sdsm_dfma_peak', 'sdsm_launch_count', 'sdsm_solver_stats', 'sdsm_sweep_eval')
+           'sdsm_dfma_peak', 'sdsm_launch_count', 'sdsm_solver_stats', 'sdsm_sweep_eval', 'sdsm_finish_times')
 
 _lib = None
 
@@ -71,6 +71,7 @@ def load():
     lib.sdsm_launch_count.argtypes = [vp]
     lib.sdsm_launch_count.restype = i64
     lib.sdsm_solver_stats.argtypes = [vp, vp, vp, vp]
+    lib.sdsm_finish_times.argtypes = [vp, vp, vp, vp]
     lib.sdsm_sweep_eval.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, i32, i32, i32, vp, vp]
     if lib.sdsm_abi_version() != 3:
         raise ImportError('libsuperdsm_b200.so: ABI version mismatch')

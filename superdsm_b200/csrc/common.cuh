@@ -17,13 +17,22 @@ constexpr int TILE_LD    = 36;    // row stride (doubles) of the per-warp tile T
 constexpr int SOLVE_BLOCK = 256;  // k_solve: persistent CTAs, every task is executed by one CTA
 constexpr int EVAL_BLOCK = SOLVE_BLOCK;   // evaluation task: one warp per pixel cell
 constexpr int EVAL_WARPS = EVAL_BLOCK / 32;
-constexpr int EVAL_CELLS = 32;    // non-empty pixel cells per evaluation task: the CTA's warps take them one by one
-constexpr int TILE_DOUBLES = 32 * TILE_LD + 64;                 // tile + dd[32] + xi[32]
+constexpr int EVAL_CELLS = 32;    // most non-empty pixel cells per evaluation task: the CTA's warps take them one by one
+// per-warp shared memory of the evaluation tasks (doubles): the value + gradient pass stages the pixel data of STAGES
+// chunks of 32 pixels there with cp.async (STAGE_BYTES each: G~ rows [25][32] f32, y [32] f64, rc [32] u32); the Hessian pass
+// reuses the space for its tile T[32][TILE_LD] + dd[32]; then xi[32].
+constexpr int STAGES = 3;
+constexpr int STAGE_BYTES = NSLOT * 32 * 4 + 32 * 8 + 32 * 4;   // 3584
+constexpr int WARP_AREA_DOUBLES = STAGES * STAGE_BYTES / 8;      // 1344 >= 32 * TILE_LD + 32
+static_assert(WARP_AREA_DOUBLES >= 32 * TILE_LD + 32, "the Hessian tile must fit the staging area");
+constexpr int XI_OFF = WARP_AREA_DOUBLES;
+constexpr int TILE_DOUBLES = WARP_AREA_DOUBLES + 32;
 constexpr int CTRL_BLOCK = SOLVE_BLOCK;   // control task: one CTA advances one candidate's state machine
 constexpr int CTRL_WARPS = CTRL_BLOCK / 32;
 constexpr int SMEM_L_CAP = 5504;  // doubles of shared memory for the packed Cholesky factor (N <= 104)
 constexpr int SMALL_N_MAX = 104;  // systems up to this size are factorised in shared memory, larger ones blocked in global memory / L2
 constexpr int BIG_BLOCK  = SOLVE_BLOCK;
+constexpr int N_COUNTERS = 32;
 constexpr int NVEC       = 12;    // N-vectors of the interior-point solver
 
 struct Img { const double* y; const int32_t* atoms; int32_t H, W; };
@@ -63,6 +72,7 @@ struct EvalReq {
     const double* x;       // point to evaluate (6 + m values, or 6)
     double hfac;           // factor of the Hessian rows the T_HG tasks write: z * scale / n (objects.py:380), or 1 (diagnostics)
     int32_t want_h, use_xi;
+    int32_t cpt, pad;      // non-empty cells per evaluation task of this request (EVAL_WARPS .. EVAL_CELLS)
 };
 
 // Workspace carved out of the caller's buffer.  Per-pixel / per-cell / per-table arrays are indexed with the
@@ -93,7 +103,7 @@ struct WS {
     uint2*    q_task;      // [q_cap]  x = type << 28 | candidate, y = first item of the task
     uint32_t* q_seq;       // [q_cap]  slot sequence numbers (slot i is free for ticket t when seq == t, full when seq == t + 1)
     int32_t*  pending;     // [n_cand] tasks of the candidate's current stage that have not finished yet
-    unsigned long long* counters;   // [16]  Q_HEAD, Q_TAIL, Q_DONE, then busy-cycle / task statistics (sched.cuh)
+    unsigned long long* counters;   // [N_COUNTERS]  Q_HEAD, Q_TAIL, Q_DONE, then busy-cycle / task statistics (sched.cuh)
     uint32_t  q_mask;      // q_cap - 1 (power of two)
     int32_t   n_cand;
 };
@@ -141,7 +151,7 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_q_task = take(sizeof(uint2) * q_cap);
     L.o_q_seq = take(sizeof(uint32_t) * q_cap);
     L.o_pending = take(sizeof(int32_t) * (size_t)n_cand);
-    L.o_counters = take(sizeof(unsigned long long) * 16);
+    L.o_counters = take(sizeof(unsigned long long) * N_COUNTERS);
     L.C = C;
     L.q_cap = q_cap;
     L.n_cand = n_cand;
@@ -266,7 +276,8 @@ __device__ __forceinline__ bool fp_member(int lab, const int32_t* fp, int n)
 // above the number of tasks that can be in flight (sdsm_plan_batch), so producers only ever wait for a consumer that
 // has claimed its ticket and is about to read the slot.
 
-enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG, Q_CYC_CTRL, Q_CYC_IDLE, Q_N_EVAL, Q_N_HG, Q_N_CTRL, Q_CYC_TOTAL };
+enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG, Q_CYC_CTRL, Q_CYC_IDLE, Q_N_EVAL, Q_N_HG, Q_N_CTRL, Q_CYC_TOTAL, Q_T0,
+       Q_CYC_KIND = 16 /* [4]: evaluation-task cycles by kind = use_xi * 2 + want_h */, Q_N_KIND = 20 /* [4]: tasks by kind */ };
 enum { T_CTRL = 0, T_EVAL = 1, T_HG = 2 };
 constexpr uint32_t T_SHIFT = 28, T_CMASK = (1u << T_SHIFT) - 1u;
 

@@ -155,26 +155,32 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
         P.H[a * N + t] = v;
         P.H[t * N + a] = v;
     }
-    // (2) xi gradient: grid point j collects from the cells around its own
-    for (int j = tid; j < m; j += BLOCK) {
-        const uint32_t gp = P.grid[j];
-        const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
-        double s = 0;
-        for (int da = -NC; da <= NC; ++da) {
-            const int a = ja - da;
-            if (a < 0 || a >= ch) continue;
-            for (int db = -NC; db <= NC; ++db) {
-                const int b = jb - db;
-                if (b < 0 || b >= cw) continue;
-                const int cell = a * cw + b;
-                if (P.cstart[cell + 1] == P.cstart[cell]) continue;
-                const int li = local_index(P.amask[cell], da, db);
-                if (li >= 0) s += P.scrG[(size_t)cell * SCRG + li];
+    // (2) xi gradient: grid point j collects from the (up to 25) cells around its own; a warp per grid point, a lane per
+    //     cell, so that the dependent loads (cell -> mask -> scratch entry) of the 25 cells overlap; fixed reduction tree
+    {
+        const int lane = tid & 31, warp = tid >> 5;
+        for (int j = warp; j < m; j += BLOCK / 32) {
+            const uint32_t gp = P.grid[j];
+            const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
+            double v = 0;
+            if (lane < NSLOT) {
+                const int da = lane / 5 - NC, db = lane % 5 - NC;
+                const int a = ja - da, b = jb - db;
+                if (a >= 0 && a < ch && b >= 0 && b < cw) {
+                    const int cell = a * cw + b;
+                    if (P.cstart[cell + 1] != P.cstart[cell]) {
+                        const int li = local_index(P.amask[cell], da, db);
+                        if (li >= 0) v = P.scrG[(size_t)cell * SCRG + li];
+                    }
+                }
+            }
+            double s = warp_sum(v);
+            if (lane == 0) {
+                const double xv = x[6 + j];
+                s += P.alpha * (xv / sqrt(xv * xv + P.eps));                      // dsm.py:350
+                g[6 + j] = sc * s;
             }
         }
-        const double v = x[6 + j];
-        s += P.alpha * (v / sqrt(v * v + P.eps));                             // dsm.py:350
-        g[6 + j] = sc * s;
     }
     // the xi-theta and xi-xi blocks of the Hessian are assembled by the T_HG tasks (one warp per grid point), before this task runs
     __syncthreads();
@@ -607,7 +613,7 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
 // finished.  first = false: there is an evaluation to consume (always true except for the task that starts the candidate).
 template <int BLOCK, bool BIG>
 __device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
-                          Sm& sm, const sdsm_out& out, double* trace)
+                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells)
 {
     const int tid = threadIdx.x;
     CState S = ws.cstate[c];                 // every thread keeps its own copy; all threads compute the same scalars
@@ -989,6 +995,7 @@ __device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sds
         if (requested) {
             EvalReq rq;
             rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = S.z * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;
+            rq.cpt = P.n_ne <= task_small_cells ? EVAL_WARPS : EVAL_CELLS; rq.pad = 0;
             ws.req[c] = rq;
         }
     }

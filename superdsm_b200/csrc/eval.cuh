@@ -131,9 +131,42 @@ __device__ __forceinline__ void eval_cell_poly(const double* __restrict__ py, co
 // cell_hessian: the local Hessian  sum_p dd_p row_p row_p^T: the lanes stage their rows in a shared-memory tile
 // T[parameter][pixel] and the warp multiplies the 8 x 8 output tiles of the lower triangle on the FP64 tensor cores.
 
+// cp.async (LDGSTS): 4 / 8 bytes global -> shared without passing through registers
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Stages chunk k (32 pixels from p0 = 32 k) of the cell into shared memory: every lane copies its own pixel's y, rc and the
+// na entries of its row of G~ (a lane only ever reads back what it copied itself, so no warp synchronisation is needed).
+// Lanes beyond the cell's last pixel copy the chunk's first pixel: finite data that the caller masks out.
+__device__ __forceinline__ void stage_chunk(char* stage, const double* __restrict__ py, const uint32_t* __restrict__ prc,
+                                            const float* __restrict__ gcell, int npix, int na, int p0, int lane)
+{
+    const int p = (p0 + lane < npix) ? p0 + lane : p0;
+    float* G = reinterpret_cast<float*>(stage);
+    double* Y = reinterpret_cast<double*>(stage + NSLOT * 32 * 4);
+    uint32_t* RC = reinterpret_cast<uint32_t*>(stage + NSLOT * 32 * 4 + 32 * 8);
+    cp_async8(Y + lane, py + p);
+    cp_async4(RC + lane, prc + p);
+    const float* gp = gcell + p;
+#pragma unroll
+    for (int a = 0; a < NSLOT; ++a) {
+        if (a < na) cp_async4(G + a * 32 + lane, gp);
+        gp += npix;
+    }
+}
+
 __device__ __forceinline__ void cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
                                              int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
-                                             const double* x, double tol, const double* XI, double* sg)
+                                             const double* x, double tol, char* stages, const double* XI, double* sg)
 {
     const int lane = threadIdx.x & 31;
     const double th[6] = {x[0], x[1], x[2], x[3], x[4], x[5]};
@@ -141,39 +174,50 @@ __device__ __forceinline__ void cell_value_grad(const double* __restrict__ py, c
     double acc[32];                                   // acc[e] = local gradient entry e, acc[31] = value
 #pragma unroll
     for (int k = 0; k < 32; ++k) acc[k] = 0;
-    for (int p0 = 0; p0 < npix; p0 += 32) {
-        const int p = p0 + lane;
-        const bool act = p < npix;
-        // The row of G~ is read twice (second time from L1) instead of being kept in 25 registers across the logistic
-        // function: with the 32 accumulators that would not fit the 128 registers two resident CTAs per SM allow.
-        const float* gp = gcell + (act ? p : 0);
-        double y = 0, x1 = 0, x2 = 0;
-        if (act) {
-            const uint32_t rc = prc[p];
-            x1 = xr[rc & 0xffffu];
-            x2 = xc[rc >> 16];
-            y = py[p];
-        }
+    const int nchunks = (npix + 31) >> 5;
+    // software pipeline: chunk k + STAGES - 1 is in flight while chunk k is evaluated
+#pragma unroll
+    for (int k = 0; k < STAGES - 1; ++k) {
+        if (k < nchunks) stage_chunk(stages + k * STAGE_BYTES, py, prc, gcell, npix, na, 32 * k, lane);
+        cp_async_commit();
+    }
+    int slot = 0, slot_in = STAGES - 1;
+    for (int k = 0; k < nchunks; ++k) {
+        if (k + STAGES - 1 < nchunks) stage_chunk(stages + slot_in * STAGE_BYTES, py, prc, gcell, npix, na, 32 * (k + STAGES - 1), lane);
+        cp_async_commit();
+        cp_async_wait<STAGES - 1>();                  // this lane's copies of chunk k have landed
+        const char* stage = stages + slot * STAGE_BYTES;
+        const float* G = reinterpret_cast<const float*>(stage) + lane;
+        const bool act = 32 * k + lane < npix;
+        const uint32_t rc = reinterpret_cast<const uint32_t*>(stage + NSLOT * 32 * 4 + 32 * 8)[lane];
+        const double y = act ? reinterpret_cast<const double*>(stage + NSLOT * 32 * 4)[lane] : 0.0;
+        const double x1 = xr[rc & 0xffffu], x2 = xc[rc >> 16];
         double S = cell_S(th, x1, x2);
         double sx0 = 0, sx1 = 0;
 #pragma unroll
         for (int a = 0; a < NSLOT; a += 2) {
-            if (a < na) sx0 = fma((double)gp[(size_t)a * npix], XI[a], sx0);
-            if (a + 1 < NSLOT && a + 1 < na) sx1 = fma((double)gp[(size_t)(a + 1) * npix], XI[a + 1], sx1);
+            if (a < na) sx0 = fma((double)G[a * 32], XI[a], sx0);
+            if (a + 1 < NSLOT && a + 1 < na) sx1 = fma((double)G[(a + 1) * 32], XI[a + 1], sx1);
         }
         S += sx0 + sx1;
         double phi = 0, theta = 0;
         if (act) logistic(y, S, phi, theta);
         const double u = -y * theta;                  // 0 for the lanes beyond the cell's last pixel (y = 0)
-        const double q[6] = {x1 * x1, x2 * x2, 2 * (x1 * x2), 2 * x1, 2 * x2, act ? 1.0 : 0.0};
+        const double q[6] = {x1 * x1, x2 * x2, 2 * (x1 * x2), 2 * x1, 2 * x2, 1.0};
         acc[31] += phi;
 #pragma unroll
-        for (int k = 0; k < 6; ++k) acc[k] = fma(u, q[k], acc[k]);
+        for (int e = 0; e < 6; ++e) acc[e] = fma(u, q[e], acc[e]);
         // the xi part of the gradient drops |u| < sparsity_tol (dsm.py:346); the theta part does not
         const double ux = (tol > 0 && fabs(u) < tol) ? 0.0 : u;
+        // the row of G~ is read from shared memory a second time instead of living in 25 registers across the logistic
+        // function: with the 32 accumulators that would not fit the 128 registers two resident CTAs per SM allow
+        const volatile float* G2 = G;
 #pragma unroll
-        for (int a = 0; a < NSLOT; ++a) if (a < na) acc[6 + a] = fma(ux, (double)ldg_again(gp + (size_t)a * npix), acc[6 + a]);
+        for (int a = 0; a < NSLOT; ++a) if (a < na) acc[6 + a] = fma(ux, (double)G2[a * 32], acc[6 + a]);
+        slot = (slot + 1 == STAGES) ? 0 : slot + 1;
+        slot_in = (slot_in + 1 == STAGES) ? 0 : slot_in + 1;
     }
+    cp_async_wait<0>();
     const double tot = warp_sum_transposed(acc);     // lane: local gradient entry, 31: value
     sg[lane] = (lane == 31 || lane < L) ? tot : 0.0;
 }
@@ -258,13 +302,15 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
                                              double* sg, double* sh)
 {
     const int lane = threadIdx.x & 31;
-    double* XI = Tt + 32 * TILE_LD + 32;
+    double* XI = Tt + XI_OFF;
     const int na = __popc(am);
     __syncwarp();
     if (lane < na) XI[lane] = x[6 + slotj[lane]];     // the xi values this cell sees
     __syncwarp();
-    cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, XI, sg);
+    cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI, sg);
+    __syncwarp();
     if (HESS) cell_hessian(py, prc, gcell, npix, na, xr, xc, x, tol, Tt, XI, sh);
+    __syncwarp();
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -283,7 +329,7 @@ __device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __res
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const CInfo ci = ws.cinfo[c];
-    const int count = min(EVAL_CELLS, ci.n_ne - first);
+    const int count = min(ws.req[c].cpt, ci.n_ne - first);
     for (;;) {
         int i = 0;
         if (lane == 0) i = atomicAdd(s_next, 1);

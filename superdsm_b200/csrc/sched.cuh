@@ -27,6 +27,7 @@ struct SolveArgs {
     int n_target;            // candidates that must finish
     int lcap;                // shared-memory capacity (doubles) for a packed Cholesky factor
     int solo_cells;          // candidates with at most this many non-empty cells run their chain inside one CTA
+    int task_small_cells;    // candidates with at most this many non-empty cells get one cell per warp (EVAL_WARPS per task)
     unsigned long long timeout_ns;   // watchdog: idle CTAs abort the kernel after this long
     double* trace;           // diagnostics (STG_TRACE) or nullptr
 };
@@ -49,8 +50,9 @@ __global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, in
         } else ws.q_seq[i] = i;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        for (int k = 0; k < 16; ++k) ws.counters[k] = 0ull;
+        for (int k = 0; k < N_COUNTERS; ++k) ws.counters[k] = 0ull;
         ws.counters[Q_TAIL] = (unsigned long long)n_first;
+        ws.counters[Q_T0] = globaltimer_ns();
     }
 }
 
@@ -94,7 +96,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     __shared__ unsigned long long s_base;
     const int tid = threadIdx.x;
     const unsigned long long n_target = (unsigned long long)args.n_target;
-    unsigned long long t_start = 0, cyc[4] = {0, 0, 0, 0}, cnt[3] = {0, 0, 0};
+    unsigned long long t_start = 0, cyc[4] = {0, 0, 0, 0}, cnt[3] = {0, 0, 0}, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0};
     if (tid == 0) t_start = globaltimer_ns();
     const long long c_begin = clock64();
 
@@ -120,6 +122,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         const long long c0 = clock64();
         if (type == T_EVAL) {
             eval_task(par, cands, ws, c, (int)task.y, (double*)smem_solve, s_slotj, &s_next);
+            if (tid == 0) { const EvalReq rq = ws.req[c]; const int kind = (rq.use_xi ? 2 : 0) + (rq.want_h ? 1 : 0); kcyc[kind] += (unsigned long long)(clock64() - c0); kcnt[kind] += 1; }
             finish_stage_task<BLOCK>(ws, T_EVAL, c, &s_flag, &s_base);
         } else if (type == T_HG) {
             hg_task(par, cands, ws, c, (int)task.y, (double*)smem_solve);
@@ -139,18 +142,23 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                 const bool big = (ws.cstate[c].use_xi ? 6 + ci.m : 6) > SMALL_N_MAX;
                 Sm sm;
                 bool requested;
-                if (big) { carve_smem_big(sm, smem_solve); requested = ctrl_step<BLOCK, true>(par, img, cd, ci, ws, c, sm, out, args.trace); }
-                else { carve_smem(sm, smem_solve, args.lcap); requested = ctrl_step<BLOCK, false>(par, img, cd, ci, ws, c, sm, out, args.trace); }
+                if (big) { carve_smem_big(sm, smem_solve); requested = ctrl_step<BLOCK, true>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
+                else { carve_smem(sm, smem_solve, args.lcap); requested = ctrl_step<BLOCK, false>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
                 if (!requested) {
-                    if (tid == 0) { __threadfence(); atomicAdd(ws.counters + Q_DONE, 1ull); }
+                    if (tid == 0) {
+                        ws.pending[c] = (int32_t)((globaltimer_ns() - ws.counters[Q_T0]) / 1000ull);   // diagnostics: finish time, us
+                        __threadfence();
+                        atomicAdd(ws.counters + Q_DONE, 1ull);
+                    }
                     break;
                 }
-                const int n_tasks = (ci.n_ne + EVAL_CELLS - 1) / EVAL_CELLS;
+                const int cpt = ws.req[c].cpt;
+                const int n_tasks = (ci.n_ne + cpt - 1) / cpt;
                 if (!solo) {
                     // publishing is the LAST thing a control task does: the candidate's next control task may start on another
                     // SM as soon as the evaluations have finished
                     if (tid == 0) ws.pending[c] = n_tasks;
-                    q_push_range<BLOCK>(ws, T_EVAL, (uint32_t)c, n_tasks, EVAL_CELLS, &s_base);
+                    q_push_range<BLOCK>(ws, T_EVAL, (uint32_t)c, n_tasks, cpt, &s_base);
                     break;
                 }
                 // the whole chain in this CTA: evaluate here and go on
@@ -158,7 +166,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                 for (int k = 0; k < n_tasks; ++k) {
                     if (tid == 0) s_next = 0;
                     __syncthreads();
-                    eval_task(par, cands, ws, c, k * EVAL_CELLS, (double*)smem_solve, s_slotj, &s_next);
+                    eval_task(par, cands, ws, c, k * cpt, (double*)smem_solve, s_slotj, &s_next);
                     __syncthreads();
                 }
                 if (rq.want_h && rq.use_xi)
@@ -172,6 +180,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         atomicAdd(ws.counters + Q_CYC_HG, cyc[T_HG]);     atomicAdd(ws.counters + Q_CYC_IDLE, cyc[3]);
         atomicAdd(ws.counters + Q_N_CTRL, cnt[T_CTRL]);   atomicAdd(ws.counters + Q_N_EVAL, cnt[T_EVAL]);
         atomicAdd(ws.counters + Q_N_HG, cnt[T_HG]);       atomicAdd(ws.counters + Q_CYC_TOTAL, (unsigned long long)(clock64() - c_begin));
+        for (int k = 0; k < 4; ++k) { atomicAdd(ws.counters + Q_CYC_KIND + k, kcyc[k]); atomicAdd(ws.counters + Q_N_KIND + k, kcnt[k]); }
     }
 }
 
@@ -194,7 +203,7 @@ k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, co
     for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) P.H[i] = 0.0;
     bad = __syncthreads_or(bad);
     if (tid == 0) {
-        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = P.m > 0 ? 1 : 0;
+        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = P.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.pad = 0;
         ws.req[c] = rq;
         ws.cstate[c].pc = bad ? -1 : PC_DONE;
     }
@@ -302,7 +311,7 @@ k_sweep_prep(Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, in
         __syncthreads();
         if (threadIdx.x == 0) {
             const int ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
-            EvalReq rq; rq.x = ws.vecs + cd.vec_off + (size_t)V_X * ld; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = ci.m > 0 ? 1 : 0;
+            EvalReq rq; rq.x = ws.vecs + cd.vec_off + (size_t)V_X * ld; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = ci.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.pad = 0;
             ws.req[c] = rq;
             s_base = atomicAdd(ws.counters + Q_TAIL, (unsigned long long)count);
         }

@@ -28,7 +28,8 @@ struct sdsm_ctx {
     int64_t P = 0, C = 0, T = 0, V = 0, M = 0, K = 0;
     int32_t n_cand = 0;
     int solve_ctas_per_sm = 1;               // resident CTAs of k_solve per SM (occupancy query)
-    int solo_cells = 16;                     // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
+    int solo_cells = 8;                      // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
+    int task_small_cells = 512;              // SDSM_TASK_SMALL_CELLS: candidates up to this many cells get one cell per warp
     double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
     std::string err;
 };
@@ -65,6 +66,7 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->solve_ctas_per_sm, k_solve, SOLVE_BLOCK, (size_t)smem_max));
     if (ctx->solve_ctas_per_sm < 1) { ctx->err = "k_solve does not fit on an SM"; return SDSM_E_UNSUPPORTED; }
     if (const char* e = getenv("SDSM_SOLO_CELLS")) ctx->solo_cells = atoi(e);
+    if (const char* e = getenv("SDSM_TASK_SMALL_CELLS")) ctx->task_small_cells = atoi(e);
     if (const char* e = getenv("SDSM_TIMEOUT_S")) ctx->timeout_s = atof(e);
     return SDSM_OK;
 }
@@ -188,6 +190,7 @@ static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_can
     args.n_target = n_first;
     args.lcap = lcap;
     args.solo_cells = ctx->solo_cells;
+    args.task_small_cells = ctx->task_small_cells;
     args.timeout_ns = (unsigned long long)(ctx->timeout_s * 1e9);
     args.trace = trace;
     const int grid = ctx->sm_count * ctx->solve_ctas_per_sm;
@@ -303,7 +306,7 @@ extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_
     WS ws = make_ws(const_cast<void*>(d_workspace), L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    CUDA_TRY(ctx, cudaMemcpyAsync(h_stats, ws.counters, sizeof(uint64_t) * 16, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_stats, ws.counters, sizeof(uint64_t) * N_COUNTERS, cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
     return SDSM_OK;
 }
@@ -316,7 +319,7 @@ extern "C" int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_
     WS ws = make_ws(d_workspace, L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * 16, stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, sizeof(unsigned long long) * N_COUNTERS, stream));
     const int prep_grid = n_cand < 8 * ctx->sm_count ? n_cand : 8 * ctx->sm_count;
     k_sweep_prep<<<prep_grid, SOLVE_BLOCK, 0, stream>>>(ctx->par, d_cands, n_cand, ws, want_h, rows);
     const size_t smem = solve_smem_bytes(ctrl_lcap(plan->n_max));
@@ -324,5 +327,17 @@ extern "C" int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_
         k_sweep<<<ctx->sm_count * ctx->solve_ctas_per_sm, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, ws, rows);
     ctx->launches += 1 + repeats;
     CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_finish_times(sdsm_ctx* ctx, const void* d_workspace, int32_t* h_us, void* stream_)
+{
+    if (!ctx || !d_workspace || !h_us) return SDSM_E_ARG;
+    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    WS ws = make_ws(const_cast<void*>(d_workspace), L);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_us, ws.pending, sizeof(int32_t) * (size_t)ctx->n_cand, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(stream));
     return SDSM_OK;
 }

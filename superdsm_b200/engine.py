@@ -164,9 +164,19 @@ class Engine(object):
     def solver_stats(self, ws=None):
         """Counters of the persistent solver kernel of the last batch (synchronises): see ``sdsm_solver_stats``."""
         if ws is None: ws = self._last[2]
-        st = np.zeros(16, dtype=np.uint64)
+        st = np.zeros(32, dtype=np.uint64)
         self._check(self.lib.sdsm_solver_stats(self.ctx, ws.data_ptr(), st.ctypes.data, self.stream.cuda_stream))
-        return {k: int(st[i]) for i, k in enumerate(self.STAT_NAMES)}
+        out = {k: int(st[i]) for i, k in enumerate(self.STAT_NAMES)}
+        for j, kind in enumerate(('poly_f', 'poly_h', 'xi_f', 'xi_h')):
+            out['cyc_' + kind], out['n_' + kind] = int(st[16 + j]), int(st[20 + j])
+        return out
+
+    def finish_times_us(self, ws=None, n=None):
+        """Per-candidate finish time of the last batch, microseconds after the solver kernel started (synchronises)."""
+        if ws is None: ws, n = self._last[2], len(self._last[3])
+        out = np.zeros(n, dtype=np.int32)
+        self._check(self.lib.sdsm_finish_times(self.ctx, ws.data_ptr(), out.ctypes.data, self.stream.cuda_stream))
+        return out
 
     def _check_solved(self, ws, n):
         """Raises if the watchdog of the persistent solver fired or a candidate did not finish."""
