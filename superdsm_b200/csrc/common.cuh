@@ -95,7 +95,9 @@ struct WS {
     CInfo*    cinfo;       // [n_cand]
     CState*   cstate;      // [n_cand]
     EvalReq*  req;         // [n_cand]
-    double*   scrG;        // [C * 32]   per-cell value + local gradient of the last evaluation
+    double*   scrG;        // [C * 32]   per-cell value ([31]) + theta gradient ([0..5]) of the last evaluation
+    double*   xig;         // [C * 25]   xi gradient of the last evaluation: entry [j * 25 + s] = contribution to grid point j of the
+                           //            cell at neighbour position s of j's cell (zero where there is none; zeroed per batch)
     double*   scrH;        // [C * 496]  per-cell packed local Hessian of the last evaluation
     double*   vecs;        // [V]      NVEC vectors of length 6 + cell_cap per candidate
     double*   mats;        // [M]      H, H2 (N x N) and the packed Cholesky factor per candidate
@@ -111,7 +113,7 @@ struct WS {
 struct Layout {
     size_t total;
     size_t o_pix_y, o_pix_rc, o_pix_s, o_pix_dist, o_gval, o_cell_start, o_cell_amask, o_cellmap, o_grid_rc, o_grid_tmp, o_cell_list,
-           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_scrH, o_vecs, o_mats, o_q_task, o_q_seq, o_pending, o_counters;
+           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_xig, o_scrH, o_vecs, o_mats, o_q_task, o_q_seq, o_pending, o_counters;
     int64_t C, q_cap;
     int32_t n_cand;
 };
@@ -143,6 +145,7 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_cstate = take(sizeof(CState) * (size_t)n_cand);
     L.o_req = take(sizeof(EvalReq) * (size_t)n_cand);
     L.o_scrG = take(sizeof(double) * SCRG * C);
+    L.o_xig = take(sizeof(double) * NSLOT * C);
     L.o_scrH = take(sizeof(double) * SCRH * C);
     L.o_vecs = take(sizeof(double) * V);
     L.o_mats = take(sizeof(double) * M);
@@ -181,6 +184,7 @@ inline WS make_ws(void* base, const Layout& L)
     w.cstate = (CState*)(b + L.o_cstate);
     w.req = (EvalReq*)(b + L.o_req);
     w.scrG = (double*)(b + L.o_scrG);
+    w.xig = (double*)(b + L.o_xig);
     w.scrH = (double*)(b + L.o_scrH);
     w.vecs = (double*)(b + L.o_vecs);
     w.mats = (double*)(b + L.o_mats);

@@ -26,7 +26,7 @@ struct Prob {
     const double* xr; const double* xc;
     double scale_cp, alpha, eps, tol;
     double *V, *H, *H2, *Lg;
-    const double *scrG, *scrH;
+    const double *scrG, *scrH, *xig;
     int sub;
 };
 
@@ -68,6 +68,7 @@ __device__ __forceinline__ void setup_problem(Prob& P, const Par& par, const sds
     const size_t nn = (size_t)P.ld * P.ld;
     P.H = ws.mats + cd.mat_off; P.H2 = P.H + nn; P.Lg = P.H2 + nn;
     P.scrG = ws.scrG + (size_t)cd.cell_off * SCRG; P.scrH = ws.scrH + (size_t)cd.cell_off * SCRH;
+    P.xig = ws.xig + (size_t)cd.cell_off * NSLOT;
 }
 
 // slot index (0..24) of the cell at offset (da, db) from a cell, and the local index of that slot in the cell's vector
@@ -155,32 +156,19 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
         P.H[a * N + t] = v;
         P.H[t * N + a] = v;
     }
-    // (2) xi gradient: grid point j collects from the (up to 25) cells around its own; a warp per grid point, a lane per
-    //     cell, so that the dependent loads (cell -> mask -> scratch entry) of the 25 cells overlap; fixed reduction tree
-    {
-        const int lane = tid & 31, warp = tid >> 5;
-        for (int j = warp; j < m; j += BLOCK / 32) {
-            const uint32_t gp = P.grid[j];
-            const int ja = (int)(gp & 0xffffu) / P.sub, jb = (int)(gp >> 16) / P.sub;
-            double v = 0;
-            if (lane < NSLOT) {
-                const int da = lane / 5 - NC, db = lane % 5 - NC;
-                const int a = ja - da, b = jb - db;
-                if (a >= 0 && a < ch && b >= 0 && b < cw) {
-                    const int cell = a * cw + b;
-                    if (P.cstart[cell + 1] != P.cstart[cell]) {
-                        const int li = local_index(P.amask[cell], da, db);
-                        if (li >= 0) v = P.scrG[(size_t)cell * SCRG + li];
-                    }
-                }
-            }
-            double s = warp_sum(v);
-            if (lane == 0) {
-                const double xv = x[6 + j];
-                s += P.alpha * (xv / sqrt(xv * xv + P.eps));                      // dsm.py:350
-                g[6 + j] = sc * s;
-            }
-        }
+    // (2) xi gradient: the evaluation tasks left the contributions of the (up to 25) cells around grid point j in 25
+    //     contiguous slots (zero where there is no cell); fixed summation order
+    for (int j = tid; j < m; j += BLOCK) {
+        const double* r = P.xig + (size_t)j * NSLOT;
+        double v[NSLOT];
+#pragma unroll
+        for (int k = 0; k < NSLOT; ++k) v[k] = r[k];
+        double s = 0;
+#pragma unroll
+        for (int k = 0; k < NSLOT; ++k) s += v[k];
+        const double xv = x[6 + j];
+        s += P.alpha * (xv / sqrt(xv * xv + P.eps));                             // dsm.py:350
+        g[6 + j] = sc * s;
     }
     // the xi-theta and xi-xi blocks of the Hessian are assembled by the T_HG tasks (one warp per grid point), before this task runs
     __syncthreads();

@@ -164,13 +164,13 @@ __device__ __forceinline__ void stage_chunk(char* stage, const double* __restric
     }
 }
 
-__device__ __forceinline__ void cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
-                                             int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
-                                             const double* x, double tol, char* stages, const double* XI, double* sg)
+// Returns, in lane e, the cell's local gradient entry e (e < 6 + na), and in lane 31 its value.
+__device__ __forceinline__ double cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
+                                               int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
+                                               const double* x, double tol, char* stages, const double* XI)
 {
     const int lane = threadIdx.x & 31;
     const double th[6] = {x[0], x[1], x[2], x[3], x[4], x[5]};
-    const int L = 6 + na;
     double acc[32];                                   // acc[e] = local gradient entry e, acc[31] = value
 #pragma unroll
     for (int k = 0; k < 32; ++k) acc[k] = 0;
@@ -218,8 +218,7 @@ __device__ __forceinline__ void cell_value_grad(const double* __restrict__ py, c
         slot_in = (slot_in + 1 == STAGES) ? 0 : slot_in + 1;
     }
     cp_async_wait<0>();
-    const double tot = warp_sum_transposed(acc);     // lane: local gradient entry, 31: value
-    sg[lane] = (lane == 31 || lane < L) ? tot : 0.0;
+    return warp_sum_transposed(acc);                 // lane: local gradient entry, 31: value
 }
 
 __device__ __forceinline__ void cell_hessian(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
@@ -299,7 +298,7 @@ template <bool HESS>
 __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
                                              int npix, uint32_t am, const double* __restrict__ xr, const double* __restrict__ xc,
                                              const double* x, double tol, double* Tt, const int* slotj,
-                                             double* sg, double* sh)
+                                             double* sg, double* xig, double* sh)
 {
     const int lane = threadIdx.x & 31;
     double* XI = Tt + XI_OFF;
@@ -307,7 +306,15 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
     __syncwarp();
     if (lane < na) XI[lane] = x[6 + slotj[lane]];     // the xi values this cell sees
     __syncwarp();
-    cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI, sg);
+    const double tot = cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI);
+    if (lane < 6 || lane == 31) sg[lane] = tot;
+    else if (lane < 6 + na) {
+        // xi gradient: straight into the slot that grid point slotj[a] keeps for this cell (seen from the grid point's cell,
+        // this cell sits at the mirrored neighbour position), so that the control task sums 25 contiguous numbers per
+        // grid point instead of chasing cell -> mask -> scratch entry
+        const int a = lane - 6;
+        xig[(size_t)slotj[a] * NSLOT + (NSLOT - 1 - nth_set_bit(am, a))] = tot;
+    }
     __syncwarp();
     if (HESS) cell_hessian(py, prc, gcell, npix, na, xr, xc, x, tol, Tt, XI, sh);
     __syncwarp();
@@ -372,8 +379,9 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     }
     __syncwarp();
     const float* gcell = ws.gval + (size_t)NSLOT * (pix_off + st);
-    if (rq.want_h) eval_cell_xi<true>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, sh);
-    else eval_cell_xi<false>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, sh);
+    double* xig = ws.xig + (size_t)cell_off * NSLOT;
+    if (rq.want_h) eval_cell_xi<true>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
+    else eval_cell_xi<false>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
 }
 
 }  // namespace sdsm

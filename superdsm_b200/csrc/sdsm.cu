@@ -213,6 +213,7 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     WS ws = make_ws(d_workspace, L);
     CUDA_TRY(ctx, cudaMemsetAsync(ws.cstate, 0, sizeof(CState) * (size_t)n_cand, stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.xig, 0, sizeof(double) * NSLOT * (size_t)L.C, stream));
     CUDA_TRY(ctx, cudaMemsetAsync(out->d_fgmask, 0, (size_t)plan->fgmask_len, stream));
 
     const int pack_grid = n_cand < 8 * ctx->sm_count ? n_cand : 8 * ctx->sm_count;
