@@ -135,7 +135,7 @@ k_pack(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const 
             }
         }
         __syncthreads();
-        // the non-empty cells, in cell order: the work items of k_eval
+        // the non-empty cells: the work items of the evaluation tasks
         {
             int32_t* pos = (int32_t*)(ws.grid_tmp + cd.cell_off);          // free until k_grid
             int32_t* clist = ws.cell_list + cd.cell_off;
@@ -144,6 +144,18 @@ k_pack(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const 
             const int n_ne = excl_scan_i32<BLOCK>(pos, ncells + 1, s_scan);
             for (int i = tid; i < ncells; i += BLOCK) if (cstart[i] > 0) clist[pos[i]] = i;
             if (tid == 0) ws.cinfo[c].n_ne = n_ne;
+            __syncthreads();
+            // ... ordered by their number of 32-pixel chunks, largest first (stable): the cells one evaluation task hands
+            // to the warps of a CTA then take about the same time, and the partly filled cells of the region's rim end up
+            // together in the last tasks
+            for (int i = tid; i < n_ne; i += BLOCK) {
+                const int key = (cstart[clist[i]] + 31) >> 5;
+                int rank = 0;
+                for (int j = 0; j < n_ne; ++j) { const int kj = (cstart[clist[j]] + 31) >> 5; rank += (kj > key || (kj == key && j < i)) ? 1 : 0; }
+                pos[rank] = clist[i];
+            }
+            __syncthreads();
+            for (int i = tid; i < n_ne; i += BLOCK) clist[i] = pos[i];
         }
         __syncthreads();
         excl_scan_i32<BLOCK>(cstart, ncells + 1, s_scan);

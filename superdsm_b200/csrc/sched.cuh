@@ -7,8 +7,8 @@
 // Candidates with few cells run their whole chain inside one CTA (no queue hop between the links).
 //
 // Nothing ever blocks on another task: a task only waits for a queue slot whose previous occupant has already been
-// claimed by a consumer.  The kernel ends when every candidate has reported completion (Q_DONE == n_target), or when the
-// watchdog fires (Q_ABORT; sdsm_solver_stats reports it).
+// claimed by a consumer.  The kernel ends when every candidate has reported completion (H_DONE == n_target), or when the
+// watchdog fires (H_ABORT; sdsm_solver_stats reports it).
 #pragma once
 #include "common.cuh"
 #include "eval.cuh"
@@ -28,6 +28,7 @@ struct SolveArgs {
     int lcap;                // shared-memory capacity (doubles) for a packed Cholesky factor
     int solo_cells;          // candidates with at most this many non-empty cells run their chain inside one CTA
     int task_small_cells;    // candidates with at most this many non-empty cells get one cell per warp (EVAL_WARPS per task)
+    int hi_evals;            // a candidate that has needed more evaluations of F than this becomes urgent (ring 1)
     unsigned long long timeout_ns;   // watchdog: idle CTAs abort the kernel after this long
     double* trace;           // diagnostics (STG_TRACE) or nullptr
 };
@@ -39,19 +40,33 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
     return t;
 }
 
-// Seeds the queue: slot i holds the control task that starts candidate order[i] (most expensive first).
-__global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, int single)
+// Seeds the queues: the control tasks that start the candidates order[0 .. n_first) (most expensive first); the first n_hi
+// of them are urgent from the start (ring 1), the others go to ring 0.
+__global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, int single, int n_hi)
 {
     const uint32_t q_cap = ws.q_mask + 1u;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < q_cap; i += gridDim.x * blockDim.x) {
-        if ((int)i < n_first) {
-            ws.q_task[i] = make_uint2(((uint32_t)T_CTRL << T_SHIFT) | (uint32_t)(order ? order[i] : single), 0u);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 2u * q_cap; i += gridDim.x * blockDim.x) {
+        ws.q_ev[i] = (int)i < n_first ? i + 1u : i;                      // one arrival event per seeded task
+        if (i >= q_cap) continue;
+        if ((int)i < n_hi) {
+            ws.q_task[q_cap + i] = make_uint2(((uint32_t)T_CTRL << T_SHIFT) | (uint32_t)order[i], 0u);
+            ws.q_seq[q_cap + i] = i + 1u;
+        } else ws.q_seq[q_cap + i] = i;
+        if ((int)i < n_first - n_hi) {
+            ws.q_task[i] = make_uint2(((uint32_t)T_CTRL << T_SHIFT) | (uint32_t)(order ? order[n_hi + i] : single), 0u);
             ws.q_seq[i] = i + 1u;
         } else ws.q_seq[i] = i;
     }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_first; i += gridDim.x * blockDim.x)
+        ws.prio[order ? order[i] : single] = i < n_hi ? 1 : 0;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         for (int k = 0; k < N_COUNTERS; ++k) ws.counters[k] = 0ull;
-        ws.counters[Q_TAIL] = (unsigned long long)n_first;
+        for (int k = 0; k < N_HOT * HOT_STRIDE; ++k) ws.hot[k] = 0ull;
+        *hot(ws, H_TAIL_LO) = (unsigned long long)(n_first - n_hi);
+        *hot(ws, H_TAIL_HI) = (unsigned long long)n_hi;
+        *hot(ws, H_EV_TAIL) = (unsigned long long)n_first;
+        *hot(ws, H_AVAIL_LO) = (unsigned long long)(n_first - n_hi);
+        *hot(ws, H_AVAIL_HI) = (unsigned long long)n_hi;
         ws.counters[Q_T0] = globaltimer_ns();
     }
 }
@@ -81,8 +96,9 @@ __device__ __forceinline__ void finish_stage_task(const WS& ws, uint32_t type, i
     const int next = *s_flag;
     __syncthreads();                                         // thread 0 reuses s_flag as soon as it is back in the task loop
     if (next == 0) return;
-    if (next == 1) { if (threadIdx.x == 0) q_push_one(ws, T_CTRL, (uint32_t)c, 0u); }
-    else q_push_range<BLOCK>(ws, T_HG, (uint32_t)c, next - 1, HG_WARPS, s_base);
+    const int ring = ws.prio[c];
+    if (next == 1) { if (threadIdx.x == 0) q_push_one(ws, ring, T_CTRL, (uint32_t)c, 0u); }
+    else q_push_range<BLOCK>(ws, ring, T_HG, (uint32_t)c, next - 1, HG_WARPS, s_base);
 }
 
 __global__ void __launch_bounds__(SOLVE_BLOCK, 2)
@@ -93,7 +109,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     __shared__ int s_slotj[EVAL_WARPS * 32];
     __shared__ uint2 s_task;
     __shared__ int s_flag, s_next;
-    __shared__ unsigned long long s_base;
+    __shared__ unsigned long long s_base[2];
     const int tid = threadIdx.x;
     const unsigned long long n_target = (unsigned long long)args.n_target;
     unsigned long long t_start = 0, cyc[4] = {0, 0, 0, 0}, cnt[3] = {0, 0, 0}, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0};
@@ -101,11 +117,12 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     const long long c_begin = clock64();
 
     unsigned n_popped = 0;
+    unsigned long long n_promoted = 0;
     for (;;) {
         if (tid == 0) {
             const long long c0 = clock64();
             uint2 task;
-            if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) atomicExch(ws.counters + Q_ABORT, 1ull);
+            if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) atomicExch(hot(ws, H_ABORT), 1ull);
             const bool ok = q_pop(ws, n_target, args.timeout_ns, t_start, &task);
             cyc[3] += (unsigned long long)(clock64() - c0);
             s_task = task;
@@ -123,21 +140,21 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         if (type == T_EVAL) {
             eval_task(par, cands, ws, c, (int)task.y, (double*)smem_solve, s_slotj, &s_next);
             if (tid == 0) { const EvalReq rq = ws.req[c]; const int kind = (rq.use_xi ? 2 : 0) + (rq.want_h ? 1 : 0); kcyc[kind] += (unsigned long long)(clock64() - c0); kcnt[kind] += 1; }
-            finish_stage_task<BLOCK>(ws, T_EVAL, c, &s_flag, &s_base);
+            finish_stage_task<BLOCK>(ws, T_EVAL, c, &s_flag, s_base);
         } else if (type == T_HG) {
             hg_task(par, cands, ws, c, (int)task.y, (double*)smem_solve);
-            finish_stage_task<BLOCK>(ws, T_HG, c, &s_flag, &s_base);
+            finish_stage_task<BLOCK>(ws, T_HG, c, &s_flag, s_base);
         } else {
             const sdsm_cand cd = cands[c];
             const CInfo ci = ws.cinfo[c];
             const bool solo = ci.n_ne <= args.solo_cells;
             for (unsigned link = 1;; ++link) {
                 if ((link & 63u) == 0) {                    // watchdog of a chain that never leaves this CTA
-                    if (tid == 0) s_flag = (globaltimer_ns() - t_start > args.timeout_ns || ld_relaxed_u64(ws.counters + Q_ABORT)) ? 1 : 0;
+                    if (tid == 0) s_flag = (globaltimer_ns() - t_start > args.timeout_ns || q_aborted(ws)) ? 1 : 0;
                     __syncthreads();
                     const bool stop = s_flag != 0;
                     __syncthreads();
-                    if (stop) { if (tid == 0) atomicExch(ws.counters + Q_ABORT, 1ull); break; }
+                    if (stop) { if (tid == 0) atomicExch(hot(ws, H_ABORT), 1ull); break; }
                 }
                 const bool big = (ws.cstate[c].use_xi ? 6 + ci.m : 6) > SMALL_N_MAX;
                 Sm sm;
@@ -148,7 +165,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     if (tid == 0) {
                         ws.pending[c] = (int32_t)((globaltimer_ns() - ws.counters[Q_T0]) / 1000ull);   // diagnostics: finish time, us
                         __threadfence();
-                        atomicAdd(ws.counters + Q_DONE, 1ull);
+                        atomicAdd(hot(ws, H_DONE), 1ull);
                     }
                     break;
                 }
@@ -157,8 +174,13 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                 if (!solo) {
                     // publishing is the LAST thing a control task does: the candidate's next control task may start on another
                     // SM as soon as the evaluations have finished
-                    if (tid == 0) ws.pending[c] = n_tasks;
-                    q_push_range<BLOCK>(ws, T_EVAL, (uint32_t)c, n_tasks, cpt, &s_base);
+                    if (tid == 0) {
+                        ws.pending[c] = n_tasks;
+                        // a chain that turns out long becomes urgent: it would otherwise finish long after the bulk of the batch
+                        if (!ws.prio[c]) { const CState* S = ws.cstate + c; if (S->nf + S->nh > args.hi_evals) { ws.prio[c] = 1; ++n_promoted; } }
+                    }
+                    __syncthreads();
+                    q_push_range<BLOCK>(ws, ws.prio[c], T_EVAL, (uint32_t)c, n_tasks, cpt, s_base);
                     break;
                 }
                 // the whole chain in this CTA: evaluate here and go on
@@ -181,6 +203,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         atomicAdd(ws.counters + Q_N_CTRL, cnt[T_CTRL]);   atomicAdd(ws.counters + Q_N_EVAL, cnt[T_EVAL]);
         atomicAdd(ws.counters + Q_N_HG, cnt[T_HG]);       atomicAdd(ws.counters + Q_CYC_TOTAL, (unsigned long long)(clock64() - c_begin));
         for (int k = 0; k < 4; ++k) { atomicAdd(ws.counters + Q_CYC_KIND + k, kcyc[k]); atomicAdd(ws.counters + Q_N_KIND + k, kcnt[k]); }
+        if (n_promoted) atomicAdd(ws.counters + Q_N_PROMOTED, n_promoted);
     }
 }
 

@@ -31,6 +31,8 @@ struct sdsm_ctx {
     int solo_cells = 8;                      // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
     int task_small_cells = 512;              // SDSM_TASK_SMALL_CELLS: candidates up to this many cells get one cell per warp
     double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
+    double hi_frac = 0.08;                   // SDSM_HI_FRAC: this share of the batch (the most expensive candidates) is urgent from the start
+    int hi_evals = 400;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     std::string err;
 };
 
@@ -68,6 +70,8 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     if (const char* e = getenv("SDSM_SOLO_CELLS")) ctx->solo_cells = atoi(e);
     if (const char* e = getenv("SDSM_TASK_SMALL_CELLS")) ctx->task_small_cells = atoi(e);
     if (const char* e = getenv("SDSM_TIMEOUT_S")) ctx->timeout_s = atof(e);
+    if (const char* e = getenv("SDSM_HI_FRAC")) ctx->hi_frac = atof(e);
+    if (const char* e = getenv("SDSM_HI_EVALS")) ctx->hi_evals = atoi(e);
     return SDSM_OK;
 }
 
@@ -185,12 +189,16 @@ static int check_plan(sdsm_ctx* ctx, int32_t n_cand, size_t workspace_bytes, Lay
 static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_cands, const WS& ws, const sdsm_out& out, int lcap,
                       const int32_t* d_order, int n_first, int single, double* trace)
 {
-    k_seed<<<64, 256, 0, stream>>>(ws, d_order, n_first, single);
+    // urgent from the start: the candidates at the head of the processing order (most expensive first); 0 for single solves
+    int n_hi = d_order ? (int)(ctx->hi_frac * n_first) : 0;
+    if (n_hi > n_first) n_hi = n_first;
+    k_seed<<<64, 256, 0, stream>>>(ws, d_order, n_first, single, n_hi);
     SolveArgs args{};
     args.n_target = n_first;
     args.lcap = lcap;
     args.solo_cells = ctx->solo_cells;
     args.task_small_cells = ctx->task_small_cells;
+    args.hi_evals = ctx->hi_evals;
     args.timeout_ns = (unsigned long long)(ctx->timeout_s * 1e9);
     args.trace = trace;
     const int grid = ctx->sm_count * ctx->solve_ctas_per_sm;
@@ -307,8 +315,13 @@ extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_
     WS ws = make_ws(const_cast<void*>(d_workspace), L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    uint64_t h_hot[N_HOT * HOT_STRIDE];
     CUDA_TRY(ctx, cudaMemcpyAsync(h_stats, ws.counters, sizeof(uint64_t) * N_COUNTERS, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_hot, ws.hot, sizeof(h_hot), cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
+    h_stats[Q_HEAD] = h_hot[H_HEAD_LO * HOT_STRIDE]; h_stats[Q_TAIL] = h_hot[H_TAIL_LO * HOT_STRIDE];
+    h_stats[Q_HEAD_HI] = h_hot[H_HEAD_HI * HOT_STRIDE]; h_stats[Q_TAIL_HI] = h_hot[H_TAIL_HI * HOT_STRIDE];
+    h_stats[Q_DONE] = h_hot[H_DONE * HOT_STRIDE]; h_stats[Q_ABORT] = h_hot[H_ABORT * HOT_STRIDE];
     return SDSM_OK;
 }
 
