@@ -254,14 +254,16 @@ def run_gpu(args):
             'e2e': {'value': cand_total * e2e_steps / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
                     'd2h_bytes_per_step': int(d2h), 'includes': 'host EDT + descriptors, pinned H2D of y/atoms/descriptors, solve, D2H, Object materialisation'},
             'gpu_launches': int(gpu_launches),
-            'roofline': {'kernel': 'k_solve (persistent solver: evaluation, Hessian-row and control tasks from a device-side queue)', 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak,
+            'roofline': {'kernel': 'k_solve (persistent solver: control CTAs + evaluation warps fed by device-side priority queues)', 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak,
                          'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': None, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': alg_bytes,
                          'fp64': {'achieved_gflops': alg_flops / (solver_ms * 1e-3) / 1e9, 'peak_gflops': dfma,
                                   'frac': alg_flops / (solver_ms * 1e-3) / 1e9 / dfma, 'peak_source': 'register-resident DFMA loop measured in this run',
                                   'note': 'the kernel is FP64-pipe/latency bound, not HBM bound: its working set stays in L2/shared memory (DESIGN.md)'}},
             'clocks': clocks,
-            'solver': {k: stats[k] for k in ('n_eval', 'n_hrows', 'n_ctrl')} | {'cta_time_share': {k[4:]: round(stats[k] / max(stats['cyc_total'], 1), 4) for k in ('cyc_eval', 'cyc_hrows', 'cyc_ctrl', 'cyc_idle')}},
+            'solver': {k: stats[k] for k in ('n_eval', 'n_hrows', 'n_ctrl', 'n_promoted')} | {
+                'control_cta_time_share': {k[4:]: round(stats[k] / max(stats['cyc_total'], 1), 4) for k in ('cyc_ctrl', 'cyc_idle')},
+                'evaluation_warp_time_share': {k[4:]: round(stats[k] / max(stats['cyc_wtotal'], 1), 4) for k in ('cyc_eval', 'cyc_hrows', 'cyc_widle')}},
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1

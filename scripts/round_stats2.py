@@ -12,8 +12,9 @@ eng.set_params(w['dsm_cfg'])
 for _ in range(2):
     t0 = time.perf_counter(); res = eng.solve(w['footprints']); dt = time.perf_counter() - t0
 print('solve', dt)
-st = eng.solver_stats(); tot = max(st['cyc_total'], 1)
-print({k: round(st[k] / tot, 3) for k in ('cyc_eval', 'cyc_hrows', 'cyc_ctrl', 'cyc_idle')}, {k: st[k] for k in st if k.startswith('n_')})
+st = eng.solver_stats(); tot = max(st['cyc_total'], 1); wtot = max(st['cyc_wtotal'], 1)
+print('ctrl CTAs: busy %.3f idle %.3f | eval warps: eval %.3f hrows %.3f idle %.3f' % (st['cyc_ctrl'] / tot, st['cyc_idle'] / tot, st['cyc_eval'] / wtot, st['cyc_hrows'] / wtot, st['cyc_widle'] / wtot),
+      {k: st[k] for k in st if k.startswith('n_')}, 'urgent', st['q_tail_hi'], 'of', st['q_tail'])
 print({k: (st['cyc_' + k] / max(st['n_' + k], 1)) for k in ('poly_f', 'poly_h', 'xi_f', 'xi_h')})
 info = res.info; ft = eng.finish_times_us().astype(float); n = res.cands['n']; ev = (info[:, 6] + info[:, 7]).astype(float)
 print('finish pct 10/25/50/75/90/99/100', np.percentile(ft, [10, 25, 50, 75, 90, 99, 100]))

@@ -1,5 +1,6 @@
 """Times the evaluation sweeps (value+gradient, +Hessian, Hessian rows) over the whole bench workload, outside the solver."""
 import sys
+sys.path.insert(0, ".")
 import numpy as np
 from superdsm_b200 import synth
 from superdsm_b200.objects import get_engine

@@ -35,6 +35,15 @@ constexpr int BIG_BLOCK  = SOLVE_BLOCK;
 constexpr int N_COUNTERS = 32;
 constexpr int NVEC       = 12;    // N-vectors of the interior-point solver
 
+// one task queue: two rings (0: normal, 1: urgent) of `mask + 1` slots each, one ring of 2 (mask + 1) arrival events
+struct Queue {
+    uint2*    task;        // [2 cap]  x = type << 28 | candidate, y = first item of the task
+    uint32_t* seq;         // [2 cap]  slot sequence numbers
+    uint32_t* ev;          // [2 cap]  arrival events (sequence numbers only)
+    unsigned long long* hot;        // [N_HOT * HOT_STRIDE] head / tail / availability counters, one cache line each
+    uint32_t  mask, ev_mask;
+};
+
 struct Img { const double* y; const int32_t* atoms; int32_t H, W; };
 
 struct Par {
@@ -72,7 +81,7 @@ struct EvalReq {
     const double* x;       // point to evaluate (6 + m values, or 6)
     double hfac;           // factor of the Hessian rows the T_HG tasks write: z * scale / n (objects.py:380), or 1 (diagnostics)
     int32_t want_h, use_xi;
-    int32_t cpt, pad;      // non-empty cells per evaluation task of this request (EVAL_WARPS .. EVAL_CELLS)
+    int32_t cpt, cpw;      // non-empty cells per CTA-wide evaluation task (chains that stay in one CTA, diagnostics) / per warp item
 };
 
 // Workspace carved out of the caller's buffer.  Per-pixel / per-cell / per-table arrays are indexed with the
@@ -101,24 +110,21 @@ struct WS {
     double*   scrH;        // [C * 496]  per-cell packed local Hessian of the last evaluation
     double*   vecs;        // [V]      NVEC vectors of length 6 + cell_cap per candidate
     double*   mats;        // [M]      H, H2 (N x N) and the packed Cholesky factor per candidate
-    // device-side scheduler (sched.cuh): bounded multi-producer / multi-consumer ring of tasks
-    uint2*    q_task;      // [2 q_cap]  two rings (0: normal, 1: urgent); x = type << 28 | candidate, y = first item of the task
-    uint32_t* q_seq;       // [2 q_cap]  slot sequence numbers (slot i is free for ticket t when seq == t, full when seq == t + 1)
-    int32_t*  pending;     // [n_cand] tasks of the candidate's current stage that have not finished yet
+    // device-side scheduler (sched.cuh): qc = control tasks (consumed by whole CTAs), qe = evaluation and Hessian-row items
+    // (consumed by single warps)
+    Queue     qc, qe;
+    int32_t*  pending;     // [n_cand] items of the candidate's current stage that have not finished yet
     int32_t*  prio;        // [n_cand] ring the candidate's tasks go to (1: its chain is on the critical path of the batch)
-    uint32_t* q_ev;        // [2 q_cap]  arrival events (sequence numbers only)
-    unsigned long long* hot;        // [N_HOT * HOT_STRIDE] the queue's head / tail counters, done and abort, one cache line each
-    unsigned long long* counters;   // [N_COUNTERS]  Q_HEAD, Q_TAIL, Q_DONE, then busy-cycle / task statistics (sched.cuh)
-    uint32_t  q_mask;      // q_cap - 1 (power of two)
-    uint32_t  ev_mask;     // 2 q_cap - 1
+    unsigned long long* glob;       // [N_GLOB * HOT_STRIDE] candidates done / abort flag, one cache line each
+    unsigned long long* counters;   // [N_COUNTERS]  busy-cycle / task statistics (sched.cuh)
     int32_t   n_cand;
 };
 
 struct Layout {
     size_t total;
     size_t o_pix_y, o_pix_rc, o_pix_s, o_pix_dist, o_gval, o_cell_start, o_cell_amask, o_cellmap, o_grid_rc, o_grid_tmp, o_cell_list,
-           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_xig, o_scrH, o_vecs, o_mats, o_q_task, o_q_seq, o_pending, o_prio, o_q_ev, o_hot, o_counters;
-    int64_t C, q_cap;
+           o_xtab, o_inv, o_fwd, o_cinfo, o_cstate, o_req, o_scrG, o_xig, o_scrH, o_vecs, o_mats, o_qc_task, o_qc_seq, o_qc_ev, o_qc_hot, o_qe_task, o_qe_seq, o_qe_ev, o_qe_hot, o_pending, o_prio, o_glob, o_counters;
+    int64_t C, qc_cap, qe_cap;
     int32_t n_cand;
 };
 
@@ -153,17 +159,24 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_scrH = take(sizeof(double) * SCRH * C);
     L.o_vecs = take(sizeof(double) * V);
     L.o_mats = take(sizeof(double) * M);
-    int64_t q_cap = 1024;
-    while (q_cap < K + 1024) q_cap <<= 1;
-    L.o_q_task = take(sizeof(uint2) * 2 * q_cap);
-    L.o_q_seq = take(sizeof(uint32_t) * 2 * q_cap);
+    int64_t qc_cap = 1024, qe_cap = 1024;
+    while (qc_cap < n_cand + 1024) qc_cap <<= 1;
+    while (qe_cap < K + 1024) qe_cap <<= 1;
+    L.o_qc_task = take(sizeof(uint2) * 2 * qc_cap);
+    L.o_qc_seq = take(sizeof(uint32_t) * 2 * qc_cap);
+    L.o_qc_ev = take(sizeof(uint32_t) * 2 * qc_cap);
+    L.o_qc_hot = take(sizeof(unsigned long long) * 8 * 16);
+    L.o_qe_task = take(sizeof(uint2) * 2 * qe_cap);
+    L.o_qe_seq = take(sizeof(uint32_t) * 2 * qe_cap);
+    L.o_qe_ev = take(sizeof(uint32_t) * 2 * qe_cap);
+    L.o_qe_hot = take(sizeof(unsigned long long) * 8 * 16);
     L.o_pending = take(sizeof(int32_t) * (size_t)n_cand);
     L.o_prio = take(sizeof(int32_t) * (size_t)n_cand);
-    L.o_q_ev = take(sizeof(uint32_t) * 2 * q_cap);
-    L.o_hot = take(sizeof(unsigned long long) * 10 * 16);  // N_HOT * HOT_STRIDE
+    L.o_glob = take(sizeof(unsigned long long) * 2 * 16);
     L.o_counters = take(sizeof(unsigned long long) * N_COUNTERS);
     L.C = C;
-    L.q_cap = q_cap;
+    L.qc_cap = qc_cap;
+    L.qe_cap = qe_cap;
     L.n_cand = n_cand;
     L.total = o;
     return L;
@@ -195,15 +208,14 @@ inline WS make_ws(void* base, const Layout& L)
     w.scrH = (double*)(b + L.o_scrH);
     w.vecs = (double*)(b + L.o_vecs);
     w.mats = (double*)(b + L.o_mats);
-    w.q_task = (uint2*)(b + L.o_q_task);
-    w.q_seq = (uint32_t*)(b + L.o_q_seq);
+    w.qc.task = (uint2*)(b + L.o_qc_task); w.qc.seq = (uint32_t*)(b + L.o_qc_seq); w.qc.ev = (uint32_t*)(b + L.o_qc_ev);
+    w.qc.hot = (unsigned long long*)(b + L.o_qc_hot); w.qc.mask = (uint32_t)(L.qc_cap - 1); w.qc.ev_mask = (uint32_t)(2 * L.qc_cap - 1);
+    w.qe.task = (uint2*)(b + L.o_qe_task); w.qe.seq = (uint32_t*)(b + L.o_qe_seq); w.qe.ev = (uint32_t*)(b + L.o_qe_ev);
+    w.qe.hot = (unsigned long long*)(b + L.o_qe_hot); w.qe.mask = (uint32_t)(L.qe_cap - 1); w.qe.ev_mask = (uint32_t)(2 * L.qe_cap - 1);
     w.pending = (int32_t*)(b + L.o_pending);
     w.prio = (int32_t*)(b + L.o_prio);
-    w.q_ev = (uint32_t*)(b + L.o_q_ev);
-    w.hot = (unsigned long long*)(b + L.o_hot);
-    w.ev_mask = (uint32_t)(2 * L.q_cap - 1);
+    w.glob = (unsigned long long*)(b + L.o_glob);
     w.counters = (unsigned long long*)(b + L.o_counters);
-    w.q_mask = (uint32_t)(L.q_cap - 1);
     w.n_cand = L.n_cand;
     return w;
 }
@@ -285,30 +297,33 @@ __device__ __forceinline__ bool fp_member(int lab, const int32_t* fp, int n)
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Device-side task queue: two bounded MPMC rings of tasks (ring 1 = urgent, served first) behind one ring of arrival
-// events.  A candidate's tasks all go to the ring ws.prio[c] names: the candidates whose chains bound the batch's makespan
-// (the largest regions, and chains that turn out long) are not held up behind the bulk of the batch.
+// Device-side task queues (struct Queue): two bounded MPMC rings of tasks (ring 1 = urgent, served first) behind one ring
+// of arrival events.  A candidate's tasks all go to the ring ws.prio[c] names: the candidates whose chains bound the
+// batch's makespan (the largest regions, and chains that turn out long) are not held up behind the bulk of the batch.
 //
-// Every ring uses 64-bit tickets and per-slot sequence numbers: slot t & q_mask is free for the producer of ticket t when
+// Every ring uses 64-bit tickets and per-slot sequence numbers: slot t & mask is free for the producer of ticket t when
 // its sequence number equals (uint32) t, and full for the consumer of ticket t when it equals (uint32) t + 1; the consumer
 // hands it on with t + capacity.  The rings are sized above the number of tasks that can be in flight (sdsm_plan_batch),
 // so producers only ever wait for a consumer that has claimed its ticket and is about to read the slot.
 //
-// A producer publishes the task in its ring first and then one arrival event.  An idle consumer takes an event ticket and
-// sleeps on ITS OWN event slot (no shared line is polled); once the event is there, at least one task is waiting for it
-// in one of the rings -- not necessarily the one whose arrival woke it up -- and it takes the oldest urgent task if there
-// is one, else the oldest normal task.
-// The hot counters sit on cache lines of their own (ws.hot, stride HOT_STRIDE).
+// A producer publishes the task in its ring first, raises the ring's availability count, and then publishes one arrival
+// event.  An idle consumer takes an event ticket and sleeps on ITS OWN event slot (no shared line is polled); once the
+// event is there, at least one task is waiting for it in one of the rings -- not necessarily the one whose arrival woke
+// it up -- and it takes the oldest urgent task if there is one, else the oldest normal task.  Everything is wait-free
+// (fetch-and-add only): compare-and-swap loops on the heads collapse when a few hundred consumers wake up together.
+// The hot counters sit on cache lines of their own (stride HOT_STRIDE).
 
 enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG, Q_CYC_CTRL, Q_CYC_IDLE, Q_N_EVAL, Q_N_HG, Q_N_CTRL, Q_CYC_TOTAL, Q_T0,
-       Q_CYC_KIND = 16 /* [4]: evaluation-task cycles by kind = use_xi * 2 + want_h */, Q_N_KIND = 20 /* [4]: tasks by kind */,
+       Q_CYC_WIDLE = 13 /* idle cycles of the evaluation warps */, Q_CYC_WTOTAL = 14 /* lifetime cycles of the evaluation warps */,
+       Q_CYC_KIND = 16 /* [4]: evaluation-item cycles by kind = use_xi * 2 + want_h */, Q_N_KIND = 20 /* [4]: items by kind */,
        Q_HEAD_HI = 24, Q_TAIL_HI = 25, Q_N_PROMOTED = 26 };
 constexpr int HOT_STRIDE = 16;   // unsigned long longs = 128 bytes
-enum { H_EV_HEAD = 0, H_EV_TAIL = 1, H_HEAD_LO = 2, H_TAIL_LO = 3, H_HEAD_HI = 4, H_TAIL_HI = 5, H_DONE = 6, H_ABORT = 7, H_AVAIL_LO = 8, H_AVAIL_HI = 9, N_HOT = 10 };
+enum { H_EV_HEAD = 0, H_EV_TAIL = 1, H_HEAD_LO = 2, H_TAIL_LO = 3, H_HEAD_HI = 4, H_TAIL_HI = 5, H_AVAIL_LO = 6, H_AVAIL_HI = 7, N_HOT = 8 };
+enum { G_DONE = 0, G_ABORT = 1, N_GLOB = 2 };
 enum { T_CTRL = 0, T_EVAL = 1, T_HG = 2 };
 constexpr uint32_t T_SHIFT = 28, T_CMASK = (1u << T_SHIFT) - 1u;
 
-__device__ __forceinline__ unsigned long long* hot(const WS& ws, int which) { return ws.hot + which * HOT_STRIDE; }
+__device__ __forceinline__ unsigned long long* hot(const Queue& q, int which) { return q.hot + which * HOT_STRIDE; }
 
 __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p)
 {
@@ -327,89 +342,108 @@ __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long
     return v;
 }
 
-__device__ __forceinline__ bool q_aborted(const WS& ws) { return ld_relaxed_u64(hot(ws, H_ABORT)) != 0ull; }
+__device__ __forceinline__ bool q_aborted(const WS& ws) { return ld_relaxed_u64(ws.glob + G_ABORT * HOT_STRIDE) != 0ull; }
+__device__ __forceinline__ void q_abort(const WS& ws) { atomicExch(ws.glob + G_ABORT * HOT_STRIDE, 1ull); }
+__device__ __forceinline__ unsigned long long q_done(const WS& ws) { return ld_relaxed_u64(ws.glob + G_DONE * HOT_STRIDE); }
 
 // one thread: publishes one task under ticket `t` of `ring` and its arrival event under event ticket `e`
-__device__ __forceinline__ void q_put(const WS& ws, int ring, unsigned long long t, unsigned long long e, uint32_t type, uint32_t c, uint32_t first)
+__device__ __forceinline__ void q_put(const WS& ws, const Queue& q, int ring, unsigned long long t, unsigned long long e, uint32_t type, uint32_t c, uint32_t first)
 {
-    const uint32_t slot = ((uint32_t)t & ws.q_mask) + (ring ? ws.q_mask + 1u : 0u);
-    while (ld_acquire_u32(ws.q_seq + slot) != (uint32_t)t) {
+    const uint32_t slot = ((uint32_t)t & q.mask) + (ring ? q.mask + 1u : 0u);
+    while (ld_acquire_u32(q.seq + slot) != (uint32_t)t) {
         if (q_aborted(ws)) return;
         __nanosleep(32);
     }
-    ws.q_task[slot] = make_uint2((type << T_SHIFT) | c, first);
-    st_release_u32(ws.q_seq + slot, (uint32_t)t + 1u);
+    q.task[slot] = make_uint2((type << T_SHIFT) | c, first);
+    st_release_u32(q.seq + slot, (uint32_t)t + 1u);
     __threadfence();
-    atomicAdd(hot(ws, ring ? H_AVAIL_HI : H_AVAIL_LO), 1ull);
-    const uint32_t es = (uint32_t)e & ws.ev_mask;
-    while (ld_acquire_u32(ws.q_ev + es) != (uint32_t)e) {
+    atomicAdd(hot(q, ring ? H_AVAIL_HI : H_AVAIL_LO), 1ull);
+    const uint32_t es = (uint32_t)e & q.ev_mask;
+    while (ld_acquire_u32(q.ev + es) != (uint32_t)e) {
         if (q_aborted(ws)) return;
         __nanosleep(32);
     }
-    st_release_u32(ws.q_ev + es, (uint32_t)e + 1u);
+    st_release_u32(q.ev + es, (uint32_t)e + 1u);
 }
 
 // whole CTA: publishes `count` tasks (type, c, first = k * stride for k < count).  Everything the CTA wrote before the call
 // is visible to the consumers of the tasks.  s_base: two unsigned long longs of shared memory.
 template <int BLOCK>
-__device__ __forceinline__ void q_push_range(const WS& ws, int ring, uint32_t type, uint32_t c, int count, int stride, unsigned long long* s_base)
+__device__ __forceinline__ void q_push_range(const WS& ws, const Queue& q, int ring, uint32_t type, uint32_t c, int count, int stride, unsigned long long* s_base)
 {
     __syncthreads();
     if (threadIdx.x == 0) {
-        s_base[0] = atomicAdd(hot(ws, ring ? H_TAIL_HI : H_TAIL_LO), (unsigned long long)count);
-        s_base[1] = atomicAdd(hot(ws, H_EV_TAIL), (unsigned long long)count);
+        __threadfence();
+        s_base[0] = atomicAdd(hot(q, ring ? H_TAIL_HI : H_TAIL_LO), (unsigned long long)count);
+        s_base[1] = atomicAdd(hot(q, H_EV_TAIL), (unsigned long long)count);
     }
     __syncthreads();
     const unsigned long long base = s_base[0], ebase = s_base[1];
-    for (int k = threadIdx.x; k < count; k += BLOCK) q_put(ws, ring, base + k, ebase + k, type, c, (uint32_t)(k * stride));
+    for (int k = threadIdx.x; k < count; k += BLOCK) q_put(ws, q, ring, base + k, ebase + k, type, c, (uint32_t)(k * stride));
+}
+
+// whole warp: the same for a warp (everything the WARP wrote before the call is visible to the consumers)
+__device__ __forceinline__ void q_push_range_warp(const WS& ws, const Queue& q, int ring, uint32_t type, uint32_t c, int count, int stride)
+{
+    const int lane = threadIdx.x & 31;
+    unsigned long long base = 0, ebase = 0;
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) {
+        base = atomicAdd(hot(q, ring ? H_TAIL_HI : H_TAIL_LO), (unsigned long long)count);
+        ebase = atomicAdd(hot(q, H_EV_TAIL), (unsigned long long)count);
+    }
+    base = __shfl_sync(0xffffffffu, base, 0);
+    ebase = __shfl_sync(0xffffffffu, ebase, 0);
+    for (int k = lane; k < count; k += 32) q_put(ws, q, ring, base + k, ebase + k, type, c, (uint32_t)(k * stride));
+    __syncwarp();
 }
 
 // one thread: publishes a single task
-__device__ __forceinline__ void q_push_one(const WS& ws, int ring, uint32_t type, uint32_t c, uint32_t first)
+__device__ __forceinline__ void q_push_one(const WS& ws, const Queue& q, int ring, uint32_t type, uint32_t c, uint32_t first)
 {
-    const unsigned long long t = atomicAdd(hot(ws, ring ? H_TAIL_HI : H_TAIL_LO), 1ull);
-    const unsigned long long e = atomicAdd(hot(ws, H_EV_TAIL), 1ull);
-    q_put(ws, ring, t, e, type, c, first);
+    const unsigned long long t = atomicAdd(hot(q, ring ? H_TAIL_HI : H_TAIL_LO), 1ull);
+    const unsigned long long e = atomicAdd(hot(q, H_EV_TAIL), 1ull);
+    q_put(ws, q, ring, t, e, type, c, first);
 }
 
-// one thread: takes the next task, urgent ring first.  Returns false when every candidate is finished, or when the
-// watchdog fired: a CTA that has been idle since `timeout_ns` after its start sets H_ABORT and everybody leaves.
-__device__ __forceinline__ bool q_pop(const WS& ws, unsigned long long n_target, unsigned long long timeout_ns, unsigned long long t_start,
-                                      uint2* task)
+// one thread: takes the next task of the queue, urgent ring first.  Returns false when every candidate is finished, or when
+// the watchdog fired: a consumer that has been idle since `timeout_ns` after its start sets the abort flag and everybody leaves.
+__device__ __forceinline__ bool q_pop(const WS& ws, const Queue& q, unsigned long long n_target, unsigned long long timeout_ns,
+                                      unsigned long long t_start, uint2* task)
 {
     // (1) wait for an arrival event of our own
-    const unsigned long long e = atomicAdd(hot(ws, H_EV_HEAD), 1ull);
-    const uint32_t es = (uint32_t)e & ws.ev_mask;
+    const unsigned long long e = atomicAdd(hot(q, H_EV_HEAD), 1ull);
+    const uint32_t es = (uint32_t)e & q.ev_mask;
     unsigned ns = 32, spins = 0;
-    while (ld_acquire_u32(ws.q_ev + es) != (uint32_t)e + 1u) {
-        if (ld_relaxed_u64(hot(ws, H_DONE)) >= n_target) return false;
+    while (ld_acquire_u32(q.ev + es) != (uint32_t)e + 1u) {
+        if (q_done(ws) >= n_target) return false;
         if (q_aborted(ws)) return false;
         if ((++spins & 1023u) == 0) {
             unsigned long long now;
             asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
-            if (now - t_start > timeout_ns) { atomicExch(hot(ws, H_ABORT), 1ull); return false; }
+            if (now - t_start > timeout_ns) { q_abort(ws); return false; }
         }
         __nanosleep(ns);
         if (ns < 512) ns <<= 1;
     }
-    st_release_u32(ws.q_ev + es, (uint32_t)e + ws.ev_mask + 1u);
+    st_release_u32(q.ev + es, (uint32_t)e + q.ev_mask + 1u);
     // (2) a task is waiting for us: the oldest urgent one if there is any, else the oldest normal one.  H_AVAIL_* count the
-    //     published tasks nobody has a right to yet: whoever decrements a positive count owns the ring's next ticket
-    //     (wait-free: no compare-and-swap loop on the heads, whatever the number of CTAs woken at the same time).
+    //     published tasks nobody has a right to yet: whoever decrements a positive count owns the ring's next ticket.
     for (;;) {
 #pragma unroll
         for (int ring = 1; ring >= 0; --ring) {
-            unsigned long long* avail = hot(ws, ring ? H_AVAIL_HI : H_AVAIL_LO);
+            unsigned long long* avail = hot(q, ring ? H_AVAIL_HI : H_AVAIL_LO);
             if ((long long)ld_relaxed_u64(avail) <= 0) continue;
             if ((long long)atomicAdd(avail, ~0ull) <= 0) { atomicAdd(avail, 1ull); continue; }     // lost the race: give it back
-            const unsigned long long h = atomicAdd(hot(ws, ring ? H_HEAD_HI : H_HEAD_LO), 1ull);
-            const uint32_t slot = ((uint32_t)h & ws.q_mask) + (ring ? ws.q_mask + 1u : 0u);
-            while (ld_acquire_u32(ws.q_seq + slot) != (uint32_t)h + 1u) {          // published before H_AVAIL was raised: immediate
+            const unsigned long long h = atomicAdd(hot(q, ring ? H_HEAD_HI : H_HEAD_LO), 1ull);
+            const uint32_t slot = ((uint32_t)h & q.mask) + (ring ? q.mask + 1u : 0u);
+            while (ld_acquire_u32(q.seq + slot) != (uint32_t)h + 1u) {             // an older ticket still being published
                 if (q_aborted(ws)) return false;
                 __nanosleep(20);
             }
-            *task = ws.q_task[slot];
-            st_release_u32(ws.q_seq + slot, (uint32_t)h + ws.q_mask + 1u);
+            *task = q.task[slot];
+            st_release_u32(q.seq + slot, (uint32_t)h + q.mask + 1u);
             return true;
         }
         if (q_aborted(ws)) return false;

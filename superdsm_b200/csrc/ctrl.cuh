@@ -185,17 +185,17 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
 constexpr int HG_BLOCK = SOLVE_BLOCK;
 constexpr int HG_WARPS = HG_BLOCK / 32;
 constexpr int HG_ACC = 96;
+constexpr int HG_ITEM_ROWS = 2;      // grid points per queued Hessian-row item (one warp)
+constexpr int WARP_ITEM_CELLS = 4;   // cells per queued evaluation item of a large candidate (one warp)
 
-// task (c, first): the CTA's warps take the grid points first .. first + HG_WARPS of candidate c.  s_acc: HG_WARPS * HG_ACC doubles.
-__device__ __forceinline__ void hg_task(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* s_acc)
+// one warp: row 6 + j of candidate c's Hessian.  acc: HG_ACC doubles of shared memory of the warp's own.
+__device__ __forceinline__ void hg_row(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int j, double* acc)
 {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double* acc = s_acc + warp * HG_ACC;
+    const int lane = threadIdx.x & 31;
     constexpr int SP = 4 * NC + 1;   // 9
     const sdsm_cand* cd = cands + c;
     const int64_t cell_off = cd->cell_off;
     const CInfo ci = ws.cinfo[c];
-    const int j = first + warp;
     if (j >= ci.m) return;
     const int cw = ci.cw, ch = ci.ch, N = 6 + ci.m;
     const EvalReq rq = ws.req[c];
@@ -256,6 +256,14 @@ __device__ __forceinline__ void hg_task(const Par& par, const sdsm_cand* __restr
         H[(size_t)(6 + j) * N + lane] = s;
         H[(size_t)lane * N + 6 + j] = s;
     }
+}
+
+// CTA-wide task (c, first): the CTA's warps take the grid points first .. first + HG_WARPS of candidate c (chains that stay in
+// one CTA, diagnostics).  s_acc: HG_WARPS * HG_ACC doubles.
+__device__ __forceinline__ void hg_task(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* s_acc)
+{
+    const int warp = threadIdx.x >> 5;
+    hg_row(par, cands, ws, c, first + warp, s_acc + warp * HG_ACC);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -983,7 +991,8 @@ __device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sds
         if (requested) {
             EvalReq rq;
             rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = S.z * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;
-            rq.cpt = P.n_ne <= task_small_cells ? EVAL_WARPS : EVAL_CELLS; rq.pad = 0;
+            rq.cpt = P.n_ne <= task_small_cells ? EVAL_WARPS : EVAL_CELLS;
+            rq.cpw = P.n_ne <= task_small_cells ? 1 : WARP_ITEM_CELLS;
             ws.req[c] = rq;
         }
     }

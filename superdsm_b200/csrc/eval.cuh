@@ -15,7 +15,7 @@ constexpr double NEG_LOG_DBL_MAX = -709.782712893384;   // -log(finfo(float64).m
 
 __device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }   // i >= j
 
-__device__ __forceinline__ void logistic(double y, double S, double& phi, double& theta)
+__device__ __noinline__ void logistic(double y, double S, double& phi, double& theta)
 {
     const double t = y * S;
     if (t >= NEG_LOG_DBL_MAX) {
@@ -83,7 +83,7 @@ __device__ __forceinline__ double cell_S(const double (&th)[6], double x1, doubl
 // scrG[0..5] = gradient, scrG[31] = value, scrH[0..20] = packed lower triangle of the 6 x 6 block.
 
 template <bool HESS>
-__device__ __forceinline__ void eval_cell_poly(const double* __restrict__ py, const uint32_t* __restrict__ prc, int npix,
+__device__ __noinline__ void eval_cell_poly(const double* __restrict__ py, const uint32_t* __restrict__ prc, int npix,
                                                const double* __restrict__ xr, const double* __restrict__ xc, const double* x,
                                                double tol, double* sg, double* sh)
 {
@@ -147,7 +147,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // Stages chunk k (32 pixels from p0 = 32 k) of the cell into shared memory: every lane copies its own pixel's y, rc and the
 // na entries of its row of G~ (a lane only ever reads back what it copied itself, so no warp synchronisation is needed).
 // Lanes beyond the cell's last pixel copy the chunk's first pixel: finite data that the caller masks out.
-__device__ __forceinline__ void stage_chunk(char* stage, const double* __restrict__ py, const uint32_t* __restrict__ prc,
+__device__ __noinline__ void stage_chunk(char* stage, const double* __restrict__ py, const uint32_t* __restrict__ prc,
                                             const float* __restrict__ gcell, int npix, int na, int p0, int lane)
 {
     const int p = (p0 + lane < npix) ? p0 + lane : p0;
@@ -157,15 +157,13 @@ __device__ __forceinline__ void stage_chunk(char* stage, const double* __restric
     cp_async8(Y + lane, py + p);
     cp_async4(RC + lane, prc + p);
     const float* gp = gcell + p;
-#pragma unroll
-    for (int a = 0; a < NSLOT; ++a) {
-        if (a < na) cp_async4(G + a * 32 + lane, gp);
-        gp += npix;
-    }
+    float* gs = G + lane;
+#pragma unroll 1
+    for (int a = 0; a < na; ++a) { cp_async4(gs, gp); gp += npix; gs += 32; }     // rolled: the code of the evaluation items must stay small (instruction cache)
 }
 
 // Returns, in lane e, the cell's local gradient entry e (e < 6 + na), and in lane 31 its value.
-__device__ __forceinline__ double cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
+__device__ __noinline__ double cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
                                                int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
                                                const double* x, double tol, char* stages, const double* XI)
 {
@@ -194,10 +192,14 @@ __device__ __forceinline__ double cell_value_grad(const double* __restrict__ py,
         const double x1 = xr[rc & 0xffffu], x2 = xc[rc >> 16];
         double S = cell_S(th, x1, x2);
         double sx0 = 0, sx1 = 0;
-#pragma unroll
-        for (int a = 0; a < NSLOT; a += 2) {
+        {
+            int a = 0;
+#pragma unroll 2
+            for (; a + 1 < na; a += 2) {
+                sx0 = fma((double)G[a * 32], XI[a], sx0);
+                sx1 = fma((double)G[(a + 1) * 32], XI[a + 1], sx1);
+            }
             if (a < na) sx0 = fma((double)G[a * 32], XI[a], sx0);
-            if (a + 1 < NSLOT && a + 1 < na) sx1 = fma((double)G[(a + 1) * 32], XI[a + 1], sx1);
         }
         S += sx0 + sx1;
         double phi = 0, theta = 0;
@@ -221,7 +223,7 @@ __device__ __forceinline__ double cell_value_grad(const double* __restrict__ py,
     return warp_sum_transposed(acc);                 // lane: local gradient entry, 31: value
 }
 
-__device__ __forceinline__ void cell_hessian(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
+__device__ __noinline__ void cell_hessian(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
                                              int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
                                              const double* x, double tol, double* Tt, const double* XI, double* sh)
 {
@@ -248,10 +250,16 @@ __device__ __forceinline__ void cell_hessian(const double* __restrict__ py, cons
         double S = cell_S(th, x1, x2);
         double* col = Tt + lane;
         double sx0 = 0, sx1 = 0;
-#pragma unroll
-        for (int a = 0; a < NSLOT; a += 2) {
-            if (a < na) { const double g = act ? (double)gcell[(size_t)a * npix + p] : 0.0; col[(6 + a) * TILE_LD] = g; sx0 = fma(g, XI[a], sx0); }
-            if (a + 1 < NSLOT && a + 1 < na) { const double g = act ? (double)gcell[(size_t)(a + 1) * npix + p] : 0.0; col[(7 + a) * TILE_LD] = g; sx1 = fma(g, XI[a + 1], sx1); }
+        {
+            const float* gp = gcell + (act ? p : 0);
+            int a = 0;
+#pragma unroll 2
+            for (; a + 1 < na; a += 2) {
+                const double g0 = act ? (double)gp[(size_t)a * npix] : 0.0, g1 = act ? (double)gp[(size_t)(a + 1) * npix] : 0.0;
+                col[(6 + a) * TILE_LD] = g0; col[(7 + a) * TILE_LD] = g1;
+                sx0 = fma(g0, XI[a], sx0); sx1 = fma(g1, XI[a + 1], sx1);
+            }
+            if (a < na) { const double g0 = act ? (double)gp[(size_t)a * npix] : 0.0; col[(6 + a) * TILE_LD] = g0; sx0 = fma(g0, XI[a], sx0); }
         }
         S += sx0 + sx1;
         double phi = 0, theta = 0;

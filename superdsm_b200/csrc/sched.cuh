@@ -1,14 +1,20 @@
 // K3: k_solve -- the persistent solver kernel.  Every candidate's fit is a chain of dependent steps
-//     control task -> evaluation tasks (one per EVAL_CELLS pixel cells) [-> Hessian-row tasks] -> control task -> ...
+//     control task -> evaluation items (one per 1-4 pixel cells) [-> Hessian-row items] -> control task -> ...
 // (a few dozen to a few thousand links, objects.py:361-412 around cvxopt's cp), and the chains of a batch differ in length
-// and width by orders of magnitude.  Instead of lock-step launches, the CTAs of one persistent grid pull tasks from a
-// device-side queue (common.cuh): whoever finishes the last evaluation task of a candidate publishes its next control
-// task, so every candidate advances at its own pace and a straggler only occupies the CTAs its own tasks need.
-// Candidates with few cells run their whole chain inside one CTA (no queue hop between the links).
+// and width by orders of magnitude.  Instead of lock-step launches, one persistent grid pulls work from device-side
+// queues (common.cuh): whoever finishes the last item of a candidate's stage publishes its next stage, so every candidate
+// advances at its own pace.
+//
+// The CTAs have one of two roles.  Control CTAs (the first n_ctrl_ctas) take control tasks from ws.qc, one CTA per task:
+// the interior-point bookkeeping, Cholesky factorisations and triangular solves need a CTA's worth of threads and
+// barriers.  The WARPS of all other CTAs are independent consumers of ws.qe: an evaluation item is a few pixel cells, a
+// Hessian-row item a few grid points, each handled by one warp from start to end -- no CTA-wide barrier is ever waited
+// on in the evaluation path, so a warp with a short item never idles behind a long one.
+// Candidates with few cells run their whole chain inside one control CTA (no queue hop between the links).
 //
 // Nothing ever blocks on another task: a task only waits for a queue slot whose previous occupant has already been
-// claimed by a consumer.  The kernel ends when every candidate has reported completion (H_DONE == n_target), or when the
-// watchdog fires (H_ABORT; sdsm_solver_stats reports it).
+// claimed by a consumer.  The kernel ends when every candidate has reported completion (G_DONE == n_target), or when the
+// watchdog fires (G_ABORT; sdsm_solver_stats reports it).
 #pragma once
 #include "common.cuh"
 #include "eval.cuh"
@@ -27,9 +33,10 @@ struct SolveArgs {
     int n_target;            // candidates that must finish
     int lcap;                // shared-memory capacity (doubles) for a packed Cholesky factor
     int solo_cells;          // candidates with at most this many non-empty cells run their chain inside one CTA
-    int task_small_cells;    // candidates with at most this many non-empty cells get one cell per warp (EVAL_WARPS per task)
+    int task_small_cells;    // candidates with at most this many non-empty cells get one cell per evaluation item
     int hi_evals;            // a candidate that has needed more evaluations of F than this becomes urgent (ring 1)
-    unsigned long long timeout_ns;   // watchdog: idle CTAs abort the kernel after this long
+    int n_ctrl_ctas;         // CTAs [0, n_ctrl_ctas) run control tasks, the warps of the others evaluation / Hessian-row items
+    unsigned long long timeout_ns;   // watchdog: idle consumers abort the kernel after this long
     double* trace;           // diagnostics (STG_TRACE) or nullptr
 };
 
@@ -40,65 +47,76 @@ __device__ __forceinline__ unsigned long long globaltimer_ns()
     return t;
 }
 
+__device__ __forceinline__ void seed_queue(const Queue& q, uint32_t i, uint32_t stride, int n_lo, int n_hi)
+{
+    const uint32_t cap = q.mask + 1u;
+    for (; i < 2u * cap; i += stride) {
+        q.ev[i] = (int)i < n_lo + n_hi ? i + 1u : i;                     // one arrival event per seeded task
+        if (i >= cap) continue;
+        q.seq[cap + i] = (int)i < n_hi ? i + 1u : i;
+        q.seq[i] = (int)i < n_lo ? i + 1u : i;
+    }
+}
+
 // Seeds the queues: the control tasks that start the candidates order[0 .. n_first) (most expensive first); the first n_hi
-// of them are urgent from the start (ring 1), the others go to ring 0.
+// of them are urgent from the start (ring 1), the others go to ring 0.  The evaluation queue starts empty.
 __global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, int single, int n_hi)
 {
-    const uint32_t q_cap = ws.q_mask + 1u;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 2u * q_cap; i += gridDim.x * blockDim.x) {
-        ws.q_ev[i] = (int)i < n_first ? i + 1u : i;                      // one arrival event per seeded task
-        if (i >= q_cap) continue;
-        if ((int)i < n_hi) {
-            ws.q_task[q_cap + i] = make_uint2(((uint32_t)T_CTRL << T_SHIFT) | (uint32_t)order[i], 0u);
-            ws.q_seq[q_cap + i] = i + 1u;
-        } else ws.q_seq[q_cap + i] = i;
-        if ((int)i < n_first - n_hi) {
-            ws.q_task[i] = make_uint2(((uint32_t)T_CTRL << T_SHIFT) | (uint32_t)(order ? order[n_hi + i] : single), 0u);
-            ws.q_seq[i] = i + 1u;
-        } else ws.q_seq[i] = i;
+    const uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    seed_queue(ws.qc, i0, stride, n_first - n_hi, n_hi);
+    seed_queue(ws.qe, i0, stride, 0, 0);
+    const uint32_t cap = ws.qc.mask + 1u;
+    for (int i = i0; i < n_first; i += stride) {
+        const int c = order ? order[i] : single;
+        ws.prio[c] = i < n_hi ? 1 : 0;
+        ws.qc.task[i < n_hi ? cap + i : i - n_hi] = make_uint2(((uint32_t)T_CTRL << T_SHIFT) | (uint32_t)c, 0u);
     }
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_first; i += gridDim.x * blockDim.x)
-        ws.prio[order ? order[i] : single] = i < n_hi ? 1 : 0;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (i0 == 0) {
         for (int k = 0; k < N_COUNTERS; ++k) ws.counters[k] = 0ull;
-        for (int k = 0; k < N_HOT * HOT_STRIDE; ++k) ws.hot[k] = 0ull;
-        *hot(ws, H_TAIL_LO) = (unsigned long long)(n_first - n_hi);
-        *hot(ws, H_TAIL_HI) = (unsigned long long)n_hi;
-        *hot(ws, H_EV_TAIL) = (unsigned long long)n_first;
-        *hot(ws, H_AVAIL_LO) = (unsigned long long)(n_first - n_hi);
-        *hot(ws, H_AVAIL_HI) = (unsigned long long)n_hi;
+        for (int k = 0; k < N_HOT * HOT_STRIDE; ++k) { ws.qc.hot[k] = 0ull; ws.qe.hot[k] = 0ull; }
+        for (int k = 0; k < N_GLOB * HOT_STRIDE; ++k) ws.glob[k] = 0ull;
+        *hot(ws.qc, H_TAIL_LO) = (unsigned long long)(n_first - n_hi);
+        *hot(ws.qc, H_TAIL_HI) = (unsigned long long)n_hi;
+        *hot(ws.qc, H_EV_TAIL) = (unsigned long long)n_first;
+        *hot(ws.qc, H_AVAIL_LO) = (unsigned long long)(n_first - n_hi);
+        *hot(ws.qc, H_AVAIL_HI) = (unsigned long long)n_hi;
         ws.counters[Q_T0] = globaltimer_ns();
     }
 }
 
-// the CTA that finished a task of candidate c's current stage: the last one to finish starts the next stage
-template <int BLOCK>
-__device__ __forceinline__ void finish_stage_task(const WS& ws, uint32_t type, int c, int* s_flag, unsigned long long* s_base)
+// one warp: the evaluation item (c, first) = cells cell_list[first .. first + cpw) of candidate c's pending request
+__device__ __forceinline__ void eval_item(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* Tt, int* slotj)
 {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
+    const CInfo ci = ws.cinfo[c];
+    const int count = min(ws.req[c].cpw, ci.n_ne - first);
+    for (int i = 0; i < count; ++i) eval_cell(par, cands, ws, c, ci, first + i, Tt, slotj);
+}
+
+// the warp that finished an item of candidate c's current stage: the last one to finish starts the next stage
+__device__ __forceinline__ void finish_item(const WS& ws, uint32_t type, int c)
+{
+    const int lane = threadIdx.x & 31;
+    __threadfence();
+    __syncwarp();
+    int next = 0;                                            // 0: not the last, 1: control task, > 1: that many T_HG items
+    if (lane == 0) {
         const int old = atomicSub(ws.pending + c, 1);
         __threadfence();
-        int next = 0;                                        // 0: not the last, 1: control task, > 1: that many T_HG tasks
         if (old == 1) {
             const EvalReq rq = ws.req[c];
             next = 1;
             if (type == T_EVAL && rq.want_h && rq.use_xi) {
-                const int nt = (ws.cinfo[c].m + HG_WARPS - 1) / HG_WARPS;
+                const int nt = (ws.cinfo[c].m + HG_ITEM_ROWS - 1) / HG_ITEM_ROWS;
                 ws.pending[c] = nt;
                 next = 1 + nt;
             }
         }
-        *s_flag = next;
     }
-    __syncthreads();
-    const int next = *s_flag;
-    __syncthreads();                                         // thread 0 reuses s_flag as soon as it is back in the task loop
+    next = __shfl_sync(0xffffffffu, next, 0);
     if (next == 0) return;
     const int ring = ws.prio[c];
-    if (next == 1) { if (threadIdx.x == 0) q_push_one(ws, ring, T_CTRL, (uint32_t)c, 0u); }
-    else q_push_range<BLOCK>(ws, ring, T_HG, (uint32_t)c, next - 1, HG_WARPS, s_base);
+    if (next == 1) { if (lane == 0) q_push_one(ws, ws.qc, ring, T_CTRL, (uint32_t)c, 0u); }
+    else q_push_range_warp(ws, ws.qe, ring, T_HG, (uint32_t)c, next - 1, HG_ITEM_ROWS);
 }
 
 __global__ void __launch_bounds__(SOLVE_BLOCK, 2)
@@ -110,21 +128,66 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     __shared__ uint2 s_task;
     __shared__ int s_flag, s_next;
     __shared__ unsigned long long s_base[2];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned long long n_target = (unsigned long long)args.n_target;
-    unsigned long long t_start = 0, cyc[4] = {0, 0, 0, 0}, cnt[3] = {0, 0, 0}, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0};
-    if (tid == 0) t_start = globaltimer_ns();
+    const unsigned long long t_start = globaltimer_ns();
     const long long c_begin = clock64();
 
+    if ((int)blockIdx.x >= args.n_ctrl_ctas) {
+        // ---- evaluation warps: independent consumers of ws.qe ----
+        double* Tt = (double*)smem_solve + warp * TILE_DOUBLES;      // TILE_DOUBLES >= HG_ACC
+        int* slotj = s_slotj + warp * 32;
+        unsigned long long cyc_idle = 0, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0}, cyc_hg = 0, n_hg = 0;
+        unsigned n_popped = 0;
+        for (;;) {
+            uint2 task = make_uint2(0u, 0u);
+            int ok = 0;
+            const long long c0 = clock64();
+            if (lane == 0) {
+                if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) q_abort(ws);
+                ok = q_pop(ws, ws.qe, n_target, args.timeout_ns, t_start, &task) ? 1 : 0;
+            }
+            ok = __shfl_sync(0xffffffffu, ok, 0);
+            if (!ok) break;
+            task.x = __shfl_sync(0xffffffffu, task.x, 0);
+            task.y = __shfl_sync(0xffffffffu, task.y, 0);
+            const long long c1 = clock64();
+            cyc_idle += (unsigned long long)(c1 - c0);
+            const uint32_t type = task.x >> T_SHIFT;
+            const int c = (int)(task.x & T_CMASK);
+            if (type == T_EVAL) {
+                eval_item(par, cands, ws, c, (int)task.y, Tt, slotj);
+                const EvalReq rq = ws.req[c];
+                const int kind = (rq.use_xi ? 2 : 0) + (rq.want_h ? 1 : 0);
+                kcyc[kind] += (unsigned long long)(clock64() - c1); kcnt[kind] += 1;
+            } else {
+                const int m = ws.cinfo[c].m;
+                for (int j = (int)task.y; j < (int)task.y + HG_ITEM_ROWS && j < m; ++j) { hg_row(par, cands, ws, c, j, Tt); __syncwarp(); }
+                cyc_hg += (unsigned long long)(clock64() - c1); n_hg += 1;
+            }
+            finish_item(ws, type, c);
+        }
+        if (lane == 0) {
+            unsigned long long ce = 0, ne = 0;
+            for (int k = 0; k < 4; ++k) { atomicAdd(ws.counters + Q_CYC_KIND + k, kcyc[k]); atomicAdd(ws.counters + Q_N_KIND + k, kcnt[k]); ce += kcyc[k]; ne += kcnt[k]; }
+            atomicAdd(ws.counters + Q_CYC_EVAL, ce); atomicAdd(ws.counters + Q_N_EVAL, ne);
+            atomicAdd(ws.counters + Q_CYC_HG, cyc_hg); atomicAdd(ws.counters + Q_N_HG, n_hg);
+            atomicAdd(ws.counters + Q_CYC_WIDLE, cyc_idle);
+            atomicAdd(ws.counters + Q_CYC_WTOTAL, (unsigned long long)(clock64() - c_begin));
+        }
+        return;
+    }
+
+    // ---- control CTAs: one control task at a time, from ws.qc ----
+    unsigned long long cyc_ctrl = 0, cyc_idle = 0, n_ctrl = 0, n_promoted = 0;
     unsigned n_popped = 0;
-    unsigned long long n_promoted = 0;
     for (;;) {
         if (tid == 0) {
             const long long c0 = clock64();
             uint2 task;
-            if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) atomicExch(hot(ws, H_ABORT), 1ull);
-            const bool ok = q_pop(ws, n_target, args.timeout_ns, t_start, &task);
-            cyc[3] += (unsigned long long)(clock64() - c0);
+            if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) q_abort(ws);
+            const bool ok = q_pop(ws, ws.qc, n_target, args.timeout_ns, t_start, &task);
+            cyc_idle += (unsigned long long)(clock64() - c0);
             s_task = task;
             s_flag = ok ? 1 : 0;
             s_next = 0;
@@ -134,17 +197,9 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         const bool ok = s_flag != 0;
         __syncthreads();
         if (!ok) break;
-        const uint32_t type = task.x >> T_SHIFT;
         const int c = (int)(task.x & T_CMASK);
         const long long c0 = clock64();
-        if (type == T_EVAL) {
-            eval_task(par, cands, ws, c, (int)task.y, (double*)smem_solve, s_slotj, &s_next);
-            if (tid == 0) { const EvalReq rq = ws.req[c]; const int kind = (rq.use_xi ? 2 : 0) + (rq.want_h ? 1 : 0); kcyc[kind] += (unsigned long long)(clock64() - c0); kcnt[kind] += 1; }
-            finish_stage_task<BLOCK>(ws, T_EVAL, c, &s_flag, s_base);
-        } else if (type == T_HG) {
-            hg_task(par, cands, ws, c, (int)task.y, (double*)smem_solve);
-            finish_stage_task<BLOCK>(ws, T_HG, c, &s_flag, s_base);
-        } else {
+        {
             const sdsm_cand cd = cands[c];
             const CInfo ci = ws.cinfo[c];
             const bool solo = ci.n_ne <= args.solo_cells;
@@ -154,7 +209,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     __syncthreads();
                     const bool stop = s_flag != 0;
                     __syncthreads();
-                    if (stop) { if (tid == 0) atomicExch(hot(ws, H_ABORT), 1ull); break; }
+                    if (stop) { if (tid == 0) q_abort(ws); break; }
                 }
                 const bool big = (ws.cstate[c].use_xi ? 6 + ci.m : 6) > SMALL_N_MAX;
                 Sm sm;
@@ -165,26 +220,28 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     if (tid == 0) {
                         ws.pending[c] = (int32_t)((globaltimer_ns() - ws.counters[Q_T0]) / 1000ull);   // diagnostics: finish time, us
                         __threadfence();
-                        atomicAdd(hot(ws, H_DONE), 1ull);
+                        atomicAdd(ws.glob + G_DONE * HOT_STRIDE, 1ull);
                     }
                     break;
                 }
-                const int cpt = ws.req[c].cpt;
-                const int n_tasks = (ci.n_ne + cpt - 1) / cpt;
                 if (!solo) {
                     // publishing is the LAST thing a control task does: the candidate's next control task may start on another
                     // SM as soon as the evaluations have finished
+                    const int cpw = ws.req[c].cpw;
+                    const int n_items = (ci.n_ne + cpw - 1) / cpw;
                     if (tid == 0) {
-                        ws.pending[c] = n_tasks;
+                        ws.pending[c] = n_items;
                         // a chain that turns out long becomes urgent: it would otherwise finish long after the bulk of the batch
                         if (!ws.prio[c]) { const CState* S = ws.cstate + c; if (S->nf + S->nh > args.hi_evals) { ws.prio[c] = 1; ++n_promoted; } }
                     }
                     __syncthreads();
-                    q_push_range<BLOCK>(ws, ws.prio[c], T_EVAL, (uint32_t)c, n_tasks, cpt, s_base);
+                    q_push_range<BLOCK>(ws, ws.qe, ws.prio[c], T_EVAL, (uint32_t)c, n_items, cpw, s_base);
                     break;
                 }
                 // the whole chain in this CTA: evaluate here and go on
                 const EvalReq rq = ws.req[c];
+                const int cpt = rq.cpt;
+                const int n_tasks = (ci.n_ne + cpt - 1) / cpt;
                 for (int k = 0; k < n_tasks; ++k) {
                     if (tid == 0) s_next = 0;
                     __syncthreads();
@@ -195,14 +252,11 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     for (int j = 0; j < ci.m; j += HG_WARPS) { hg_task(par, cands, ws, c, j, (double*)smem_solve); __syncthreads(); }
             }
         }
-        if (tid == 0) { cyc[type] += (unsigned long long)(clock64() - c0); cnt[type] += 1; }
+        if (tid == 0) { cyc_ctrl += (unsigned long long)(clock64() - c0); n_ctrl += 1; }
     }
     if (tid == 0) {
-        atomicAdd(ws.counters + Q_CYC_CTRL, cyc[T_CTRL]); atomicAdd(ws.counters + Q_CYC_EVAL, cyc[T_EVAL]);
-        atomicAdd(ws.counters + Q_CYC_HG, cyc[T_HG]);     atomicAdd(ws.counters + Q_CYC_IDLE, cyc[3]);
-        atomicAdd(ws.counters + Q_N_CTRL, cnt[T_CTRL]);   atomicAdd(ws.counters + Q_N_EVAL, cnt[T_EVAL]);
-        atomicAdd(ws.counters + Q_N_HG, cnt[T_HG]);       atomicAdd(ws.counters + Q_CYC_TOTAL, (unsigned long long)(clock64() - c_begin));
-        for (int k = 0; k < 4; ++k) { atomicAdd(ws.counters + Q_CYC_KIND + k, kcyc[k]); atomicAdd(ws.counters + Q_N_KIND + k, kcnt[k]); }
+        atomicAdd(ws.counters + Q_CYC_CTRL, cyc_ctrl); atomicAdd(ws.counters + Q_CYC_IDLE, cyc_idle); atomicAdd(ws.counters + Q_N_CTRL, n_ctrl);
+        atomicAdd(ws.counters + Q_CYC_TOTAL, (unsigned long long)(clock64() - c_begin));
         if (n_promoted) atomicAdd(ws.counters + Q_N_PROMOTED, n_promoted);
     }
 }
@@ -226,7 +280,7 @@ k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, co
     for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) P.H[i] = 0.0;
     bad = __syncthreads_or(bad);
     if (tid == 0) {
-        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = P.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.pad = 0;
+        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = P.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.cpw = 1;
         ws.req[c] = rq;
         ws.cstate[c].pc = bad ? -1 : PC_DONE;
     }
@@ -334,14 +388,14 @@ k_sweep_prep(Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, in
         __syncthreads();
         if (threadIdx.x == 0) {
             const int ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
-            EvalReq rq; rq.x = ws.vecs + cd.vec_off + (size_t)V_X * ld; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = ci.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.pad = 0;
+            EvalReq rq; rq.x = ws.vecs + cd.vec_off + (size_t)V_X * ld; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = ci.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.cpw = 1;
             ws.req[c] = rq;
             s_base = atomicAdd(ws.counters + Q_TAIL, (unsigned long long)count);
         }
         __syncthreads();
         const unsigned long long base = s_base;
         for (int k = threadIdx.x; k < count; k += SOLVE_BLOCK)
-            ws.q_task[base + k] = make_uint2((uint32_t)c, (uint32_t)(k * (rows ? HG_WARPS : EVAL_CELLS)));
+            ws.qe.task[base + k] = make_uint2((uint32_t)c, (uint32_t)(k * (rows ? HG_WARPS : EVAL_CELLS)));
     }
 }
 
@@ -353,7 +407,7 @@ k_sweep(Par par, const sdsm_cand* __restrict__ cands, WS ws, int rows)
     __shared__ int s_next;
     const unsigned long long n_tasks = ws.counters[Q_TAIL];
     for (unsigned long long i = blockIdx.x; i < n_tasks; i += gridDim.x) {
-        const uint2 task = ws.q_task[i];
+        const uint2 task = ws.qe.task[i];
         if (threadIdx.x == 0) s_next = 0;
         __syncthreads();
         if (rows) hg_task(par, cands, ws, (int)task.x, (int)task.y, (double*)smem_solve);

@@ -32,6 +32,7 @@ struct sdsm_ctx {
     int task_small_cells = 512;              // SDSM_TASK_SMALL_CELLS: candidates up to this many cells get one cell per warp
     double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
     double hi_frac = 0.08;                   // SDSM_HI_FRAC: this share of the batch (the most expensive candidates) is urgent from the start
+    int ctrl_ctas = 64;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
     int hi_evals = 400;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     std::string err;
 };
@@ -72,6 +73,7 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     if (const char* e = getenv("SDSM_TIMEOUT_S")) ctx->timeout_s = atof(e);
     if (const char* e = getenv("SDSM_HI_FRAC")) ctx->hi_frac = atof(e);
     if (const char* e = getenv("SDSM_HI_EVALS")) ctx->hi_evals = atoi(e);
+    if (const char* e = getenv("SDSM_CTRL_CTAS")) ctx->ctrl_ctas = atoi(e);
     return SDSM_OK;
 }
 
@@ -160,7 +162,7 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
         c.fg_off = FG;  FG += (int64_t)c.h * c.w;
         c.vec_off = V;  V += (int64_t)NVEC * ld;
         c.mat_off = M;  M += 3 * ld * ld;
-        K += 1 + (cap + EVAL_WARPS - 1) / EVAL_WARPS;     // tasks of the candidate that can be queued at the same time
+        K += 1 + cap;                                     // items of the candidate that can be queued at the same time
         if (ld > n_max) n_max = (int32_t)ld;
         if (cap > cells_max) cells_max = cap;
     }
@@ -199,9 +201,12 @@ static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_can
     args.solo_cells = ctx->solo_cells;
     args.task_small_cells = ctx->task_small_cells;
     args.hi_evals = ctx->hi_evals;
+    args.n_ctrl_ctas = ctx->ctrl_ctas;
     args.timeout_ns = (unsigned long long)(ctx->timeout_s * 1e9);
     args.trace = trace;
     const int grid = ctx->sm_count * ctx->solve_ctas_per_sm;
+    if (args.n_ctrl_ctas < 1) args.n_ctrl_ctas = 1;
+    if (args.n_ctrl_ctas > grid - 1) args.n_ctrl_ctas = grid - 1;
     k_solve<<<grid, SOLVE_BLOCK, solve_smem_bytes(lcap), stream>>>(ctx->img, ctx->par, d_cands, ws, out, args);
     ctx->launches += 2;
     CUDA_TRY(ctx, cudaGetLastError());
@@ -315,13 +320,17 @@ extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_
     WS ws = make_ws(const_cast<void*>(d_workspace), L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    uint64_t h_hot[N_HOT * HOT_STRIDE];
+    uint64_t h_qc[N_HOT * HOT_STRIDE], h_qe[N_HOT * HOT_STRIDE], h_gl[N_GLOB * HOT_STRIDE];
     CUDA_TRY(ctx, cudaMemcpyAsync(h_stats, ws.counters, sizeof(uint64_t) * N_COUNTERS, cudaMemcpyDeviceToHost, stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(h_hot, ws.hot, sizeof(h_hot), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_qc, ws.qc.hot, sizeof(h_qc), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_qe, ws.qe.hot, sizeof(h_qe), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_gl, ws.glob, sizeof(h_gl), cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
-    h_stats[Q_HEAD] = h_hot[H_HEAD_LO * HOT_STRIDE]; h_stats[Q_TAIL] = h_hot[H_TAIL_LO * HOT_STRIDE];
-    h_stats[Q_HEAD_HI] = h_hot[H_HEAD_HI * HOT_STRIDE]; h_stats[Q_TAIL_HI] = h_hot[H_TAIL_HI * HOT_STRIDE];
-    h_stats[Q_DONE] = h_hot[H_DONE * HOT_STRIDE]; h_stats[Q_ABORT] = h_hot[H_ABORT * HOT_STRIDE];
+    h_stats[Q_HEAD] = h_qc[H_EV_HEAD * HOT_STRIDE] + h_qe[H_EV_HEAD * HOT_STRIDE];     // event tickets taken by consumers
+    h_stats[Q_TAIL] = h_qc[H_EV_TAIL * HOT_STRIDE] + h_qe[H_EV_TAIL * HOT_STRIDE];     // tasks published
+    h_stats[Q_HEAD_HI] = h_qc[H_HEAD_HI * HOT_STRIDE] + h_qe[H_HEAD_HI * HOT_STRIDE];  // of which urgent, taken
+    h_stats[Q_TAIL_HI] = h_qc[H_TAIL_HI * HOT_STRIDE] + h_qe[H_TAIL_HI * HOT_STRIDE];  // of which urgent, published
+    h_stats[Q_DONE] = h_gl[G_DONE * HOT_STRIDE]; h_stats[Q_ABORT] = h_gl[G_ABORT * HOT_STRIDE];
     return SDSM_OK;
 }
 

@@ -159,7 +159,7 @@ class Engine(object):
         return int(self.lib.sdsm_launch_count(self.ctx))
 
     STAT_NAMES = ('q_head', 'q_tail', 'done', 'abort', 'cyc_eval', 'cyc_hrows', 'cyc_ctrl', 'cyc_idle', 'n_eval', 'n_hrows',
-                  'n_ctrl', 'cyc_total')
+                  'n_ctrl', 'cyc_total', 't0', 'cyc_widle', 'cyc_wtotal')
 
     def solver_stats(self, ws=None):
         """Counters of the persistent solver kernel of the last batch (synchronises): see ``sdsm_solver_stats``."""
@@ -169,6 +169,7 @@ class Engine(object):
         out = {k: int(st[i]) for i, k in enumerate(self.STAT_NAMES)}
         for j, kind in enumerate(('poly_f', 'poly_h', 'xi_f', 'xi_h')):
             out['cyc_' + kind], out['n_' + kind] = int(st[16 + j]), int(st[20 + j])
+        out['q_head_hi'], out['q_tail_hi'], out['n_promoted'] = int(st[24]), int(st[25]), int(st[26])
         return out
 
     def finish_times_us(self, ws=None, n=None):
