@@ -16,6 +16,7 @@ st = eng.solver_stats(); tot = max(st['cyc_total'], 1); wtot = max(st['cyc_wtota
 print('ctrl CTAs: busy %.3f idle %.3f | eval warps: eval %.3f hrows %.3f idle %.3f' % (st['cyc_ctrl'] / tot, st['cyc_idle'] / tot, st['cyc_eval'] / wtot, st['cyc_hrows'] / wtot, st['cyc_widle'] / wtot),
       {k: st[k] for k in st if k.startswith('n_')}, 'urgent', st['q_tail_hi'], 'of', st['q_tail'])
 print({k: (st['cyc_' + k] / max(st['n_' + k], 1)) for k in ('poly_f', 'poly_h', 'xi_f', 'xi_h')})
+print('cycles per control task: big systems %.0f (%d), small %.0f (%d)' % (st['cyc_ctrl_big'] / max(st['n_ctrl_big'], 1), st['n_ctrl_big'], (st['cyc_ctrl'] - st['cyc_ctrl_big']) / max(st['n_ctrl'] - st['n_ctrl_big'], 1), st['n_ctrl'] - st['n_ctrl_big']))
 info = res.info; ft = eng.finish_times_us().astype(float); n = res.cands['n']; ev = (info[:, 6] + info[:, 7]).astype(float)
 print('finish pct 10/25/50/75/90/99/100', np.percentile(ft, [10, 25, 50, 75, 90, 99, 100]))
 hist, edges = np.histogram(ft, bins=20); print('finish histogram', hist.tolist(), edges[-1])

@@ -21,6 +21,7 @@ constexpr int EVAL_CELLS = 32;    // most non-empty pixel cells per evaluation t
 // per-warp shared memory of the evaluation tasks (doubles): the value + gradient pass stages the pixel data of STAGES
 // chunks of 32 pixels there with cp.async (STAGE_BYTES each: G~ rows [25][32] f32, y [32] f64, rc [32] u32); the Hessian pass
 // reuses the space for its tile T[32][TILE_LD] + dd[32]; then xi[32].
+constexpr int SLOTJ_INTS = 64;    // per-warp shared memory of the evaluation items (ints): grid index of the cell's active slots [32], slot of each active entry [32]
 constexpr int STAGES = 3;
 constexpr int STAGE_BYTES = NSLOT * 32 * 4 + 32 * 8 + 32 * 4;   // 3584
 constexpr int WARP_AREA_DOUBLES = STAGES * STAGE_BYTES / 8;      // 1344 >= 32 * TILE_LD + 32
@@ -316,7 +317,7 @@ __device__ __forceinline__ bool fp_member(int lab, const int32_t* fp, int n)
 enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG, Q_CYC_CTRL, Q_CYC_IDLE, Q_N_EVAL, Q_N_HG, Q_N_CTRL, Q_CYC_TOTAL, Q_T0,
        Q_CYC_WIDLE = 13 /* idle cycles of the evaluation warps */, Q_CYC_WTOTAL = 14 /* lifetime cycles of the evaluation warps */,
        Q_CYC_KIND = 16 /* [4]: evaluation-item cycles by kind = use_xi * 2 + want_h */, Q_N_KIND = 20 /* [4]: items by kind */,
-       Q_HEAD_HI = 24, Q_TAIL_HI = 25, Q_N_PROMOTED = 26 };
+       Q_HEAD_HI = 24, Q_TAIL_HI = 25, Q_N_PROMOTED = 26, Q_CYC_CTRL_BIG = 27 /* control tasks of systems > SMALL_N_MAX */, Q_N_CTRL_BIG = 28 };
 constexpr int HOT_STRIDE = 16;   // unsigned long longs = 128 bytes
 enum { H_EV_HEAD = 0, H_EV_TAIL = 1, H_HEAD_LO = 2, H_TAIL_LO = 3, H_HEAD_HI = 4, H_TAIL_HI = 5, H_AVAIL_LO = 6, H_AVAIL_HI = 7, N_HOT = 8 };
 enum { G_DONE = 0, G_ABORT = 1, N_GLOB = 2 };

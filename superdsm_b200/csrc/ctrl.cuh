@@ -37,10 +37,11 @@ struct Sm {
     double* red_out;   // [32]
     int*    flag;      // [8]
     int     lcap;      // doubles available for the factor
+    CState* cst;       // [CTRL_WARPS] the candidate's state while a control task runs, one copy per warp (see ctrl_step)
     double *D, *Xj, *yv;   // k_ctrl_big only: diagonal block, panel block, solved block (see cholesky_big)
 };
 constexpr int CTRL_BPAD = 128;
-__host__ __device__ inline size_t ctrl_smem_bytes(int lcap) { return sizeof(double) * (size_t)(lcap + CTRL_BPAD + CTRL_WARPS * 32 + 32) + sizeof(int) * 8; }
+__host__ __device__ inline size_t ctrl_smem_bytes(int lcap) { return sizeof(double) * (size_t)(lcap + CTRL_BPAD + CTRL_WARPS * 32 + 32) + sizeof(int) * 8 + CTRL_WARPS * sizeof(CState); }
 // factor capacity (doubles) a batch whose largest system has n_max unknowns asks for: the whole packed factor if n_max <= 104
 __host__ __device__ inline int ctrl_lcap(int n_max) { const int need = n_max * (n_max + 1) / 2; return need <= SMEM_L_CAP ? (need < 64 ? 64 : need) : SMEM_L_CAP; }
 
@@ -50,6 +51,7 @@ __device__ __forceinline__ void carve_smem(Sm& sm, char* base, int lcap)
     sm.red_part = sm.Lf + lcap + CTRL_BPAD;
     sm.red_out = sm.red_part + CTRL_WARPS * 32;
     sm.flag = (int*)(sm.red_out + 32);
+    sm.cst = (CState*)(sm.flag + 8);
     sm.lcap = lcap;
     sm.D = sm.Xj = sm.yv = nullptr;
 }
@@ -349,7 +351,7 @@ __device__ void chol_solve(const double* L, int N, double* v, double* bv, int bv
 constexpr int CB = 32;               // panel width
 constexpr int CB_LD = CB + 1;
 
-constexpr size_t BIG_SMEM = sizeof(double) * (2 * CB * CB_LD + CB + (BIG_BLOCK / 32) * 32 + 32) + sizeof(int) * 8;
+constexpr size_t BIG_SMEM = sizeof(double) * (2 * CB * CB_LD + CB + (BIG_BLOCK / 32) * 32 + 32) + sizeof(int) * 8 + (BIG_BLOCK / 32) * sizeof(CState);
 
 __device__ __forceinline__ void carve_smem_big(Sm& sm, char* base)
 {
@@ -359,6 +361,7 @@ __device__ __forceinline__ void carve_smem_big(Sm& sm, char* base)
     sm.red_part = sm.yv + CB;
     sm.red_out = sm.red_part + (BIG_BLOCK / 32) * 32;
     sm.flag = (int*)(sm.red_out + 32);
+    sm.cst = (CState*)(sm.flag + 8);
     sm.Lf = nullptr;
     sm.lcap = 0;
 }
@@ -608,11 +611,22 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
 // Returns true if an evaluation was requested (ws.req[c] describes it; the caller schedules it), false if the candidate is
 // finished.  first = false: there is an evaluation to consume (always true except for the task that starts the candidate).
 template <int BLOCK, bool BIG>
-__device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
+__device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
                           Sm& sm, const sdsm_out& out, double* trace, int task_small_cells)
 {
     const int tid = threadIdx.x;
-    CState S = ws.cstate[c];                 // every thread keeps its own copy; all threads compute the same scalars
+    // The candidate's state lives in shared memory while the task runs, one copy per warp: all threads compute the same
+    // scalars (warp-uniform code: the lanes of a warp read and write their copy in lock-step), and the ~60 doubles neither
+    // fit the registers next to everything else nor belong in per-thread local memory (256 copies = 130 KB, i.e. L2 latency
+    // on every access: ncu showed control tasks of small systems at 39 us).
+    static_assert(sizeof(CState) % 8 == 0, "CState is copied in 8-byte words");
+    CState& S = sm.cst[tid >> 5];
+    {
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(ws.cstate + c);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(&S);
+        for (int i = tid & 31; i < (int)(sizeof(CState) / 8); i += 32) dst[i] = src[i];
+        __syncwarp();
+    }
     Prob P;
     setup_problem(P, par, cd, ci, ws);
     const int ld = P.ld;
@@ -986,8 +1000,12 @@ __device__ __noinline__ bool ctrl_step(const Par& par, const Img& img, const sds
     }
 #undef REQUEST
     __syncthreads();
+    if (tid < 32) {
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(&S);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(ws.cstate + c);
+        for (int i = tid; i < (int)(sizeof(CState) / 8); i += 32) dst[i] = src[i];
+    }
     if (tid == 0) {
-        ws.cstate[c] = S;
         if (requested) {
             EvalReq rq;
             rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = S.z * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;

@@ -158,8 +158,15 @@ __device__ __noinline__ void stage_chunk(char* stage, const double* __restrict__
     cp_async4(RC + lane, prc + p);
     const float* gp = gcell + p;
     float* gs = G + lane;
+    // rolled: the code of the evaluation items must stay small (instruction cache)
+    int a = 0;
 #pragma unroll 1
-    for (int a = 0; a < na; ++a) { cp_async4(gs, gp); gp += npix; gs += 32; }     // rolled: the code of the evaluation items must stay small (instruction cache)
+    for (; a + 4 <= na; a += 4) {
+        cp_async4(gs, gp); cp_async4(gs + 32, gp + npix); cp_async4(gs + 64, gp + 2 * npix); cp_async4(gs + 96, gp + 3 * npix);
+        gp += 4 * npix; gs += 128;
+    }
+#pragma unroll 1
+    for (; a < na; ++a) { cp_async4(gs, gp); gp += npix; gs += 32; }
 }
 
 // Returns, in lane e, the cell's local gradient entry e (e < 6 + na), and in lane 31 its value.
@@ -215,7 +222,12 @@ __device__ __noinline__ double cell_value_grad(const double* __restrict__ py, co
         // function: with the 32 accumulators that would not fit the 128 registers two resident CTAs per SM allow
         const volatile float* G2 = G;
 #pragma unroll
-        for (int a = 0; a < NSLOT; ++a) if (a < na) acc[6 + a] = fma(ux, (double)G2[a * 32], acc[6 + a]);
+        for (int g = 0; g < NSLOT; g += 5) {
+            if (g < na) {                             // (warp-uniform) nothing is issued for the slots beyond the cell's last one
+#pragma unroll
+                for (int a = g; a < g + 5; ++a) if (a < na) acc[6 + a] = fma(ux, (double)G2[a * 32], acc[6 + a]);
+            }
+        }
         slot = (slot + 1 == STAGES) ? 0 : slot + 1;
         slot_in = (slot_in + 1 == STAGES) ? 0 : slot_in + 1;
     }
@@ -321,7 +333,7 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
         // this cell sits at the mirrored neighbour position), so that the control task sums 25 contiguous numbers per
         // grid point instead of chasing cell -> mask -> scratch entry
         const int a = lane - 6;
-        xig[(size_t)slotj[a] * NSLOT + (NSLOT - 1 - nth_set_bit(am, a))] = tot;
+        xig[(size_t)slotj[a] * NSLOT + (NSLOT - 1 - slotj[32 + a])] = tot;
     }
     __syncwarp();
     if (HESS) cell_hessian(py, prc, gcell, npix, na, xr, xc, x, tol, Tt, XI, sh);
@@ -350,7 +362,7 @@ __device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __res
         if (lane == 0) i = atomicAdd(s_next, 1);
         i = __shfl_sync(0xffffffffu, i, 0);
         if (i >= count) break;
-        eval_cell(par, cands, ws, c, ci, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * 32);
+        eval_cell(par, cands, ws, c, ci, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * SLOTJ_INTS);
     }
 }
 
@@ -381,8 +393,10 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     const int na = __popc(am);
     const int ca = cell / cw, cb = cell - ca * cw;
     __syncwarp();
+    if (lane < NSLOT && ((am >> lane) & 1u)) slotj[32 + __popc(am & ((1u << lane) - 1u))] = lane;     // slot of the cell's e-th active entry
+    __syncwarp();
     if (lane < na) {
-        const int s = nth_set_bit(am, lane);
+        const int s = slotj[32 + lane];
         slotj[lane] = ws.cellmap[cell_off + (ca + s / 5 - NC) * cw + (cb + s % 5 - NC)];
     }
     __syncwarp();

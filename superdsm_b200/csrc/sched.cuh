@@ -124,7 +124,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
 {
     constexpr int BLOCK = SOLVE_BLOCK;
     extern __shared__ __align__(16) char smem_solve[];
-    __shared__ int s_slotj[EVAL_WARPS * 32];
+    __shared__ int s_slotj[EVAL_WARPS * SLOTJ_INTS];
     __shared__ uint2 s_task;
     __shared__ int s_flag, s_next;
     __shared__ unsigned long long s_base[2];
@@ -136,7 +136,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     if ((int)blockIdx.x >= args.n_ctrl_ctas) {
         // ---- evaluation warps: independent consumers of ws.qe ----
         double* Tt = (double*)smem_solve + warp * TILE_DOUBLES;      // TILE_DOUBLES >= HG_ACC
-        int* slotj = s_slotj + warp * 32;
+        int* slotj = s_slotj + warp * SLOTJ_INTS;
         unsigned long long cyc_idle = 0, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0}, cyc_hg = 0, n_hg = 0;
         unsigned n_popped = 0;
         for (;;) {
@@ -179,7 +179,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     }
 
     // ---- control CTAs: one control task at a time, from ws.qc ----
-    unsigned long long cyc_ctrl = 0, cyc_idle = 0, n_ctrl = 0, n_promoted = 0;
+    unsigned long long cyc_ctrl = 0, cyc_idle = 0, n_ctrl = 0, n_promoted = 0, cyc_big = 0, n_big = 0;
     unsigned n_popped = 0;
     for (;;) {
         if (tid == 0) {
@@ -252,12 +252,17 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     for (int j = 0; j < ci.m; j += HG_WARPS) { hg_task(par, cands, ws, c, j, (double*)smem_solve); __syncthreads(); }
             }
         }
-        if (tid == 0) { cyc_ctrl += (unsigned long long)(clock64() - c0); n_ctrl += 1; }
+        if (tid == 0) {
+            const unsigned long long dc = (unsigned long long)(clock64() - c0);
+            cyc_ctrl += dc; n_ctrl += 1;
+            if (6 + ws.cinfo[c].m > SMALL_N_MAX) { cyc_big += dc; n_big += 1; }
+        }
     }
     if (tid == 0) {
         atomicAdd(ws.counters + Q_CYC_CTRL, cyc_ctrl); atomicAdd(ws.counters + Q_CYC_IDLE, cyc_idle); atomicAdd(ws.counters + Q_N_CTRL, n_ctrl);
         atomicAdd(ws.counters + Q_CYC_TOTAL, (unsigned long long)(clock64() - c_begin));
         if (n_promoted) atomicAdd(ws.counters + Q_N_PROMOTED, n_promoted);
+        atomicAdd(ws.counters + Q_CYC_CTRL_BIG, cyc_big); atomicAdd(ws.counters + Q_N_CTRL_BIG, n_big);
     }
 }
 
@@ -290,7 +295,7 @@ __global__ void __launch_bounds__(SOLVE_BLOCK)
 k_diag_eval_cells(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws)
 {
     extern __shared__ __align__(16) char smem_solve[];
-    __shared__ int s_slotj[EVAL_WARPS * 32];
+    __shared__ int s_slotj[EVAL_WARPS * SLOTJ_INTS];
     __shared__ int s_next;
     const int n_ne = ws.cinfo[c].n_ne;
     for (int first = blockIdx.x * EVAL_CELLS; first < n_ne; first += gridDim.x * EVAL_CELLS) {
@@ -403,7 +408,7 @@ __global__ void __launch_bounds__(SOLVE_BLOCK, 2)
 k_sweep(Par par, const sdsm_cand* __restrict__ cands, WS ws, int rows)
 {
     extern __shared__ __align__(16) char smem_solve[];
-    __shared__ int s_slotj[EVAL_WARPS * 32];
+    __shared__ int s_slotj[EVAL_WARPS * SLOTJ_INTS];
     __shared__ int s_next;
     const unsigned long long n_tasks = ws.counters[Q_TAIL];
     for (unsigned long long i = blockIdx.x; i < n_tasks; i += gridDim.x) {

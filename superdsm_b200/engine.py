@@ -170,6 +170,7 @@ class Engine(object):
         for j, kind in enumerate(('poly_f', 'poly_h', 'xi_f', 'xi_h')):
             out['cyc_' + kind], out['n_' + kind] = int(st[16 + j]), int(st[20 + j])
         out['q_head_hi'], out['q_tail_hi'], out['n_promoted'] = int(st[24]), int(st[25]), int(st[26])
+        out['cyc_ctrl_big'], out['n_ctrl_big'] = int(st[27]), int(st[28])
         return out
 
     def finish_times_us(self, ws=None, n=None):
