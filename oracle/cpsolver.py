@@ -13,7 +13,7 @@ c = (0, 1), one nonlinear constraint, scalar slack s, multiplier z and Nesterov-
 scaling d = sqrt(s/z), lambda = sqrt(s z).  With no linear constraints the ``chol2`` KKT
 solver reduces to a Cholesky factorisation of  H = z * Hess f(x).
 
-The CUDA solver (``superdsm_b200/csrc/solver.cuh``) implements exactly the state machine
+The CUDA solver (``superdsm_b200/csrc/ctrl.cuh``) implements exactly the state machine
 below; the two are compared iterate-for-iterate in ``tests/``.
 """
 import math
