@@ -239,6 +239,11 @@ def run_gpu(args):
         hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
         peak_src = 'MEASURED_PEAKS.json hbm_gbs (of measured)' if 'hbm_gbs' in peaks else '6650 GB/s (of fallback)'
         dfma = eng.dfma_peak_gflops()
+        traffic, traffic_src = None, None          # dram bytes of one k_solve launch, from the last `ncu --set full` capture
+        try:
+            tj = json.load(open(os.path.join(ROOT, 'profiles', 'ksolve_traffic.json')))
+            traffic, traffic_src = float(tj['dram_bytes_per_launch']), tj['source']
+        except Exception: pass
         ms_per_step = total_ms_max / args.steps
         solver_ms = float(np.mean(step_ms))          # the solver kernel is >99% of a step (profiles/), both on this stream
         achieved = alg_bytes / (solver_ms * 1e-3) / 1e9
@@ -255,7 +260,7 @@ def run_gpu(args):
                     'd2h_bytes_per_step': int(d2h), 'includes': 'host EDT + descriptors, pinned H2D of y/atoms/descriptors, solve, D2H, Object materialisation'},
             'gpu_launches': int(gpu_launches),
             'roofline': {'kernel': 'k_solve (persistent solver: control CTAs + evaluation warps fed by device-side priority queues)', 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak,
-                         'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': None, 'peak_source': peak_src,
+                         'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': traffic, 'traffic_source': traffic_src, 'peak_source': peak_src,
                          'algorithmic_bytes_per_launch': alg_bytes,
                          'fp64': {'achieved_gflops': alg_flops / (solver_ms * 1e-3) / 1e9, 'peak_gflops': dfma,
                                   'frac': alg_flops / (solver_ms * 1e-3) / 1e9 / dfma, 'peak_source': 'register-resident DFMA loop measured in this run',

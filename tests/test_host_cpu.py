@@ -98,3 +98,45 @@ def test_engine_fails_loudly_without_gpu():
     import torch
     if torch.cuda.is_available(): pytest.skip('GPU present')
     with pytest.raises(engine.SolverError, match='no CPU fallback'): engine.Engine(0)
+
+
+def _gloo_worker(rank, world, port, out_path):
+    import os
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from superdsm_b200 import sharding
+    rng = np.random.default_rng(7)                       # same data on both ranks
+    atoms = rng.integers(0, 40, (64, 64)).astype(np.int32)
+    fps = [set(rng.choice(np.arange(1, 40), size=int(rng.integers(1, 4)), replace=False).tolist()) for _ in range(57)]
+    objs = []
+    for fp in fps:
+        o = objects.Object(); o.footprint = fp; objs.append(o)
+    solved_here = []
+
+    def fake_solve(shard, y, atoms_, cfg, log):        # stands in for the CUDA engine: a state that depends on the footprint only
+        for k, o in enumerate(shard):
+            st = objects.Object(); st.footprint = set(o.footprint)
+            st.energy = float(sum(o.footprint)) * cfg['scale']; st.on_boundary = False; st.is_optimal = True; st.processing_time = 0.0
+            st.fg_offset = np.array([min(o.footprint), 0]); st.fg_fragment = np.ones((1, len(o.footprint)), bool)
+            solved_here.append(sorted(o.footprint))
+            yield k, st, (min(o.footprint) % 5 == 0)
+    fb = sharding.compute_objects_sharded(objs, None, atoms, dict(scale=2.0), None, solve_shard=fake_solve)
+    ok = all(o.energy == 2.0 * sum(o.footprint) and o.fg_fragment.shape[1] == len(o.footprint) for o in objs)
+    np.save(out_path % rank, np.array([int(ok), fb, len(solved_here), len(objs)]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_gloo_sharding(tmp_path):
+    """world_size 2 on gloo: every candidate is solved by exactly one rank and every rank ends up with all results."""
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0)); port = s.getsockname()[1]
+    out = str(tmp_path / 'r%d.npy')
+    mp.spawn(_gloo_worker, args=(2, port, out), nprocs=2, join=True)
+    r0, r1 = np.load(out % 0), np.load(out % 1)
+    assert r0[0] == 1 and r1[0] == 1                     # all objects computed on both ranks
+    assert r0[1] == r1[1] and r0[1] > 0                   # same fallback count everywhere
+    assert r0[2] + r1[2] == r0[3] and min(r0[2], r1[2]) > 0    # disjoint shards covering the batch
