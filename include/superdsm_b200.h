@@ -19,9 +19,13 @@
  * stream; nothing synchronises.  Errors are integer codes (0 = ok), solver trouble is per-candidate data
  * (status word), never a C++ exception.  One context per device; a context is not thread-safe.
  *
- * Environment (read by sdsm_create): SDSM_SOLO_CELLS (default 8) -- candidates with at most this many pixel cells run
- * their whole chain of solver steps inside one CTA; SDSM_TASK_SMALL_CELLS (default 512) -- candidates with at most this many
- * cells get evaluation tasks of one cell per warp (more CTAs per evaluation, shorter links); SDSM_TIMEOUT_S (default 60) -- watchdog of the persistent solver kernel.
+ * Environment (read by sdsm_create), all optional tuning knobs of the persistent solver kernel:
+ *   SDSM_CTRL_CTAS (48)   CTAs that run control tasks; the warps of all other CTAs run evaluation / Hessian-row items
+ *   SDSM_SOLO_CELLS (32)  candidates with at most this many pixel cells run their whole chain inside one control CTA
+ *   SDSM_TASK_SMALL_CELLS (512)  candidates with at most this many cells get evaluation items of one cell (else 4)
+ *   SDSM_HI_FRAC (0.02)   share of the batch (most expensive candidates first) whose tasks are urgent from the start
+ *   SDSM_HI_EVALS (200)   a candidate that has needed more evaluations than this becomes urgent
+ *   SDSM_TIMEOUT_S (60)   watchdog of the persistent solver kernel
  */
 #ifndef SUPERDSM_B200_H
 #define SUPERDSM_B200_H
@@ -145,8 +149,9 @@ int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_ca
  * chains per thread); *flops receives the floating-point operations of the launch.  Time it with CUDA events. */
 int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flops, void* stream);
 
-/* Diagnostics: h_us[n_cand] receives, for every candidate of the last sdsm_solve_batch() on this workspace, the time (in
- * microseconds after the solver kernel started) at which its fit finished; SYNCHRONISES the stream. */
+/* Diagnostics: h_us[2 * n_cand] receives, for every candidate of the last sdsm_solve_batch() on this workspace, the time (in
+ * microseconds after the solver kernel started) at which its fit finished, then [n_cand ..] the time it spent in control
+ * tasks (microseconds); SYNCHRONISES the stream. */
 int sdsm_finish_times(sdsm_ctx* ctx, const void* d_workspace, int32_t* h_us, void* stream);
 
 /* Measurement aid: `repeats` sweeps of the evaluation tasks (rows = 0; value + gradient, plus the per-cell Hessians if

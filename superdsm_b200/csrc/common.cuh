@@ -72,6 +72,7 @@ struct CState {
     double bt, uz0, vt, gux, gux_res, gex;
     double sigma, eta, step, dt, dz, ds, dsdz, dz2, ds2;
     double val1, psi_last, energy;
+    unsigned long long ns_ctrl;            // diagnostics: time spent in this candidate's control tasks so far (ns)
     int32_t pc, stage, iters, relaxed, pass, use_xi;
     int32_t req_vec, req_gvec, req_h;      // the pending evaluation: point, where the gradient goes, Hessian wanted
     int32_t status, bits, it1, it2, it3, nf, nh, have1, r_ipm;
@@ -317,7 +318,7 @@ __device__ __forceinline__ bool fp_member(int lab, const int32_t* fp, int n)
 enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG, Q_CYC_CTRL, Q_CYC_IDLE, Q_N_EVAL, Q_N_HG, Q_N_CTRL, Q_CYC_TOTAL, Q_T0,
        Q_CYC_WIDLE = 13 /* idle cycles of the evaluation warps */, Q_CYC_WTOTAL = 14 /* lifetime cycles of the evaluation warps */,
        Q_CYC_KIND = 16 /* [4]: evaluation-item cycles by kind = use_xi * 2 + want_h */, Q_N_KIND = 20 /* [4]: items by kind */,
-       Q_HEAD_HI = 24, Q_TAIL_HI = 25, Q_N_PROMOTED = 26, Q_CYC_CTRL_BIG = 27 /* control tasks of systems > SMALL_N_MAX */, Q_N_CTRL_BIG = 28 };
+       Q_HEAD_HI = 24, Q_TAIL_HI = 25, Q_N_PROMOTED = 26, Q_CYC_CTRL_BIG = 27 /* control tasks of systems > SMALL_N_MAX */, Q_N_CTRL_BIG = 28, Q_CYC_CHOL_BIG = 29, Q_N_CHOL_BIG = 30, Q_CYC_SOLVE_BIG = 31 /* first of the two solves per iteration */ };
 constexpr int HOT_STRIDE = 16;   // unsigned long longs = 128 bytes
 enum { H_EV_HEAD = 0, H_EV_TAIL = 1, H_HEAD_LO = 2, H_TAIL_LO = 3, H_HEAD_HI = 4, H_TAIL_HI = 5, H_AVAIL_LO = 6, H_AVAIL_HI = 7, N_HOT = 8 };
 enum { G_DONE = 0, G_ABORT = 1, N_GLOB = 2 };

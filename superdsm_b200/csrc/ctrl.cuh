@@ -38,7 +38,8 @@ struct Sm {
     int*    flag;      // [8]
     int     lcap;      // doubles available for the factor
     CState* cst;       // [CTRL_WARPS] the candidate's state while a control task runs, one copy per warp (see ctrl_step)
-    double *D, *Xj, *yv;   // k_ctrl_big only: diagonal block, panel block, solved block (see cholesky_big)
+    double *D, *Xj, *yv;   // large systems only: diagonal block, panel block, solved block (see cholesky_big)
+    double *Wt;            // large systems only: one CB x CB_LD tile per warp (coalesced staging of global rows)
 };
 constexpr int CTRL_BPAD = 128;
 __host__ __device__ inline size_t ctrl_smem_bytes(int lcap) { return sizeof(double) * (size_t)(lcap + CTRL_BPAD + CTRL_WARPS * 32 + 32) + sizeof(int) * 8 + CTRL_WARPS * sizeof(CState); }
@@ -53,7 +54,7 @@ __device__ __forceinline__ void carve_smem(Sm& sm, char* base, int lcap)
     sm.flag = (int*)(sm.red_out + 32);
     sm.cst = (CState*)(sm.flag + 8);
     sm.lcap = lcap;
-    sm.D = sm.Xj = sm.yv = nullptr;
+    sm.D = sm.Xj = sm.yv = sm.Wt = nullptr;
 }
 
 __device__ __forceinline__ void setup_problem(Prob& P, const Par& par, const sdsm_cand& cd, const CInfo& ci, const WS& ws)
@@ -349,15 +350,17 @@ __device__ void chol_solve(const double* L, int N, double* v, double* bv, int bv
 // non-positive pivot).  One CTA of BLOCK threads.
 
 constexpr int CB = 32;               // panel width
-constexpr int CB_LD = CB + 1;
+constexpr int CB_LD = CB + 1;      // row stride of tiles accessed by rows and by columns
+constexpr int TL = CB + 4;         // row stride of tiles read as DMMA fragments (= 4 mod 16: conflict-free)
 
-constexpr size_t BIG_SMEM = sizeof(double) * (2 * CB * CB_LD + CB + (BIG_BLOCK / 32) * 32 + 32) + sizeof(int) * 8 + (BIG_BLOCK / 32) * sizeof(CState);
+constexpr size_t BIG_SMEM = sizeof(double) * ((2 + BIG_BLOCK / 32) * CB * TL + CB + (BIG_BLOCK / 32) * 32 + 32) + sizeof(int) * 8 + (BIG_BLOCK / 32) * sizeof(CState);
 
 __device__ __forceinline__ void carve_smem_big(Sm& sm, char* base)
 {
     sm.D = (double*)base;
-    sm.Xj = sm.D + CB * CB_LD;
-    sm.yv = sm.Xj + CB * CB_LD;
+    sm.Xj = sm.D + CB * TL;
+    sm.Wt = sm.Xj + CB * TL;
+    sm.yv = sm.Wt + (BIG_BLOCK / 32) * CB * TL;
     sm.red_part = sm.yv + CB;
     sm.red_out = sm.red_part + (BIG_BLOCK / 32) * 32;
     sm.flag = (int*)(sm.red_out + 32);
@@ -366,11 +369,19 @@ __device__ __forceinline__ void carve_smem_big(Sm& sm, char* base)
     sm.lcap = 0;
 }
 
+// Left-looking by 32-column panels: the rows of panel k first receive the contributions of all earlier panels
+//   A[i, k-panel] -= sum_j A[i, j-panel] A[k-rows, j-panel]^T
+// as 32 x 32 x 32 tile products on the FP64 tensor cores (DMMA.8x8x4), then the diagonal block is factorised by warp 0 and
+// the rows below are solved against it.  Global memory (the factor lives in L2) is only touched with coalesced rows, staged
+// through shared-memory tiles: two tiles of A[k-rows, .] shared by the CTA per step, one tile per warp for its own rows.
+// (The right-looking version this replaces spent 1-3 ms per factorisation at N = 300-450 waiting for L2 round trips.)
 template <int BLOCK>
 __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = BLOCK / 32;
+    const int fr = lane >> 2, fk = lane & 3;                 // DMMA fragment coordinates (eval.cuh::dmma884)
+    double* W = sb.Wt + warp * CB * TL;
     __syncthreads();
     for (int i = warp; i < N; i += NW)
         for (int j = lane; j <= i; j += 32) A[(size_t)i * N + j] = H[(size_t)i * N + j];
@@ -378,14 +389,61 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
     __syncthreads();
     for (int k0 = 0; k0 < N; k0 += CB) {
         const int kw = min(CB, N - k0);
-        // (a) diagonal block -> shared memory, factorised by warp 0 (lane = row)
+        const int nrb = (N - k0 + CB - 1) / CB;              // row blocks of the panel; block 0 holds the diagonal block
+        // (1) contributions of the earlier panels, two at a time
+        for (int j0 = 0; j0 < k0; j0 += 2 * CB) {
+            const int nt = (j0 + CB < k0) ? 2 : 1;
+            __syncthreads();                                 // the tiles of the previous step are no longer in use
+            for (int e = tid; e < nt * CB * CB; e += BLOCK) {
+                const int t = e / (CB * CB), r = (e / CB) % CB, q = e % CB;
+                (t ? sb.Xj : sb.D)[r * TL + q] = r < kw ? A[(size_t)(k0 + r) * N + j0 + t * CB + q] : 0.0;
+            }
+            __syncthreads();
+            for (int ib = warp; ib < nrb; ib += NW) {
+                const int i0 = k0 + ib * CB, nr = min(CB, N - i0);
+                double c[4][4][2];
+#pragma unroll
+                for (int I = 0; I < 4; ++I)
+#pragma unroll
+                    for (int J = 0; J < 4; ++J) { c[I][J][0] = 0.0; c[I][J][1] = 0.0; }
+                for (int t = 0; t < nt; ++t) {
+                    const double* T = t ? sb.Xj : sb.D;
+                    __syncwarp();
+#pragma unroll 8
+                    for (int r = 0; r < CB; ++r) W[r * TL + lane] = r < nr ? A[(size_t)(i0 + r) * N + j0 + t * CB + lane] : 0.0;
+                    __syncwarp();
+#pragma unroll 2
+                    for (int kk = 0; kk < 8; ++kk) {
+                        double af[4], bf[4];
+#pragma unroll
+                        for (int X = 0; X < 4; ++X) { af[X] = W[(8 * X + fr) * TL + 4 * kk + fk]; bf[X] = T[(8 * X + fr) * TL + 4 * kk + fk]; }
+#pragma unroll
+                        for (int I = 0; I < 4; ++I)
+#pragma unroll
+                            for (int J = 0; J < 4; ++J) dmma884(c[I][J][0], c[I][J][1], af[I], bf[J]);
+                    }
+                }
+                // subtract: staged through the warp's tile so that the rows are updated with coalesced accesses
+                __syncwarp();
+#pragma unroll
+                for (int I = 0; I < 4; ++I)
+#pragma unroll
+                    for (int J = 0; J < 4; ++J) { W[(8 * I + fr) * TL + 8 * J + 2 * fk] = c[I][J][0]; W[(8 * I + fr) * TL + 8 * J + 2 * fk + 1] = c[I][J][1]; }
+                __syncwarp();
+                if (lane < kw)
+                    for (int r = 0; r < nr; ++r)
+                        if (k0 + lane <= i0 + r) A[(size_t)(i0 + r) * N + k0 + lane] -= W[r * TL + lane];      // lower triangle only
+            }
+        }
+        __syncthreads();
+        // (2) diagonal block -> shared memory, factorised by warp 0 (lane = row)
         for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
         __syncthreads();
         if (warp == 0) {
             for (int cc = 0; cc < kw; ++cc) {
                 const double dk = sb.D[cc * CB_LD + cc];
                 if (!(dk > 0.0) || !isfinite(dk)) { if (lane == 0) sb.flag[0] = 1; break; }
-                const double rinv = 1.0 / sqrt(dk);
+                const double rinv = rsqrt(dk);
                 __syncwarp();
                 if (lane == cc) sb.D[cc * CB_LD + cc] = rinv;
                 if (lane > cc && lane < kw) {
@@ -405,85 +463,67 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
         for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) A[(size_t)(k0 + r) * N + k0 + q] = sb.D[r * CB_LD + q]; }
         const int r0 = k0 + kw;
         if (r0 >= N) break;
-        // (b) panel: rows below the block, X = A[i, k0:k0+kw] D^-T, one thread per row
-        for (int i = r0 + tid; i < N; i += BLOCK) {
-            double* ar = A + (size_t)i * N + k0;
-            double r[CB];
+        // (3) rows below the block: X = A[i, k0:k0+kw] D^-T.  A warp takes 32 rows at a time: the 32 x kw tile is read and
+        //     written back row by row (lane = column: coalesced) through the warp's tile and solved with lane = row (row
+        //     stride CB_LD = 33: both accesses are free of bank conflicts).
+        for (int i0 = r0 + warp * CB; i0 < N; i0 += NW * CB) {
+            const int nr = min(CB, N - i0);
+            __syncwarp();
+            for (int r = 0; r < nr; ++r) W[r * CB_LD + lane] = lane < kw ? A[(size_t)(i0 + r) * N + k0 + lane] : 0.0;
+            __syncwarp();
+            if (lane < nr) {
+                double r[CB];
 #pragma unroll
-            for (int q = 0; q < CB; ++q) r[q] = q < kw ? ar[q] : 0.0;
+                for (int q = 0; q < CB; ++q) r[q] = W[lane * CB_LD + q];
 #pragma unroll
-            for (int q = 0; q < CB; ++q) {
-                if (q < kw) {
-                    double v = r[q];
+                for (int q = 0; q < CB; ++q) {
+                    if (q < kw) {
+                        double v = r[q];
 #pragma unroll
-                    for (int p = 0; p < q; ++p) v = fma(-r[p], sb.D[q * CB_LD + p], v);
-                    r[q] = v * sb.D[q * CB_LD + q];
+                        for (int p = 0; p < q; ++p) v = fma(-r[p], sb.D[q * CB_LD + p], v);
+                        r[q] = v * sb.D[q * CB_LD + q];
+                    }
                 }
-            }
 #pragma unroll
-            for (int q = 0; q < CB; ++q) if (q < kw) ar[q] = r[q];
+                for (int q = 0; q < CB; ++q) W[lane * CB_LD + q] = r[q];
+            }
+            __syncwarp();
+            if (lane < kw) for (int r = 0; r < nr; ++r) A[(size_t)(i0 + r) * N + k0 + lane] = W[r * CB_LD + lane];
         }
-        __syncthreads();
-        // (c) trailing update A[ib, jb] -= X[ib] X[jb]^T for the 32 x 32 blocks jb <= ib below the panel;
-        //     all warps share X[jb] (shared memory), each takes block rows ib = jb, jb + NW, ...; lane = row
-        const int nbt = (N - r0 + CB - 1) / CB;
-        for (int jb = 0; jb < nbt; ++jb) {
-            const int j0 = r0 + jb * CB, jw = min(CB, N - j0);
-            __syncthreads();
-            for (int e = tid; e < CB * CB; e += BLOCK) {
-                const int r = e / CB, q = e - r * CB;
-                sb.Xj[r * CB_LD + q] = (r < jw && q < kw) ? A[(size_t)(j0 + r) * N + k0 + q] : 0.0;
-            }
-            __syncthreads();
-            for (int ib = jb + warp; ib < nbt; ib += NW) {
-                const int i = r0 + ib * CB + lane;
-                if (i >= N) continue;
-                const double* xr = A + (size_t)i * N + k0;
-                double xv[CB];
-#pragma unroll
-                for (int q = 0; q < CB; ++q) xv[q] = q < kw ? xr[q] : 0.0;
-                double* out = A + (size_t)i * N + j0;
-                const int cmax = min(jw, i - j0 + 1);      // stay inside the lower triangle
-                for (int cc = 0; cc < cmax; ++cc) {
-                    double a = 0;
-#pragma unroll
-                    for (int q = 0; q < CB; ++q) a = fma(xv[q], sb.Xj[cc * CB_LD + q], a);
-                    out[cc] -= a;
-                }
-            }
-        }
-        __syncthreads();
+        // the next panel's step (1) starts with a CTA barrier
     }
     return true;
 }
 
 // v := (A A^T)^-1 v with the factor of cholesky_big; blocked forward / backward substitution, v in global memory.
-// Per 32-block: the diagonal block is staged in shared memory and solved by warp 0, then every thread updates one row.
+// Per 32-block: the contribution of the part already solved is gathered by all warps (coalesced rows of A), the diagonal
+// block is staged in shared memory and solved by warp 0.
 template <int BLOCK>
 __device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = BLOCK / 32;
     __syncthreads();
     // forward: L y = v
     for (int k0 = 0; k0 < N; k0 += CB) {
         const int kw = min(CB, N - k0);
         for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        for (int r = warp; r < kw; r += NW) {                // y_k = v_k - L[k-rows, 0:k0] y[0:k0], a warp per row
+            const double* ar = A + (size_t)(k0 + r) * N;
+            double a = 0;
+            for (int q = lane; q < k0; q += 32) a = fma(ar[q], v[q], a);
+            a = warp_sum(a);
+            if (lane == 0) sb.yv[r] = v[k0 + r] - a;
+        }
         __syncthreads();
         if (warp == 0) {
-            double b = lane < kw ? v[k0 + lane] : 0.0;
+            double b = lane < kw ? sb.yv[lane] : 0.0;
             for (int cc = 0; cc < kw; ++cc) {
                 const double yk = __shfl_sync(0xffffffffu, b, cc) * sb.D[cc * CB_LD + cc];
                 if (lane == cc) b = yk;
                 else if (lane > cc && lane < kw) b = fma(-sb.D[lane * CB_LD + cc], yk, b);
             }
-            if (lane < kw) { v[k0 + lane] = b; sb.yv[lane] = b; }
-        }
-        __syncthreads();
-        for (int i = k0 + kw + tid; i < N; i += BLOCK) {
-            const double* ar = A + (size_t)i * N + k0;
-            double a = 0;
-            for (int q = 0; q < kw; ++q) a = fma(ar[q], sb.yv[q], a);
-            v[i] -= a;
+            if (lane < kw) v[k0 + lane] = b;
         }
         __syncthreads();
     }
@@ -491,21 +531,26 @@ __device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
     for (int k0 = ((N - 1) / CB) * CB; k0 >= 0; k0 -= CB) {
         const int kw = min(CB, N - k0);
         for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        {   // x_k = y_k - L[rows below, k-columns]^T x[rows below]: lane = column (coalesced), the rows dealt to the warps
+            double a = 0;
+            if (lane < kw) for (int i = k0 + kw + warp; i < N; i += NW) a = fma(A[(size_t)i * N + k0 + lane], v[i], a);
+            sb.red_part[warp * 32 + lane] = a;
+        }
         __syncthreads();
         if (warp == 0) {
-            double b = lane < kw ? v[k0 + lane] : 0.0;
+            double b = 0;
+            if (lane < kw) {
+                double a = 0;
+#pragma unroll
+                for (int w = 0; w < NW; ++w) a += sb.red_part[w * 32 + lane];
+                b = v[k0 + lane] - a;
+            }
             for (int cc = kw - 1; cc >= 0; --cc) {
                 const double xk = __shfl_sync(0xffffffffu, b, cc) * sb.D[cc * CB_LD + cc];
                 if (lane == cc) b = xk;
                 else if (lane < cc) b = fma(-sb.D[cc * CB_LD + lane], xk, b);
             }
-            if (lane < kw) { v[k0 + lane] = b; sb.yv[lane] = b; }
-        }
-        __syncthreads();
-        for (int i = tid; i < k0; i += BLOCK) {
-            double a = 0;
-            for (int q = 0; q < kw; ++q) a = fma(A[(size_t)(k0 + q) * N + i], sb.yv[q], a);
-            v[i] -= a;
+            if (lane < kw) v[k0 + lane] = b;
         }
         __syncthreads();
     }
@@ -718,7 +763,9 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             }
             if (S.iters == 0) { S.d = sqrt(S.s / S.z); S.lm = sqrt(S.s * S.z); }
             S.lmsq = S.lm * S.lm;
+            const long long tc0 = clock64();
             const bool ok = BIG ? cholesky_big<BLOCK>(P.H, Nc, P.Lg, sm) : cholesky<BLOCK>(P.H, Nc, Lf, sm);
+            if (BIG && tid == 0) { atomicAdd(ws.counters + Q_CYC_CHOL_BIG, (unsigned long long)(clock64() - tc0)); atomicAdd(ws.counters + Q_N_CHOL_BIG, 1ull); }
             hres_alt = false;
             if (ok) { S.pc = PC_KKT; break; }
             if (S.iters == 0) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }                 // ValueError("Rank(A) < p or ...")
@@ -756,7 +803,9 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             const double bt = S.bt;
             __syncthreads();
             for (int i = tid; i < Nc; i += BLOCK) { const double bx = -(z * g[i]); tv[i] = bx + g[i] * bt; }
+            const long long ts0 = clock64();
             if (BIG) chol_solve_big<BLOCK>(P.Lg, Nc, tv, sm); else chol_solve<BLOCK>(Lf, Nc, tv, bv, bvcap);
+            if (BIG && tid == 0) atomicAdd(ws.counters + Q_CYC_SOLVE_BIG, (unsigned long long)(clock64() - ts0));
             S.uz0 = -d * bt;
             const double wz3 = S.uz0 / d;
             S.vt = bt + wz3;

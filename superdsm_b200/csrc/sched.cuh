@@ -211,14 +211,17 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     __syncthreads();
                     if (stop) { if (tid == 0) q_abort(ws); break; }
                 }
+                const unsigned long long t_link = tid == 0 ? globaltimer_ns() : 0ull;
                 const bool big = (ws.cstate[c].use_xi ? 6 + ci.m : 6) > SMALL_N_MAX;
                 Sm sm;
                 bool requested;
                 if (big) { carve_smem_big(sm, smem_solve); requested = ctrl_step<BLOCK, true>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
                 else { carve_smem(sm, smem_solve, args.lcap); requested = ctrl_step<BLOCK, false>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
+                if (tid == 0) ws.cstate[c].ns_ctrl += globaltimer_ns() - t_link;
                 if (!requested) {
                     if (tid == 0) {
                         ws.pending[c] = (int32_t)((globaltimer_ns() - ws.counters[Q_T0]) / 1000ull);   // diagnostics: finish time, us
+                        ws.prio[c] = (int32_t)(ws.cstate[c].ns_ctrl / 1000ull);                        // diagnostics: time in control tasks, us
                         __threadfence();
                         atomicAdd(ws.glob + G_DONE * HOT_STRIDE, 1ull);
                     }

@@ -28,12 +28,12 @@ struct sdsm_ctx {
     int64_t P = 0, C = 0, T = 0, V = 0, M = 0, K = 0;
     int32_t n_cand = 0;
     int solve_ctas_per_sm = 1;               // resident CTAs of k_solve per SM (occupancy query)
-    int solo_cells = 8;                      // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
+    int solo_cells = 32;                     // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
     int task_small_cells = 512;              // SDSM_TASK_SMALL_CELLS: candidates up to this many cells get one cell per warp
     double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
-    double hi_frac = 0.08;                   // SDSM_HI_FRAC: this share of the batch (the most expensive candidates) is urgent from the start
-    int ctrl_ctas = 64;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
-    int hi_evals = 400;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
+    double hi_frac = 0.02;                   // SDSM_HI_FRAC: this share of the batch (the most expensive candidates) is urgent from the start
+    int ctrl_ctas = 48;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
+    int hi_evals = 200;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     std::string err;
 };
 
@@ -361,6 +361,7 @@ extern "C" int sdsm_finish_times(sdsm_ctx* ctx, const void* d_workspace, int32_t
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     CUDA_TRY(ctx, cudaMemcpyAsync(h_us, ws.pending, sizeof(int32_t) * (size_t)ctx->n_cand, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_us + ctx->n_cand, ws.prio, sizeof(int32_t) * (size_t)ctx->n_cand, cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
     return SDSM_OK;
 }

@@ -171,14 +171,16 @@ class Engine(object):
             out['cyc_' + kind], out['n_' + kind] = int(st[16 + j]), int(st[20 + j])
         out['q_head_hi'], out['q_tail_hi'], out['n_promoted'] = int(st[24]), int(st[25]), int(st[26])
         out['cyc_ctrl_big'], out['n_ctrl_big'] = int(st[27]), int(st[28])
+        out['cyc_chol_big'], out['n_chol_big'], out['cyc_solve_big'] = int(st[29]), int(st[30]), int(st[31])
         return out
 
     def finish_times_us(self, ws=None, n=None):
         """Per-candidate finish time of the last batch, microseconds after the solver kernel started (synchronises)."""
         if ws is None: ws, n = self._last[2], len(self._last[3])
-        out = np.zeros(n, dtype=np.int32)
+        out = np.zeros(2 * n, dtype=np.int32)
         self._check(self.lib.sdsm_finish_times(self.ctx, ws.data_ptr(), out.ctypes.data, self.stream.cuda_stream))
-        return out
+        self.control_times_us = out[n:]
+        return out[:n]
 
     def _check_solved(self, ws, n):
         """Raises if the watchdog of the persistent solver fired or a candidate did not finish."""
