@@ -202,3 +202,57 @@ def test_full_size_properties(eng):
         assert val <= n * np.log(2) + 1e-9                                    # never worse than the zero model
         off, frag = res.foreground(k)
         assert frag.any() and off[0] >= 0 and off[1] >= 0
+
+
+def test_c2f_normalized_energy_computer(eng):
+    """c2freganal.py:58-79 on the mirror: cluster crop -> full-frame buffer -> 6-parameter fit -> J(model) / n, cached by mask
+    hash; the value agrees with the oracle's fit of the same region."""
+    from oracle import dsm_oracle as orc
+    from superdsm_b200 import c2freganal
+    from superdsm_b200.image import Image
+    from superdsm_b200.objects import Object
+    case = GoldenCase('toy')
+    y = Image(case.y, case.y_mask)
+    atoms = case.atoms
+    fp = sorted(case.footprints[0])
+    cluster_mask = np.isin(atoms, fp)
+    cluster = y.get_region(cluster_mask, shrink=True)
+    crop = np.s_[cluster.offset[0]:cluster.offset[0] + cluster.mask.shape[0], cluster.offset[1]:cluster.offset[1] + cluster.mask.shape[1]]
+    cfg = dict(case.dsm_cfg); cfg['smooth_amount'] = np.inf
+    compute = c2freganal._get_cached_normalized_energy_computer(y, cluster)
+    obj = Object(); obj.footprint = set(fp)
+    e1 = compute(obj, cluster, atoms[crop], cfg)
+    e2 = compute(obj, cluster, atoms[crop], cfg)                 # cache hit
+    assert e1 == e2 and np.isfinite(e1)
+    # the oracle on the same region, in the full frame
+    cp_region = obj.get_cvxprog_region(cluster, atoms[crop], cfg['background_margin'])
+    full = np.zeros(case.y.shape, bool); full[cluster.full_mask] = cp_region.mask[cluster.mask]
+    keys = ('scale', 'epsilon', 'alpha', 'smooth_amount', 'smooth_subsample', 'gaussian_shape_multiplier', 'smooth_mat_dtype', 'init')
+    Jo, po, so = orc.cvxprog(case.y, full, **{k: cfg[k] for k in keys})
+    assert e1 == pytest.approx(Jo(po) / full.sum(), rel=1e-6)
+
+
+@pytest.mark.parametrize('name,kw', [('bbbc039', dict()), ('nih3t3', dict()), ('tiled4k', dict(shape=(768, 768), n=700))])
+def test_other_baseline_configs(eng, name, kw):
+    """BASELINE configs 0, 2 and 4 (BBBC039-shaped with the default configuration, NIH3T3-shaped, a crop of the 4096 x 4096
+    tiled field): the whole candidate list through the C ABI; properties for all, the oracle's fit for a few."""
+    from oracle import dsm_oracle as orc
+    from superdsm_b200 import synth, _lib
+    w = synth.make_workload(name, oversegment=2, max_set_size=3, max_candidates=400, **kw)
+    eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
+    eng.set_params(w['dsm_cfg'])
+    fps = w['footprints']
+    res = eng.solve(fps)
+    assert (res.status < _lib.ST_ERROR).all()
+    ok = res.status == _lib.ST_OPTIMAL
+    assert ok.mean() > 0.85
+    n = res.cands['n'].astype(float)
+    assert np.isfinite(res.energy).all() and (res.energy[ok] <= n[ok] * np.log(2) + 1e-9).all()
+    rng = np.random.default_rng(0)
+    small = np.argsort(n)[:max(8, len(fps) // 4)]
+    for k in rng.choice(small, size=3, replace=False):          # the oracle takes seconds per candidate: the smaller ones
+        ref = orc.compute_object(w['y'], w['y_mask'], w['atoms'], fps[k], w['dsm_cfg'])
+        tol = 1e-6 * abs(ref['energy']) + 2e-7 * ref['n'] / w['dsm_cfg']['scale']
+        assert abs(res.energy[k] - ref['energy']) <= tol, (name, k, res.energy[k], ref['energy'])
+        off, frag = res.foreground(int(k))
+        assert np.array_equal(frag, ref['fg_fragment']) and np.array_equal(off, ref['fg_offset'])
