@@ -13,7 +13,7 @@ for _ in range(2):
     t0 = time.perf_counter(); res = eng.solve(w['footprints']); dt = time.perf_counter() - t0
 print('solve', dt)
 st = eng.solver_stats(); tot = max(st['cyc_total'], 1); wtot = max(st['cyc_wtotal'], 1)
-print('ctrl CTAs: busy %.3f idle %.3f | eval warps: eval %.3f hrows %.3f idle %.3f' % (st['cyc_ctrl'] / tot, st['cyc_idle'] / tot, st['cyc_eval'] / wtot, st['cyc_hrows'] / wtot, st['cyc_widle'] / wtot),
+print('ctrl CTAs: busy %.3f idle %.3f | eval warps: eval %.3f hrows %.3f idle %.3f finish %.3f' % (st['cyc_ctrl'] / tot, st['cyc_idle'] / tot, st['cyc_eval'] / wtot, st['cyc_hrows'] / wtot, st['cyc_widle'] / wtot, st['cyc_wfin'] / wtot),
       {k: st[k] for k in st if k.startswith('n_')}, 'urgent', st['q_tail_hi'], 'of', st['q_tail'])
 print({k: (st['cyc_' + k] / max(st['n_' + k], 1)) for k in ('poly_f', 'poly_h', 'xi_f', 'xi_h')})
 print('cycles per control task: big systems %.0f (%d), small %.0f (%d)' % (st['cyc_ctrl_big'] / max(st['n_ctrl_big'], 1), st['n_ctrl_big'], (st['cyc_ctrl'] - st['cyc_ctrl_big']) / max(st['n_ctrl'] - st['n_ctrl_big'], 1), st['n_ctrl'] - st['n_ctrl_big']))

@@ -316,7 +316,7 @@ __device__ __forceinline__ bool fp_member(int lab, const int32_t* fp, int n)
 // The hot counters sit on cache lines of their own (stride HOT_STRIDE).
 
 enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG, Q_CYC_CTRL, Q_CYC_IDLE, Q_N_EVAL, Q_N_HG, Q_N_CTRL, Q_CYC_TOTAL, Q_T0,
-       Q_CYC_WIDLE = 13 /* idle cycles of the evaluation warps */, Q_CYC_WTOTAL = 14 /* lifetime cycles of the evaluation warps */,
+       Q_CYC_WIDLE = 13 /* idle cycles of the evaluation warps */, Q_CYC_WTOTAL = 14 /* lifetime cycles of the evaluation warps */, Q_CYC_WFIN = 15 /* cycles of the evaluation warps in finish_item */,
        Q_CYC_KIND = 16 /* [4]: evaluation-item cycles by kind = use_xi * 2 + want_h */, Q_N_KIND = 20 /* [4]: items by kind */,
        Q_HEAD_HI = 24, Q_TAIL_HI = 25, Q_N_PROMOTED = 26, Q_CYC_CTRL_BIG = 27 /* control tasks of systems > SMALL_N_MAX */, Q_N_CTRL_BIG = 28, Q_CYC_CHOL_BIG = 29, Q_N_CHOL_BIG = 30, Q_CYC_SOLVE_BIG = 31 /* first of the two solves per iteration */ };
 constexpr int HOT_STRIDE = 16;   // unsigned long longs = 128 bytes

@@ -1059,7 +1059,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             EvalReq rq;
             rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = S.z * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;
             rq.cpt = P.n_ne <= task_small_cells ? EVAL_WARPS : EVAL_CELLS;
-            rq.cpw = P.n_ne <= task_small_cells ? 1 : WARP_ITEM_CELLS;
+            rq.cpw = P.n_ne <= task_small_cells ? 1 : (P.n_ne <= 4 * task_small_cells ? 2 : WARP_ITEM_CELLS);
             ws.req[c] = rq;
         }
     }

@@ -85,11 +85,13 @@ __global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, in
 }
 
 // one warp: the evaluation item (c, first) = cells cell_list[first .. first + cpw) of candidate c's pending request
-__device__ __forceinline__ void eval_item(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* Tt, int* slotj)
+__device__ __forceinline__ int eval_item(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* Tt, int* slotj)
 {
     const CInfo ci = ws.cinfo[c];
-    const int count = min(ws.req[c].cpw, ci.n_ne - first);
+    const EvalReq rq = ws.req[c];
+    const int count = min(rq.cpw, ci.n_ne - first);
     for (int i = 0; i < count; ++i) eval_cell(par, cands, ws, c, ci, first + i, Tt, slotj);
+    return (rq.use_xi ? 2 : 0) + (rq.want_h ? 1 : 0);       // kind of the evaluation (statistics)
 }
 
 // the warp that finished an item of candidate c's current stage: the last one to finish starts the next stage
@@ -101,8 +103,8 @@ __device__ __forceinline__ void finish_item(const WS& ws, uint32_t type, int c)
     int next = 0;                                            // 0: not the last, 1: control task, > 1: that many T_HG items
     if (lane == 0) {
         const int old = atomicSub(ws.pending + c, 1);
-        __threadfence();
         if (old == 1) {
+            __threadfence();                                 // the other items' results, before the next stage is published
             const EvalReq rq = ws.req[c];
             next = 1;
             if (type == T_EVAL && rq.want_h && rq.use_xi) {
@@ -137,7 +139,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         // ---- evaluation warps: independent consumers of ws.qe ----
         double* Tt = (double*)smem_solve + warp * TILE_DOUBLES;      // TILE_DOUBLES >= HG_ACC
         int* slotj = s_slotj + warp * SLOTJ_INTS;
-        unsigned long long cyc_idle = 0, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0}, cyc_hg = 0, n_hg = 0;
+        unsigned long long cyc_idle = 0, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0}, cyc_hg = 0, n_hg = 0, cyc_fin = 0;
         unsigned n_popped = 0;
         for (;;) {
             uint2 task = make_uint2(0u, 0u);
@@ -156,23 +158,23 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
             const uint32_t type = task.x >> T_SHIFT;
             const int c = (int)(task.x & T_CMASK);
             if (type == T_EVAL) {
-                eval_item(par, cands, ws, c, (int)task.y, Tt, slotj);
-                const EvalReq rq = ws.req[c];
-                const int kind = (rq.use_xi ? 2 : 0) + (rq.want_h ? 1 : 0);
+                const int kind = eval_item(par, cands, ws, c, (int)task.y, Tt, slotj);
                 kcyc[kind] += (unsigned long long)(clock64() - c1); kcnt[kind] += 1;
             } else {
                 const int m = ws.cinfo[c].m;
                 for (int j = (int)task.y; j < (int)task.y + HG_ITEM_ROWS && j < m; ++j) { hg_row(par, cands, ws, c, j, Tt); __syncwarp(); }
                 cyc_hg += (unsigned long long)(clock64() - c1); n_hg += 1;
             }
+            const long long c2 = clock64();
             finish_item(ws, type, c);
+            cyc_fin += (unsigned long long)(clock64() - c2);
         }
         if (lane == 0) {
             unsigned long long ce = 0, ne = 0;
             for (int k = 0; k < 4; ++k) { atomicAdd(ws.counters + Q_CYC_KIND + k, kcyc[k]); atomicAdd(ws.counters + Q_N_KIND + k, kcnt[k]); ce += kcyc[k]; ne += kcnt[k]; }
             atomicAdd(ws.counters + Q_CYC_EVAL, ce); atomicAdd(ws.counters + Q_N_EVAL, ne);
             atomicAdd(ws.counters + Q_CYC_HG, cyc_hg); atomicAdd(ws.counters + Q_N_HG, n_hg);
-            atomicAdd(ws.counters + Q_CYC_WIDLE, cyc_idle);
+            atomicAdd(ws.counters + Q_CYC_WIDLE, cyc_idle); atomicAdd(ws.counters + Q_CYC_WFIN, cyc_fin);
             atomicAdd(ws.counters + Q_CYC_WTOTAL, (unsigned long long)(clock64() - c_begin));
         }
         return;
@@ -202,7 +204,6 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         {
             const sdsm_cand cd = cands[c];
             const CInfo ci = ws.cinfo[c];
-            const bool solo = ci.n_ne <= args.solo_cells;
             for (unsigned link = 1;; ++link) {
                 if ((link & 63u) == 0) {                    // watchdog of a chain that never leaves this CTA
                     if (tid == 0) s_flag = (globaltimer_ns() - t_start > args.timeout_ns || q_aborted(ws)) ? 1 : 0;
@@ -227,6 +228,10 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                     }
                     break;
                 }
+                // Short chains of small candidates stay in this CTA (no queue hops).  A chain that turns out long leaves it:
+                // it then finishes after the bulk of the batch, when the evaluation warps are idle and spreading its cells
+                // over them makes every link several times shorter.
+                const bool solo = ci.n_ne <= EVAL_WARPS || (ci.n_ne <= args.solo_cells && ws.cstate[c].nf + ws.cstate[c].nh <= args.hi_evals);
                 if (!solo) {
                     // publishing is the LAST thing a control task does: the candidate's next control task may start on another
                     // SM as soon as the evaluations have finished

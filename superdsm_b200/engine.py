@@ -159,7 +159,7 @@ class Engine(object):
         return int(self.lib.sdsm_launch_count(self.ctx))
 
     STAT_NAMES = ('q_head', 'q_tail', 'done', 'abort', 'cyc_eval', 'cyc_hrows', 'cyc_ctrl', 'cyc_idle', 'n_eval', 'n_hrows',
-                  'n_ctrl', 'cyc_total', 't0', 'cyc_widle', 'cyc_wtotal')
+                  'n_ctrl', 'cyc_total', 't0', 'cyc_widle', 'cyc_wtotal', 'cyc_wfin')
 
     def solver_stats(self, ws=None):
         """Counters of the persistent solver kernel of the last batch (synchronises): see ``sdsm_solver_stats``."""
