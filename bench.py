@@ -257,7 +257,7 @@ def run_gpu(args):
                        'l2': 'flushed between timed iterations (256 MiB write)', 'optimal': optimal,
                        'images_per_s': world * args.steps / (total_ms_max * 1e-3)},
             'e2e': {'value': cand_total * e2e_steps / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
-                    'd2h_bytes_per_step': int(d2h), 'includes': 'host EDT + descriptors, pinned H2D of y/atoms/descriptors, solve, D2H, Object materialisation'},
+                    'd2h_bytes_per_step': int(d2h), 'includes': 'pinned H2D of y, mask, atoms; device EDT + atom statistics; descriptors; solve; D2H of results; Object materialisation'},
             'gpu_launches': int(gpu_launches),
             'roofline': {'kernel': 'k_solve (persistent solver: control CTAs + evaluation warps fed by device-side priority queues)', 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak,
                          'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': traffic, 'traffic_source': traffic_src, 'peak_source': peak_src,

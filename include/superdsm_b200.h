@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define SDSM_ABI_VERSION 3
+#define SDSM_ABI_VERSION 4
 
 /* return codes */
 #define SDSM_OK              0
@@ -118,6 +118,16 @@ const char* sdsm_last_error(const sdsm_ctx* ctx);
  * y_mask AND (EDT(y <= 0) <= background_margin) set to 0 (objects.py:126-127, candidate-independent part). */
 int sdsm_set_image(sdsm_ctx* ctx, const double* d_y, const int32_t* d_atoms, int32_t H, int32_t W);
 int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* params);
+
+/* Per-image preparation on the device (the candidate-independent part of Object.get_cvxprog_region, objects.py:126-127):
+ * d_atoms_out[p] = d_atoms[p] if d_ymask[p] and distance_transform_edt(y <= 0)[p] <= background_margin, else 0 -- the map
+ * sdsm_set_image() expects -- computed with an exact windowed Euclidean distance transform (bit-equal to the scipy
+ * expression).  d_count[n_labels + 1] / d_box[4 (n_labels + 1)] receive, per atom label, the number of usable pixels and
+ * their bounding box (r0, r1, c0, c1; end-exclusive; r0 = H, r1 = 0 if none).  background_margin = +inf keeps every masked
+ * pixel.  d_scratch: H * W bytes.  d_ymask: one byte per pixel (numpy bool). */
+int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_t* d_ymask, const int32_t* d_atoms, int32_t H, int32_t W,
+                       double background_margin, int32_t n_labels, int32_t* d_atoms_out, uint64_t* d_count, int32_t* d_box,
+                       uint8_t* d_scratch, void* stream);
 
 /* fills the offset fields of h_cands[0..n_cand) and the plan; host-only, no CUDA call */
 int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* h_cands, int32_t n_cand, sdsm_plan* plan);

@@ -40,7 +40,7 @@ class Out(ctypes.Structure):
 
 EXPORTS = ('sdsm_abi_version', 'sdsm_create', 'sdsm_destroy', 'sdsm_last_error', 'sdsm_set_image', 'sdsm_set_params',
            'sdsm_plan_batch', 'sdsm_solve_batch', 'sdsm_eval_candidate', 'sdsm_export_smooth', 'sdsm_trace_solve',
-           'sdsm_dfma_peak', 'sdsm_launch_count', 'sdsm_solver_stats', 'sdsm_sweep_eval', 'sdsm_finish_times')
+           'sdsm_dfma_peak', 'sdsm_launch_count', 'sdsm_solver_stats', 'sdsm_sweep_eval', 'sdsm_finish_times', 'sdsm_prepare_image')
 
 _lib = None
 
@@ -62,6 +62,7 @@ def load():
     lib.sdsm_last_error.restype = ctypes.c_char_p
     lib.sdsm_set_image.argtypes = [vp, vp, vp, i32, i32]
     lib.sdsm_set_params.argtypes = [vp, ctypes.POINTER(Params)]
+    lib.sdsm_prepare_image.argtypes = [vp, vp, vp, vp, i32, i32, ctypes.c_double, i32, vp, vp, vp, vp, vp]
     lib.sdsm_plan_batch.argtypes = [vp, vp, i32, ctypes.POINTER(Plan)]
     lib.sdsm_solve_batch.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, ctypes.c_size_t, ctypes.POINTER(Out), vp]
     lib.sdsm_eval_candidate.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, vp, vp, vp]
@@ -73,7 +74,7 @@ def load():
     lib.sdsm_solver_stats.argtypes = [vp, vp, vp, vp]
     lib.sdsm_finish_times.argtypes = [vp, vp, vp, vp]
     lib.sdsm_sweep_eval.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, i32, i32, i32, vp, vp]
-    if lib.sdsm_abi_version() != 3:
+    if lib.sdsm_abi_version() != 4:
         raise ImportError('libsuperdsm_b200.so: ABI version mismatch')
     _lib = lib
     return lib

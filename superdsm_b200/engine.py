@@ -218,15 +218,47 @@ class Engine(object):
     # -- per image -----------------------------------------------------------------------------------------------
 
     def set_image(self, y_model, y_mask, atoms, background_margin):
-        """Uploads the offset image and the atoms map (see :func:`prepare_image`)."""
+        """Uploads the offset image, its mask and the atoms map; the usable pixels (``objects.py:126-127``: mask and
+        ``EDT(y <= 0) <= background_margin``), the masked atoms map and the per-atom pixel counts / bounding boxes are
+        computed on the device (``sdsm_prepare_image``; :func:`prepare_image` is the numpy statement of the same thing)."""
+        torch = self.torch
         y_model = np.ascontiguousarray(y_model, dtype=np.float64)
-        atoms_v, self.atom_count, self.atom_box = prepare_image(y_model, y_mask, atoms, background_margin)
+        atoms = np.ascontiguousarray(atoms, dtype=np.int32)
+        y_mask = np.ascontiguousarray(y_mask, dtype=np.bool_)
+        assert y_model.ndim == 2 and atoms.shape == y_model.shape and y_mask.shape == y_model.shape
         H, W = y_model.shape
         self.shape = (H, W)
+        n_labels = int(atoms.max()) if atoms.size else 0
         d_y = self._upload('y', y_model)
-        d_atoms = self._upload('atoms', atoms_v)
+        d_mask = self._upload('ymask', y_mask.view(np.uint8))
+        d_atoms_in = self._upload('atoms_in', atoms)
+        d_atoms = self._buf('d_atoms', 4 * H * W)
+        d_count = self._buf('d_atom_count', 8 * (n_labels + 1))
+        d_box = self._buf('d_atom_box', 16 * (n_labels + 1))
+        d_scratch = self._buf('d_edt', H * W)
+        margin = float(background_margin)
+        self._check(self.lib.sdsm_prepare_image(self.ctx, d_y.data_ptr(), d_mask.data_ptr(), d_atoms_in.data_ptr(), H, W,
+                                                margin if np.isfinite(margin) else 1e308 * 10, n_labels, d_atoms.data_ptr(),
+                                                d_count.data_ptr(), d_box.data_ptr(), d_scratch.data_ptr(), self.stream.cuda_stream))
+        nb_c, nb_b = 8 * (n_labels + 1), 16 * (n_labels + 1)
+        h_c, h_b = self._buf('h_atom_count', nb_c, pinned=True), self._buf('h_atom_box', nb_b, pinned=True)
+        with torch.cuda.stream(self.stream):
+            h_c[:nb_c].copy_(d_count[:nb_c], non_blocking=True)
+            h_b[:nb_b].copy_(d_box[:nb_b], non_blocking=True)
+        self.stream.synchronize()
+        self.d2h_bytes += nb_c + nb_b
+        self.atom_count = h_c[:nb_c].numpy().view(np.int64).copy()
+        box = h_b[:nb_b].numpy().view(np.int32).reshape(-1, 4).astype(np.int64)
+        box[self.atom_count == 0] = 0
+        self.atom_box = box
         self._check(self.lib.sdsm_set_image(self.ctx, d_y.data_ptr(), d_atoms.data_ptr(), H, W))
         self._last = None
+
+    def masked_atoms(self):
+        """The masked atoms map of the current image (device -> host; diagnostics and tests)."""
+        H, W = self.shape
+        self.stream.synchronize()
+        return self._bufs['d_atoms'][:4 * H * W].cpu().numpy().view(np.int32).reshape(H, W)
 
     def set_params(self, dsm_cfg):
         """``dsm_cfg`` is the dictionary of ``dsmcfg.py:82-89``."""

@@ -256,3 +256,16 @@ def test_other_baseline_configs(eng, name, kw):
         assert abs(res.energy[k] - ref['energy']) <= tol, (name, k, res.energy[k], ref['energy'])
         off, frag = res.foreground(int(k))
         assert np.array_equal(frag, ref['fg_fragment']) and np.array_equal(off, ref['fg_offset'])
+
+
+@pytest.mark.parametrize('name,margin', [('toy', 9), ('toy', 6.5), ('toy', np.inf), ('gowt1', 16), ('gowt1', 16.97), ('bbbc039', 20), ('bbbc039', 0)])
+def test_device_image_preparation_bit_exact(eng, name, margin):
+    """sdsm_prepare_image (windowed exact EDT on the device) against the numpy/scipy statement of objects.py:126-127:
+    masked atoms map, per-atom pixel counts and bounding boxes -- bit-exact."""
+    from superdsm_b200 import synth, engine
+    w = synth.make_workload(name, oversegment=2, max_set_size=1)
+    ref_atoms, ref_count, ref_box = engine.prepare_image(w['y'], w['y_mask'], w['atoms'], margin)
+    eng.set_image(w['y'], w['y_mask'], w['atoms'], margin)
+    assert np.array_equal(eng.masked_atoms(), ref_atoms)
+    assert np.array_equal(eng.atom_count, ref_count)
+    assert np.array_equal(eng.atom_box, ref_box)

@@ -18,7 +18,7 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(_lib.EXPORTS)
     lib = _lib.load()
     for name in declared: assert hasattr(lib, name), name
-    assert lib.sdsm_abi_version() == 3
+    assert lib.sdsm_abi_version() == 4
 
 
 def test_struct_layouts_match_the_header():
