@@ -20,8 +20,10 @@
  * (status word), never a C++ exception.  One context per device; a context is not thread-safe.
  *
  * Environment (read by sdsm_create), all optional tuning knobs of the persistent solver kernel:
- *   SDSM_CTRL_CTAS (48)   CTAs that run control tasks; the warps of all other CTAs run evaluation / Hessian-row items
- *   SDSM_SOLO_CELLS (32)  candidates with at most this many pixel cells run their whole chain inside one control CTA
+ *   SDSM_CTRL_CTAS (48 + a share of the grid that grows with the batch's share of small candidates)   CTAs that run control
+ *                         tasks; the warps of all other CTAs run evaluation / Hessian-row items
+ *   SDSM_SOLO_CELLS (512 / smooth_subsample)  candidates with at most this many pixel cells run their whole chain inside
+ *                         one control CTA
  *   SDSM_TASK_SMALL_CELLS (512)  candidates with at most this many cells get evaluation items of one cell (else 4)
  *   SDSM_HI_FRAC (0.02)   share of the batch (most expensive candidates first) whose tasks are urgent from the start
  *   SDSM_HI_EVALS (200)   a candidate that has needed more evaluations than this becomes urgent

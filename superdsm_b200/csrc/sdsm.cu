@@ -29,14 +29,24 @@ struct sdsm_ctx {
     int64_t P = 0, C = 0, T = 0, V = 0, M = 0, K = 0;
     int32_t n_cand = 0;
     int solve_ctas_per_sm = 1;               // resident CTAs of k_solve per SM (occupancy query)
-    int solo_cells = 32;                     // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
+    int solo_cells = 0;                      // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
     int task_small_cells = 512;              // SDSM_TASK_SMALL_CELLS: candidates up to this many cells get one cell per warp
     double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
     double hi_frac = 0.02;                   // SDSM_HI_FRAC: this share of the batch (the most expensive candidates) is urgent from the start
+    bool ctrl_ctas_fixed = false;            // SDSM_CTRL_CTAS given: no adaptation to the batch
+    double solo_share = 0.0;                 // share of the last planned batch's pixels in candidates whose chains stay in one CTA
     int ctrl_ctas = 48;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
     int hi_evals = 200;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     std::string err;
 };
+
+// candidates with at most this many pixel cells run their chain inside one control CTA: about 5000 pixels' worth of cells
+static int solo_cells_of(const sdsm_ctx* ctx)
+{
+    if (ctx->solo_cells != 0) return ctx->solo_cells < 0 ? 0 : ctx->solo_cells;
+    const int v = 512 / (ctx->par.sub > 0 ? ctx->par.sub : 16);
+    return v < 8 ? 8 : (v > 128 ? 128 : v);
+}
 
 #define CUDA_TRY(ctx, expr)                                                                      \
     do {                                                                                         \
@@ -69,12 +79,12 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     CUDA_TRY(ctx, cudaFuncSetAttribute(k_diag_eval_end, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctx->solve_ctas_per_sm, k_solve, SOLVE_BLOCK, (size_t)smem_max));
     if (ctx->solve_ctas_per_sm < 1) { ctx->err = "k_solve does not fit on an SM"; return SDSM_E_UNSUPPORTED; }
-    if (const char* e = getenv("SDSM_SOLO_CELLS")) ctx->solo_cells = atoi(e);
+    if (const char* e = getenv("SDSM_SOLO_CELLS")) ctx->solo_cells = atoi(e) > 0 ? atoi(e) : -1;     // 0 (default): 512 / smooth_subsample
     if (const char* e = getenv("SDSM_TASK_SMALL_CELLS")) ctx->task_small_cells = atoi(e);
     if (const char* e = getenv("SDSM_TIMEOUT_S")) ctx->timeout_s = atof(e);
     if (const char* e = getenv("SDSM_HI_FRAC")) ctx->hi_frac = atof(e);
     if (const char* e = getenv("SDSM_HI_EVALS")) ctx->hi_evals = atoi(e);
-    if (const char* e = getenv("SDSM_CTRL_CTAS")) ctx->ctrl_ctas = atoi(e);
+    if (const char* e = getenv("SDSM_CTRL_CTAS")) { ctx->ctrl_ctas = atoi(e); ctx->ctrl_ctas_fixed = true; }
     return SDSM_OK;
 }
 
@@ -168,6 +178,7 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
     const int sub = ctx->par.sub;
     int64_t P = 0, C = 0, T = 0, V = 0, M = 0, PAR = 0, FG = 0, K = 0;
     int32_t n_max = 6, cells_max = 1;
+    double work_all = 0, work_solo = 0;
     for (int32_t i = 0; i < n_cand; ++i) {
         sdsm_cand& c = cands[i];
         if (c.h < 1 || c.w < 1 || c.n < 1 || c.r0 < 0 || c.c0 < 0 || c.r0 + c.h > ctx->img.H || c.c0 + c.w > ctx->img.W || c.fp_len < 1) {
@@ -184,6 +195,9 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
         c.fg_off = FG;  FG += (int64_t)c.h * c.w;
         c.vec_off = V;  V += (int64_t)NVEC * ld;
         c.mat_off = M;  M += 3 * ld * ld;
+        work_all += c.n;
+        // its chain will (most likely) stay in one control CTA: non-empty cells ~ 1.6 n / sub^2 (the cells of the rim are partly filled)
+        if (1.6 * c.n <= (double)solo_cells_of(ctx) * sub * sub) work_solo += c.n;
         K += 1 + cap;                                     // items of the candidate that can be queued at the same time
         if (ld > n_max) n_max = (int32_t)ld;
         if (cap > cells_max) cells_max = cap;
@@ -196,6 +210,7 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
     plan->cells_max = cells_max;
     plan->reserved0 = 0;
     plan->reserved1 = 0;
+    ctx->solo_share = work_all > 0 ? work_solo / work_all : 0.0;
     ctx->P = P; ctx->C = C; ctx->T = T; ctx->V = V; ctx->M = M; ctx->K = K; ctx->n_cand = n_cand;
     return SDSM_OK;
 }
@@ -220,13 +235,15 @@ static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_can
     SolveArgs args{};
     args.n_target = n_first;
     args.lcap = lcap;
-    args.solo_cells = ctx->solo_cells;
+    args.solo_cells = solo_cells_of(ctx);
     args.task_small_cells = ctx->task_small_cells;
     args.hi_evals = ctx->hi_evals;
     args.n_ctrl_ctas = ctx->ctrl_ctas;
     args.timeout_ns = (unsigned long long)(ctx->timeout_s * 1e9);
     args.trace = trace;
     const int grid = ctx->sm_count * ctx->solve_ctas_per_sm;
+    // batches of small candidates keep their chains inside control CTAs: give those the share of the grid their work has
+    if (!ctx->ctrl_ctas_fixed && d_order) args.n_ctrl_ctas += (int)(0.65 * (grid - 8 - args.n_ctrl_ctas) * ctx->solo_share);
     if (args.n_ctrl_ctas < 1) args.n_ctrl_ctas = 1;
     if (args.n_ctrl_ctas > grid - 1) args.n_ctrl_ctas = grid - 1;
     k_solve<<<grid, SOLVE_BLOCK, solve_smem_bytes(lcap), stream>>>(ctx->img, ctx->par, d_cands, ws, out, args);
