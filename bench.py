@@ -24,10 +24,23 @@ if ROOT not in sys.path: sys.path.insert(0, ROOT)
 
 WORKLOAD = 'gowt1'
 WORKLOAD_DESC = 'GOWT1-shaped 1024x1024 synthetic nuclei image (BASELINE config 1): atoms + universes + adjacent-atom sets, AF_scale 42.43'
+# the other BASELINE configurations (parity-test cases; `--workload` times them, the default stays the config the metric is quoted on)
+OTHER_WORKLOADS = {
+    'bbbc039': ('BBBC039-shaped 520x696 image, default configuration (BASELINE config 0)', dict()),
+    'nih3t3': ('NIH3T3-shaped 1344x1024 image, clustered nuclei, strong inhomogeneity (BASELINE config 2)', dict()),
+    'tiled': ('1024x1024 crop of the 4096x4096 tiled field, 1250 nuclei, AF_scale 10 (BASELINE config 4)', dict(shape=(1024, 1024), n=1250)),
+}
 
 
 def make_workload(rank, args):
     from superdsm_b200 import synth
+    global WORKLOAD_DESC
+    if args.workload != WORKLOAD:
+        WORKLOAD_DESC, kw = OTHER_WORKLOADS[args.workload]
+        name = 'tiled4k' if args.workload == 'tiled' else args.workload
+        base = synth.WORKLOADS[name]['seed']
+        return synth.make_workload(name, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=base + rank,
+                                   max_candidates=args.max_candidates, **kw)
     return synth.make_workload(WORKLOAD, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=1 + rank,
                                max_candidates=args.max_candidates)
 
@@ -197,8 +210,12 @@ def run_gpu(args):
     r = _R(); r.cands = handle['cands']; r.info = info
     alg_bytes, alg_flops = algorithmic_work(r)
     optimal = int((status == _lib.ST_OPTIMAL).sum())
-    if (status >= _lib.ST_ERROR).any():
-        raise SystemExit(f'solver reported errors: {np.bincount(status)}')
+    n_errors = int((status >= _lib.ST_ERROR).sum())
+    if n_errors:
+        # CvxprogError candidates (both elliptical passes failed, objects.py:351-353) are legitimate results of the reference
+        # too, but its compute_objects raises on them: the headline workload has none, the others drop them from the e2e leg
+        if args.workload == WORKLOAD: raise SystemExit(f'solver reported errors: {np.bincount(status)}')
+        fps = [fp for fp, st in zip(fps, status) if st < _lib.ST_ERROR]
 
     # ---- end to end through the public API (`e2e`): host arrays in, Objects out ----
     y_img = Image.create_from_array(w['y'], normalize=False, mask=w['y_mask'])
@@ -254,7 +271,7 @@ def run_gpu(args):
             'dtype': 'f64', 'data': 'synthetic',
             'config': {'workload': WORKLOAD_DESC, 'candidates_per_image': len(fps), 'images_per_step': world,
                        'pixels_per_step_per_gpu': int(handle['cands']['n'].sum()), 'parallelism': f'image-sharded x{world}, no collective',
-                       'l2': 'flushed between timed iterations (256 MiB write)', 'optimal': optimal,
+                       'l2': 'flushed between timed iterations (256 MiB write)', 'optimal': optimal, 'errors': n_errors,
                        'images_per_s': world * args.steps / (total_ms_max * 1e-3)},
             'e2e': {'value': cand_total * e2e_steps / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
                     'd2h_bytes_per_step': int(d2h), 'includes': 'pinned H2D of y, mask, atoms; device EDT + atom statistics; descriptors; solve; D2H of results; Object materialisation'},
@@ -293,6 +310,7 @@ def main():
     ap.add_argument('--max-set-size', type=int, default=4)
     ap.add_argument('--max-candidates', type=int, default=None)
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--workload', default=WORKLOAD, choices=[WORKLOAD] + sorted(OTHER_WORKLOADS))
     args = ap.parse_args()
     if args.impl == 'reference': run_reference(args)
     else: run_gpu(args)
