@@ -269,3 +269,27 @@ def test_device_image_preparation_bit_exact(eng, name, margin):
     assert np.array_equal(eng.masked_atoms(), ref_atoms)
     assert np.array_equal(eng.atom_count, ref_count)
     assert np.array_equal(eng.atom_box, ref_box)
+
+
+def test_large_system_against_oracle(eng):
+    """A candidate whose KKT system is larger than the shared-memory factor (6 + m > 104: blocked DMMA Cholesky in L2,
+    blocked substitutions) against the oracle's fit of the same region."""
+    from oracle import dsm_oracle as orc
+    from superdsm_b200 import synth, _lib
+    w = synth.make_workload('gowt1', oversegment=3, max_set_size=4, seed=1)
+    eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
+    eng.set_params(w['dsm_cfg'])
+    fps = w['footprints']
+    cands, _ = eng.describe(fps)
+    order = np.argsort(cands['n'])
+    pick = [int(k) for k in order if 30000 <= cands['n'][k] <= 40000][:4]      # m is about n / 256
+    res = eng.solve([fps[k] for k in pick])
+    big = [i for i in range(len(pick)) if 6 + res.m(i) > 104]
+    assert big, 'no large system among the picked candidates'
+    i = big[0]
+    ref = orc.compute_object(w['y'], w['y_mask'], w['atoms'], fps[pick[i]], w['dsm_cfg'])
+    assert (res.status[i] == _lib.ST_OPTIMAL) == bool(ref['is_optimal'])
+    tol = 1e-6 * abs(ref['energy']) + 2e-7 * ref['n'] / w['dsm_cfg']['scale']
+    assert abs(res.energy[i] - ref['energy']) <= tol, (res.energy[i], ref['energy'], res.m(i))
+    off, frag = res.foreground(i)
+    assert np.array_equal(frag, ref['fg_fragment']) and np.array_equal(off, ref['fg_offset'])
