@@ -100,10 +100,22 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
         int m = s_cnt;
 
         // (b) chessboard distance of every pixel to the lattice points (distance_transform_bf, dsm.py:169)
+        //     Only the four lattice corners around a pixel can be closer than `sub` (every other lattice point is at least
+        //     `sub` rows or columns away), and the completion below only orders the pixels whose distance is >= sub: the
+        //     scan over all m lattice points is needed for the few pixels without a lattice corner inside omega.
         for (int i = tid; i < n; i += BLOCK) {
             const uint32_t p = prc[i];
+            const int pr = (int)(p & 0xffffu), pc = (int)(p >> 16);
+            const int a = pr / sub, b = pc / sub;
             int d = 0x7fffffff;
-            for (int k = 0; k < m; ++k) d = min(d, cheb(p, gl[k]));
+#pragma unroll
+            for (int da = 0; da < 2; ++da)
+#pragma unroll
+                for (int db = 0; db < 2; ++db) {
+                    const int ca = a + da, cb = b + db;
+                    if (ca < ch && cb < cw && cellmap[ca * cw + cb] >= 0) d = min(d, max(abs(ca * sub - pr), abs(cb * sub - pc)));
+                }
+            if (d >= sub) { d = 0x7fffffff; for (int k = 0; k < m; ++k) d = min(d, cheb(p, gl[k])); }
             dist[i] = d;
         }
         __syncthreads();
