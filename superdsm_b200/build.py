@@ -23,6 +23,7 @@ def build(force=False, verbose=False):
     nvcc = os.environ.get('NVCC', 'nvcc')
     cmd = [nvcc, '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-fmad=false',
            '-Xcompiler', '-fPIC', '-shared', '-o', LIB_PATH, SOURCES[0]]
+    cmd[1:1] = os.environ.get('SDSM_NVCC_FLAGS', '').split()      # e.g. -DSDSM_GRID_TRACE (phase timing of k_grid)
     if verbose: cmd[1:1] = ['-Xptxas', '-v']
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:

@@ -54,18 +54,25 @@ __device__ __forceinline__ int cheb(uint32_t a, uint32_t b)
     return max(abs(dr), abs(dc));
 }
 
+#ifdef SDSM_GRID_TRACE
+#define GRID_T0 long long gt_[5]; gt_[4] = clock64()
+#define GRID_T(k) gt_[k] = clock64()
+#define GRID_TPRINT if (tid == 0 && it < 3) printf("k_grid it %d n %d m %d far %d: a %lld b %lld c %lld d %lld cycles\n", it, n, m, nfar, gt_[0] - gt_[4], gt_[1] - gt_[0], gt_[2] - gt_[1], gt_[3] - gt_[2])
+#else
+#define GRID_T0
+#define GRID_T(k)
+#define GRID_TPRINT
+#endif
+
 __global__ void __launch_bounds__(GRID_BLOCK)
 k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* __restrict__ order, WS ws)
 {
     constexpr int BLOCK = GRID_BLOCK;
-    extern __shared__ float s_psf[];                    // (R+1)^2
     __shared__ unsigned long long s_min[BLOCK / 32 + 1];
     __shared__ int s_cnt;
-    __shared__ int s_bad;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int sub = par.sub, R = par.R, R1 = par.R + 1;
-    for (int i = tid; i < R1 * R1; i += BLOCK) s_psf[i] = par.psf[i];
-    __syncthreads();
+    __shared__ int s_far;
+    const int tid = threadIdx.x;
+    const int sub = par.sub, R = par.R;
 
     for (int it = blockIdx.x; it < n_cand; it += gridDim.x) {
         const int c = order[it];
@@ -81,8 +88,10 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
         int32_t* cellmap = ws.cellmap + cd.cell_off;
         uint32_t* gl = ws.grid_tmp + cd.cell_off;        // unordered grid points
         uint32_t* gs = ws.grid_rc + cd.cell_off;         // sorted grid points
-        int32_t* dist = ws.pix_dist + cd.pix_off;
-        if (tid == 0) { s_cnt = 0; s_bad = 0; }
+        int32_t* far_d = ws.pix_dist + cd.pix_off;       // pixels farther than sub from every lattice point: distance,
+        uint32_t* far_p = reinterpret_cast<uint32_t*>(ws.pix_s + cd.pix_off);   // and point (pix_s is written by k_grid_rows)
+        if (tid == 0) { s_cnt = 0; s_far = 0; }
+        GRID_T0;
         __syncthreads();
 
         // (a) lattice points inside omega: the cell's first pixel sits on the cell origin
@@ -98,11 +107,13 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
         }
         __syncthreads();
         int m = s_cnt;
+        GRID_T(0);
 
         // (b) chessboard distance of every pixel to the lattice points (distance_transform_bf, dsm.py:169)
         //     Only the four lattice corners around a pixel can be closer than `sub` (every other lattice point is at least
         //     `sub` rows or columns away), and the completion below only orders the pixels whose distance is >= sub: the
         //     scan over all m lattice points is needed for the few pixels without a lattice corner inside omega.
+        //     Pixels at distance >= sub are the only ones the completion looks at: they go to a compact list (point, distance).
         for (int i = tid; i < n; i += BLOCK) {
             const uint32_t p = prc[i];
             const int pr = (int)(p & 0xffffu), pc = (int)(p >> 16);
@@ -115,20 +126,25 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
                     const int ca = a + da, cb = b + db;
                     if (ca < ch && cb < cw && cellmap[ca * cw + cb] >= 0) d = min(d, max(abs(ca * sub - pr), abs(cb * sub - pc)));
                 }
-            if (d >= sub) { d = 0x7fffffff; for (int k = 0; k < m; ++k) d = min(d, cheb(p, gl[k])); }
-            dist[i] = d;
+            if (d >= sub) {
+                d = 0x7fffffff;
+                for (int k = 0; k < m; ++k) d = min(d, cheb(p, gl[k]));
+                if (d >= sub) { const int pos = atomicAdd(&s_far, 1); far_p[pos] = p; far_d[pos] = d; }
+            }
         }
         __syncthreads();
+        GRID_T(1);
 
         // (c) greedy completion: first (row-major) pixel of minimal distance among those >= subsample
+        const int nfar = s_far;
         uint32_t newp = 0;
         bool have_new = false;
-        while (true) {
+        while (nfar > 0) {
             unsigned long long best = ~0ull;
-            for (int i = tid; i < n; i += BLOCK) {
-                const uint32_t p = prc[i];
-                int d = dist[i];
-                if (have_new) { d = min(d, cheb(p, newp)); dist[i] = d; }
+            for (int i = tid; i < nfar; i += BLOCK) {
+                const uint32_t p = far_p[i];
+                int d = far_d[i];
+                if (have_new) { d = min(d, cheb(p, newp)); far_d[i] = d; }
                 if (d >= sub) {
                     const unsigned long long key = ((unsigned long long)(uint32_t)d << 32) | (uint32_t)((p & 0xffffu) * (uint32_t)wp + (p >> 16));
                     best = key < best ? key : best;
@@ -147,6 +163,7 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
             ++m;
             __syncthreads();
         }
+        GRID_T(2);
 
         // (d) row-major order of the grid points = column order of G~
         for (int k = tid; k < m; k += BLOCK) {
@@ -159,9 +176,53 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
         }
         __syncthreads();
 
+        GRID_T(3);
+        if (tid == 0) {
+            ci.m = m;
+            ws.cinfo[c] = ci;
+        }
+        GRID_TPRINT;
+    }
+}
+
+// K2b: the per-pixel part of the smooth matrix, split over ROWS_SPLIT CTAs per candidate (the largest region of a batch
+// would otherwise keep one CTA busy for ~12 ms): CTA (it, part) takes a contiguous range of cells of candidate order[it]
+// -- and with it a contiguous range of the cell-major pixel arrays.
+constexpr int ROWS_SPLIT = 16;
+
+__global__ void __launch_bounds__(GRID_BLOCK)
+k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* __restrict__ order, WS ws)
+{
+    constexpr int BLOCK = GRID_BLOCK;
+    extern __shared__ float s_psf[];                    // (R+1)^2
+    __shared__ int s_bad;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int sub = par.sub, R = par.R, R1 = par.R + 1;
+    for (int i = tid; i < R1 * R1; i += BLOCK) s_psf[i] = par.psf[i];
+    __syncthreads();
+
+    for (int it = blockIdx.x; it < n_cand; it += gridDim.x) {
+        const int c = order[it];
+        const sdsm_cand cd = cands[c];
+        const CInfo ci = ws.cinfo[c];
+        __syncthreads();
+        if (ci.flags & 1) continue;
+        if (ci.hp <= R || ci.wp <= R) continue;          // null matrix
+        const int ncells = ci.ncells, cw = ci.cw, ch = ci.ch, m = ci.m;
+        const int per = (ncells + ROWS_SPLIT - 1) / ROWS_SPLIT;
+        const int cell0 = min(ncells, (int)blockIdx.y * per), cell1 = min(ncells, cell0 + per);
+        if (cell0 >= cell1) continue;
+        const int32_t* cstart = ws.cell_start + cd.cell_off;
+        const uint32_t* prc = ws.pix_rc + cd.pix_off;
+        const int32_t* cellmap = ws.cellmap + cd.cell_off;
+        const uint32_t* gs = ws.grid_rc + cd.cell_off;
+        const int i0 = cstart[cell0], i1 = cstart[cell1];
+        if (tid == 0) s_bad = 0;
+        __syncthreads();
+
         // (e) float32 row sums in numpy's pairwise order
         float* ps = ws.pix_s + cd.pix_off;
-        for (int i = tid; i < n; i += BLOCK) {
+        for (int i = i0 + tid; i < i1; i += BLOCK) {
             const uint32_t p = prc[i];
             const int pr = p & 0xffffu, pc = p >> 16;
             const int ca = pr / sub, cb = pc / sub;
@@ -196,7 +257,7 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
         // (f) G~ values per (cell, active slot, pixel) and the active-slot mask of every cell
         float* gv = ws.gval + (size_t)NSLOT * cd.pix_off;
         uint32_t* amask = ws.cell_amask + cd.cell_off;
-        for (int cell = warp; cell < ncells; cell += BLOCK / 32) {
+        for (int cell = cell0 + warp; cell < cell1; cell += BLOCK / 32) {
             const int st = cstart[cell], npix = cstart[cell + 1] - st;
             uint32_t am = 0;
             if (npix > 0) {
@@ -224,11 +285,7 @@ k_grid(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* 
             if (lane == 0) amask[cell] = am;
         }
         __syncthreads();
-        if (tid == 0) {
-            ci.m = m;
-            if (s_bad) ci.flags |= 2;
-            ws.cinfo[c] = ci;
-        }
+        if (tid == 0 && s_bad) atomicOr(&ws.cinfo[c].flags, 2);
     }
 }
 

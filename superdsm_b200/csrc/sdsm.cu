@@ -273,10 +273,11 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     ctx->launches++;
     if (ctx->par.has_smooth) {
         const size_t psf_bytes = sizeof(float) * (size_t)(ctx->par.R + 1) * (ctx->par.R + 1);
+        k_grid<<<pack_grid, GRID_BLOCK, 0, stream>>>(ctx->par, d_cands, n_cand, d_order, ws);
         if (psf_bytes > 48 * 1024)
-            CUDA_TRY(ctx, cudaFuncSetAttribute(k_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psf_bytes));
-        k_grid<<<pack_grid, GRID_BLOCK, psf_bytes, stream>>>(ctx->par, d_cands, n_cand, d_order, ws);
-        ctx->launches++;
+            CUDA_TRY(ctx, cudaFuncSetAttribute(k_grid_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psf_bytes));
+        k_grid_rows<<<dim3(pack_grid, ROWS_SPLIT), GRID_BLOCK, psf_bytes, stream>>>(ctx->par, d_cands, n_cand, d_order, ws);
+        ctx->launches += 2;
     }
     const int lcap = ctrl_lcap(plan->n_max);
     rc = run_solver(ctx, stream, d_cands, ws, *out, lcap, d_order, n_cand, 0, nullptr);

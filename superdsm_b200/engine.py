@@ -293,8 +293,9 @@ class Engine(object):
     def describe(self, footprints):
         return describe_candidates(self.atom_count, self.atom_box, footprints)
 
-    def solve(self, footprints, keep_device_state=False):
-        """Fits every candidate of the batch; returns a :class:`BatchResult`."""
+    def solve(self, footprints, keep_device_state=False, borrow=False):
+        """Fits every candidate of the batch; returns a :class:`BatchResult`.  ``borrow=True``: the foreground masks of the
+        result are a view of the engine's pinned staging buffer (valid until the next ``solve``) instead of a copy."""
         torch, lib = self.torch, self.lib
         t0 = time.perf_counter()
         cands, flat = self.describe(footprints)
@@ -329,7 +330,7 @@ class Engine(object):
                           host['params'][:sizes['params']].numpy().view(np.float64).copy(),
                           host['fgbox'][:sizes['fgbox']].numpy().view(np.int32).reshape(n, 4).copy(),
                           host['onb'][:n].numpy().copy(),
-                          host['fgmask'][:sizes['fgmask']].numpy().copy(),
+                          host['fgmask'][:sizes['fgmask']].numpy() if borrow else host['fgmask'][:sizes['fgmask']].numpy().copy(),
                           time.perf_counter() - t0)
         self._last = (plan, d_cands, ws, cands)
         return res

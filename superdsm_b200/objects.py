@@ -145,10 +145,11 @@ def _compute_objects(objects, y, atoms, x_map, lock, dsm_cfg, log_root_dir):
     _bind_image(engine, y, atoms, cfg['background_margin'])
     engine.set_params(cfg)
     t0 = time.time()
-    res = engine.solve([obj.footprint for obj in objects])
+    res = engine.solve([obj.footprint for obj in objects], borrow=True)
     dt = (time.time() - t0) / len(objects)
-    for cidx, obj in enumerate(objects):
-        state, fallback = _result_to_object(res, cidx, obj, dt)
+    # all states are built before the first one is handed out: the masks are views of the engine's staging buffer
+    states = [_result_to_object(res, cidx, obj, dt) for cidx, obj in enumerate(objects)]
+    for cidx, (state, fallback) in enumerate(states):
         yield cidx, state, fallback
 
 
