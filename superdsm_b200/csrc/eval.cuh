@@ -8,6 +8,7 @@
 // candidate's value / gradient / Hessian in a fixed order -- no floating-point atomics, bit-reproducible whatever the schedule.
 #pragma once
 #include "common.cuh"
+#include "logistic.cuh"
 
 namespace sdsm {
 
@@ -15,17 +16,20 @@ constexpr double NEG_LOG_DBL_MAX = -709.782712893384;   // -log(finfo(float64).m
 
 __device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }   // i >= j
 
-__device__ __noinline__ void logistic(double y, double S, double& phi, double& theta)
+// One out-of-line copy for all evaluation paths (instruction cache, and bit-identical values whoever calls): logistic.cuh.
+// The pair comes back in registers (reference parameters of an out-of-line function go through the stack).
+__device__ __noinline__ double2 logistic_pair(double y, double S)
 {
-    const double t = y * S;
-    if (t >= NEG_LOG_DBL_MAX) {
-        const double h = exp(-t);
-        phi = log(1.0 + h);          // dsm.py:321 (log, not log1p)
-        theta = h / (1.0 + h);       // dsm.py:310
-    } else {                          // exp would overflow: dsm.py:299,309,322
-        phi = -t;
-        theta = 1.0;
-    }
+    double2 r;
+    logistic_eval(y * S, r.x, r.y);
+    return r;
+}
+
+__device__ __forceinline__ void logistic(double y, double S, double& phi, double& theta)
+{
+    const double2 r = logistic_pair(y, S);
+    phi = r.x;
+    theta = r.y;
 }
 
 __device__ __forceinline__ int nth_set_bit(uint32_t mask, int n)

@@ -140,3 +140,16 @@ def test_two_rank_gloo_sharding(tmp_path):
     assert r0[0] == 1 and r1[0] == 1                     # all objects computed on both ranks
     assert r0[1] == r1[1] and r0[1] > 0                   # same fallback count everywhere
     assert r0[2] + r1[2] == r0[3] and min(r0[2], r1[2]) > 0    # disjoint shards covering the batch
+
+
+def test_logistic_restatement_accuracy(tmp_path):
+    """csrc/logistic.cuh (the device's exp / log(1 + h) / h / (1 + h), written for this path instead of the CUDA math
+    library) compiled for the host and compared with glibc in extended precision: exp <= 1.05 ulp, log <= 1 ulp, the
+    division correctly rounded; overflow branch and special values of dsm.py:298-322."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / 'logistic_check')
+    subprocess.run(['g++', '-O2', '-ffp-contract=off', '-o', exe, os.path.join(root, 'tests', 'native', 'logistic_check.cpp')], check=True)
+    res = subprocess.run([exe], capture_output=True, text=True)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert 'max ulps' in res.stdout
