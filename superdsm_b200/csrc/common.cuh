@@ -9,6 +9,7 @@ namespace sdsm {
 
 constexpr int NSLOT      = 25;    // (2*NC+1)^2 neighbour cells with NC = 2 >= ceil(R / subsample)
 constexpr int NC         = 2;
+constexpr int GROW       = 28;    // floats per pixel row of the G~ table: NSLOT rounded up to whole 16-byte groups
 constexpr int LOCAL_MAX  = 32;    // 6 polynomial + 25 slots, padded
 constexpr int SCRH       = 496;   // packed lower triangle of a 31 x 31 local Hessian
 constexpr int SCRG       = 32;    // local gradient (31) + value
@@ -19,11 +20,11 @@ constexpr int EVAL_BLOCK = SOLVE_BLOCK;   // evaluation task: one warp per pixel
 constexpr int EVAL_WARPS = EVAL_BLOCK / 32;
 constexpr int EVAL_CELLS = 32;    // most non-empty pixel cells per evaluation task: the CTA's warps take them one by one
 // per-warp shared memory of the evaluation tasks (doubles): the value + gradient pass stages the pixel data of STAGES
-// chunks of 32 pixels there with cp.async (STAGE_BYTES each: G~ rows [25][32] f32, y [32] f64, rc [32] u32); the Hessian pass
+// chunks of 32 pixels there with cp.async (STAGE_BYTES each: G~ rows [32][28] f32, y [32] f64, rc [32] u32); the Hessian pass
 // reuses the space for its tile T[32][TILE_LD] + dd[32]; then xi[32].
 constexpr int SLOTJ_INTS = 64;    // per-warp shared memory of the evaluation items (ints): grid index of the cell's active slots [32], slot of each active entry [32]
 constexpr int STAGES = 3;
-constexpr int STAGE_BYTES = NSLOT * 32 * 4 + 32 * 8 + 32 * 4;   // 3584
+constexpr int STAGE_BYTES = GROW * 32 * 4 + 32 * 8 + 32 * 4;    // 3968: G~ rows [lane][28], y [lane], rc [lane]
 constexpr int WARP_AREA_DOUBLES = STAGES * STAGE_BYTES / 8;      // 1344 >= 32 * TILE_LD + 32
 static_assert(WARP_AREA_DOUBLES >= 32 * TILE_LD + 32, "the Hessian tile must fit the staging area");
 constexpr int XI_OFF = WARP_AREA_DOUBLES;
@@ -93,7 +94,7 @@ struct WS {
     uint32_t* pix_rc;      // [P]      compacted (row | col << 16) inside the bounding box
     float*    pix_s;       // [P]      float32 row sum of the un-normalised G~ row (dsm.py:192)
     int32_t*  pix_dist;    // [P]      chessboard distance to the sub-sample grid (dsm.py:169-179)
-    float*    gval;        // [25 P]   G~ values: cell -> active slot -> pixel
+    float*    gval;        // [28 P]   G~ values: cell -> pixel -> active slot (rows of GROW floats, zero beyond the cell's last active slot)
     int32_t*  cell_start;  // [C]      first pixel of each cell (cell_cap + 1 entries per candidate)
     uint32_t* cell_amask;  // [C]      bit s: neighbour cell s holds a grid point with a non-zero weight in this cell
     int32_t*  cellmap;     // [C]      grid index of the cell's grid point or -1
@@ -143,7 +144,7 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_pix_rc = take(sizeof(uint32_t) * P);
     L.o_pix_s = take(sizeof(float) * P);
     L.o_pix_dist = take(sizeof(int32_t) * P);
-    L.o_gval = take(sizeof(float) * NSLOT * P);
+    L.o_gval = take(sizeof(float) * GROW * P);
     L.o_cell_start = take(sizeof(int32_t) * C);
     L.o_cell_amask = take(sizeof(uint32_t) * C);
     L.o_cellmap = take(sizeof(int32_t) * C);

@@ -1091,7 +1091,7 @@ k_finish(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS w
         const uint32_t* amask = ws.cell_amask + cd.cell_off;
         const int32_t* cellmap = ws.cellmap + cd.cell_off;
         const uint32_t* prc_c = ws.pix_rc + cd.pix_off;
-        const float* gv = ws.gval + (size_t)NSLOT * cd.pix_off;
+        const float* gv = ws.gval + (size_t)GROW * cd.pix_off;
         const uint16_t* inv_r = ws.inv + cd.tab_off; const uint16_t* inv_c = inv_r + cd.h;
         // model in the pixel coordinates of the image padded by 1 (dsm.py:113-128 with roi = whole image, pad = 1)
         const double gr = 1.0 / ((double)img.H - 1.0), gc = 1.0 / ((double)img.W - 1.0);
@@ -1121,14 +1121,14 @@ k_finish(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS w
                     if (lane < na) { const int sl = nth_set_bit(am, lane); slotj[lane] = cellmap[(ca + sl / 5 - NC) * ci.cw + (cb + sl % 5 - NC)]; }
                     __syncwarp();
                 }
-                const float* gcell = gv + (size_t)NSLOT * st;
+                const float* gcell = gv + (size_t)GROW * st;
                 for (int p = lane; p < npix; p += 32) {
                     const uint32_t rc = prc_c[st + p];
                     const int br = inv_r[rc & 0xffffu], bc = inv_c[rc >> 16];
                     const double X1 = (double)(cd.r0 + br + 1), X2 = (double)(cd.c0 + bc + 1);
                     double S = (X1 * M11 + X2 * M12) * X1 + (X1 * M12 + X2 * M22) * X2 + 2 * (X1 * mb1 + X2 * mb2) + mc;
                     double sxi = 0;
-                    for (int a = 0; a < na; ++a) sxi += (double)gcell[(size_t)a * npix + p] * x[6 + slotj[a]];
+                    for (int a = 0; a < na; ++a) sxi += (double)gcell[(size_t)p * GROW + a] * x[6 + slotj[a]];
                     S += sxi;
                     if (S > 0) {
                         fg[(size_t)br * cd.w + bc] = 1;
@@ -1181,7 +1181,7 @@ __global__ void k_export(Par par, const sdsm_cand* __restrict__ cands, int c, WS
     const CInfo ci = ws.cinfo[c];
     const int32_t* cstart = ws.cell_start + cd.cell_off;
     const uint32_t* prc = ws.pix_rc + cd.pix_off;
-    const float* gv = ws.gval + (size_t)NSLOT * cd.pix_off;
+    const float* gv = ws.gval + (size_t)GROW * cd.pix_off;
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < ci.m; j += gridDim.x * blockDim.x) grid[j] = ws.grid_rc[cd.cell_off + j];
     for (int cell = blockIdx.x; cell < ci.ncells; cell += gridDim.x) {
         const int st = cstart[cell], npix = cstart[cell + 1] - st;
@@ -1195,7 +1195,7 @@ __global__ void k_export(Par par, const sdsm_cand* __restrict__ cands, int c, WS
                 if (a < na) {
                     const int s = nth_set_bit(am, a);
                     col = ws.cellmap[cd.cell_off + (ca + s / 5 - NC) * ci.cw + (cb + s % 5 - NC)];
-                    v = gv[(size_t)NSLOT * st + (size_t)a * npix + p];
+                    v = gv[(size_t)GROW * (st + p) + a];
                 }
                 cols[(size_t)(st + p) * NSLOT + a] = col;
                 vals[(size_t)(st + p) * NSLOT + a] = v;

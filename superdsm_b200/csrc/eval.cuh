@@ -148,29 +148,38 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+
+// a shared-memory load the compiler may not merge with an earlier load of the same address
+__device__ __forceinline__ float4 lds128_again(const float4* p)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+    return v;
+}
+
 // Stages chunk k (32 pixels from p0 = 32 k) of the cell into shared memory: every lane copies its own pixel's y, rc and the
-// na entries of its row of G~ (a lane only ever reads back what it copied itself, so no warp synchronisation is needed).
-// Lanes beyond the cell's last pixel copy the chunk's first pixel: finite data that the caller masks out.
+// first na4 entries of its row of G~ in 16-byte pieces (a lane only ever reads back what it copied itself, so no warp
+// synchronisation is needed; rows are GROW = 28 floats apart in shared memory too, which makes both the 16-byte copies
+// and the 16-byte reads conflict-free).  Lanes beyond the cell's last pixel copy the chunk's first pixel: finite data
+// that the caller masks out.
 __device__ __noinline__ void stage_chunk(char* stage, const double* __restrict__ py, const uint32_t* __restrict__ prc,
                                             const float* __restrict__ gcell, int npix, int na, int p0, int lane)
 {
     const int p = (p0 + lane < npix) ? p0 + lane : p0;
     float* G = reinterpret_cast<float*>(stage);
-    double* Y = reinterpret_cast<double*>(stage + NSLOT * 32 * 4);
-    uint32_t* RC = reinterpret_cast<uint32_t*>(stage + NSLOT * 32 * 4 + 32 * 8);
+    double* Y = reinterpret_cast<double*>(stage + GROW * 32 * 4);
+    uint32_t* RC = reinterpret_cast<uint32_t*>(stage + GROW * 32 * 4 + 32 * 8);
     cp_async8(Y + lane, py + p);
     cp_async4(RC + lane, prc + p);
-    const float* gp = gcell + p;
-    float* gs = G + lane;
-    // rolled: the code of the evaluation items must stay small (instruction cache)
-    int a = 0;
-#pragma unroll 1
-    for (; a + 4 <= na; a += 4) {
-        cp_async4(gs, gp); cp_async4(gs + 32, gp + npix); cp_async4(gs + 64, gp + 2 * npix); cp_async4(gs + 96, gp + 3 * npix);
-        gp += 4 * npix; gs += 128;
-    }
-#pragma unroll 1
-    for (; a < na; ++a) { cp_async4(gs, gp); gp += npix; gs += 32; }
+    const float* gp = gcell + (size_t)p * GROW;
+    float* gs = G + lane * GROW;
+#pragma unroll
+    for (int a = 0; a < GROW; a += 4)
+        if (a < na) cp_async16(gs + a, gp + a);          // warp-uniform
 }
 
 // Returns, in lane e, the cell's local gradient entry e (e < 6 + na), and in lane 31 its value.
@@ -196,23 +205,23 @@ __device__ __noinline__ double cell_value_grad(const double* __restrict__ py, co
         cp_async_commit();
         cp_async_wait<STAGES - 1>();                  // this lane's copies of chunk k have landed
         const char* stage = stages + slot * STAGE_BYTES;
-        const float* G = reinterpret_cast<const float*>(stage) + lane;
+        const float4* G4 = reinterpret_cast<const float4*>(stage) + lane * (GROW / 4);
         const bool act = 32 * k + lane < npix;
-        const uint32_t rc = reinterpret_cast<const uint32_t*>(stage + NSLOT * 32 * 4 + 32 * 8)[lane];
-        const double y = act ? reinterpret_cast<const double*>(stage + NSLOT * 32 * 4)[lane] : 0.0;
+        const uint32_t rc = reinterpret_cast<const uint32_t*>(stage + GROW * 32 * 4 + 32 * 8)[lane];
+        const double y = act ? reinterpret_cast<const double*>(stage + GROW * 32 * 4)[lane] : 0.0;
         const double x1 = xr[rc & 0xffffu], x2 = xc[rc >> 16];
         double S = cell_S(th, x1, x2);
-        double sx0 = 0, sx1 = 0;
-        {
-            int a = 0;
-#pragma unroll 2
-            for (; a + 1 < na; a += 2) {
-                sx0 = fma((double)G[a * 32], XI[a], sx0);
-                sx1 = fma((double)G[(a + 1) * 32], XI[a + 1], sx1);
+        double sx0 = 0, sx1 = 0, sx2 = 0, sx3 = 0;        // XI is zero beyond the cell's last active slot, and so is the row
+#pragma unroll
+        for (int j = 0; j < GROW / 4; ++j) {
+            if (4 * j < na) {                             // (warp-uniform)
+                const float4 g = G4[j];
+                const double2 xa = reinterpret_cast<const double2*>(XI)[2 * j], xb = reinterpret_cast<const double2*>(XI)[2 * j + 1];
+                sx0 = fma((double)g.x, xa.x, sx0); sx1 = fma((double)g.y, xa.y, sx1);
+                sx2 = fma((double)g.z, xb.x, sx2); sx3 = fma((double)g.w, xb.y, sx3);
             }
-            if (a < na) sx0 = fma((double)G[a * 32], XI[a], sx0);
         }
-        S += sx0 + sx1;
+        S += (sx0 + sx1) + (sx2 + sx3);
         double phi = 0, theta = 0;
         if (act) logistic(y, S, phi, theta);
         const double u = -y * theta;                  // 0 for the lanes beyond the cell's last pixel (y = 0)
@@ -224,12 +233,14 @@ __device__ __noinline__ double cell_value_grad(const double* __restrict__ py, co
         const double ux = (tol > 0 && fabs(u) < tol) ? 0.0 : u;
         // the row of G~ is read from shared memory a second time instead of living in 25 registers across the logistic
         // function: with the 32 accumulators that would not fit the 128 registers two resident CTAs per SM allow
-        const volatile float* G2 = G;
 #pragma unroll
-        for (int g = 0; g < NSLOT; g += 5) {
-            if (g < na) {                             // (warp-uniform) nothing is issued for the slots beyond the cell's last one
-#pragma unroll
-                for (int a = g; a < g + 5; ++a) if (a < na) acc[6 + a] = fma(ux, (double)G2[a * 32], acc[6 + a]);
+        for (int j = 0; j < GROW / 4; ++j) {
+            if (4 * j < na) {                             // (warp-uniform) nothing is issued for the slots beyond the cell's last one
+                const float4 g = lds128_again(G4 + j);
+                acc[6 + 4 * j] = fma(ux, (double)g.x, acc[6 + 4 * j]);
+                if (4 * j + 1 < NSLOT) acc[7 + 4 * j] = fma(ux, (double)g.y, acc[7 + 4 * j]);
+                if (4 * j + 2 < NSLOT) acc[8 + 4 * j] = fma(ux, (double)g.z, acc[8 + 4 * j]);
+                if (4 * j + 3 < NSLOT) acc[9 + 4 * j] = fma(ux, (double)g.w, acc[9 + 4 * j]);
             }
         }
         slot = (slot + 1 == STAGES) ? 0 : slot + 1;
@@ -267,15 +278,21 @@ __device__ __noinline__ void cell_hessian(const double* __restrict__ py, const u
         double* col = Tt + lane;
         double sx0 = 0, sx1 = 0;
         {
-            const float* gp = gcell + (act ? p : 0);
-            int a = 0;
-#pragma unroll 2
-            for (; a + 1 < na; a += 2) {
-                const double g0 = act ? (double)gp[(size_t)a * npix] : 0.0, g1 = act ? (double)gp[(size_t)(a + 1) * npix] : 0.0;
-                col[(6 + a) * TILE_LD] = g0; col[(7 + a) * TILE_LD] = g1;
-                sx0 = fma(g0, XI[a], sx0); sx1 = fma(g1, XI[a + 1], sx1);
+            const float4* gp = reinterpret_cast<const float4*>(gcell + (size_t)(act ? p : 0) * GROW);
+#pragma unroll
+            for (int j = 0; j < GROW / 4; ++j) {
+                if (4 * j < na) {                         // (warp-uniform)
+                    float4 g = __ldg(gp + j);
+                    if (!act) g = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const double g0 = g.x, g1 = g.y, g2 = g.z, g3 = g.w;
+                    col[(6 + 4 * j) * TILE_LD] = g0;
+                    if (4 * j + 1 < na) col[(7 + 4 * j) * TILE_LD] = g1;
+                    if (4 * j + 2 < na) col[(8 + 4 * j) * TILE_LD] = g2;
+                    if (4 * j + 3 < na) col[(9 + 4 * j) * TILE_LD] = g3;
+                    sx0 = fma(g0, XI[4 * j], sx0); sx1 = fma(g1, XI[4 * j + 1], sx1);
+                    sx0 = fma(g2, XI[4 * j + 2], sx0); sx1 = fma(g3, XI[4 * j + 3], sx1);
+                }
             }
-            if (a < na) { const double g0 = act ? (double)gp[(size_t)a * npix] : 0.0; col[(6 + a) * TILE_LD] = g0; sx0 = fma(g0, XI[a], sx0); }
         }
         S += sx0 + sx1;
         double phi = 0, theta = 0;
@@ -328,7 +345,7 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
     double* XI = Tt + XI_OFF;
     const int na = __popc(am);
     __syncwarp();
-    if (lane < na) XI[lane] = x[6 + slotj[lane]];     // the xi values this cell sees
+    XI[lane] = lane < na ? x[6 + slotj[lane]] : 0.0;  // the xi values this cell sees (zero-padded: rows are read in groups of four)
     __syncwarp();
     const double tot = cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI);
     if (lane < 6 || lane == 31) sg[lane] = tot;
@@ -404,7 +421,7 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
         slotj[lane] = ws.cellmap[cell_off + (ca + s / 5 - NC) * cw + (cb + s % 5 - NC)];
     }
     __syncwarp();
-    const float* gcell = ws.gval + (size_t)NSLOT * (pix_off + st);
+    const float* gcell = ws.gval + (size_t)GROW * (pix_off + st);
     double* xig = ws.xig + (size_t)cell_off * NSLOT;
     if (rq.want_h) eval_cell_xi<true>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
     else eval_cell_xi<false>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);

@@ -254,15 +254,16 @@ k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int3
         }
         __syncthreads();
 
-        // (f) G~ values per (cell, active slot, pixel) and the active-slot mask of every cell
-        float* gv = ws.gval + (size_t)NSLOT * cd.pix_off;
+        // (f) G~ values per (cell, pixel, active slot) and the active-slot mask of every cell: a pixel's row is GROW floats,
+        //     the active slots first (in slot order), zeros up to the next multiple of four (the evaluation reads 16-byte groups)
+        float* gv = ws.gval + (size_t)GROW * cd.pix_off;
         uint32_t* amask = ws.cell_amask + cd.cell_off;
         for (int cell = cell0 + warp; cell < cell1; cell += BLOCK / 32) {
             const int st = cstart[cell], npix = cstart[cell + 1] - st;
             uint32_t am = 0;
             if (npix > 0) {
                 const int ca = cell / cw, cb = cell - ca * cw;
-                float* out = gv + (size_t)NSLOT * st;
+                float* out = gv + (size_t)GROW * st;
                 int na = 0;
                 for (int s = 0; s < NSLOT; ++s) {
                     const int a = ca + s / 5 - NC, b = cb + s % 5 - NC;
@@ -277,10 +278,12 @@ k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int3
                         const int dr = abs(gr - (int)(q & 0xffffu)), dc = abs(gc - (int)(q >> 16));
                         float v = 0.f;
                         if (dr <= R && dc <= R) { v = __fdiv_rn(s_psf[dr * R1 + dc], ps[st + p]); any = true; }
-                        out[(size_t)na * npix + p] = v;
+                        out[(size_t)p * GROW + na] = v;
                     }
                     if (__any_sync(0xffffffffu, any)) { am |= 1u << s; ++na; }
                 }
+                for (int a = na; a < ((na + 3) & ~3); ++a)
+                    for (int p = lane; p < npix; p += 32) out[(size_t)p * GROW + a] = 0.f;
             }
             if (lane == 0) amask[cell] = am;
         }
