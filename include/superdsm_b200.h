@@ -26,7 +26,7 @@
  *                         one control CTA
  *   SDSM_TASK_SMALL_CELLS (512)  candidates with at most this many cells get evaluation items of one cell (else 4)
  *   SDSM_HI_FRAC (0.02)   share of the batch (most expensive candidates first) whose tasks are urgent from the start
- *   SDSM_HI_EVALS (200)   a candidate that has needed more evaluations than this becomes urgent
+ *   SDSM_HI_EVALS (300)   a candidate that has needed more evaluations than this becomes urgent
  *   SDSM_TIMEOUT_S (60)   watchdog of the persistent solver kernel
  */
 #ifndef SUPERDSM_B200_H

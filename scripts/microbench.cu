@@ -40,11 +40,48 @@ __global__ void __launch_bounds__(256) k_f2f(double* out, const float* in, int i
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
             double d;
+            f[k] = f[k] * 1.0000001f + 1e-7f;              // loop-variant input (FP32 pipe, full rate)
             asm volatile("cvt.f64.f32 %0, %1;" : "=d"(d) : "f"(f[k]));
             u ^= (unsigned)__double2hiint(d);
         }
     }
     acc = u;
+    if (u == 0x12345678u) out[0] = acc;
+}
+
+// the same conversion with integer instructions (non-negative normal or zero inputs)
+__global__ void __launch_bounds__(256) k_f2f_int(double* out, const float* in, int iters)
+{
+    float f[8];
+    for (int k = 0; k < 8; ++k) f[k] = in[threadIdx.x + k];
+    unsigned u = 0;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            unsigned b;
+            f[k] = f[k] * 1.0000001f + 1e-7f;
+            asm volatile("mov.b32 %0, %1;" : "=r"(b) : "f"(f[k]));
+            const unsigned hi = b ? (b >> 3) + 0x38000000u : 0u, lo = b << 29;
+            u ^= hi + lo;
+        }
+    }
+    if (u == 0x12345678u) out[0] = (double)u;
+}
+
+// dependent chain: F2F feeding a DFMA accumulator (latency of the pair)
+__global__ void __launch_bounds__(32) k_chain(double* out, const float* in, int iters, long long* cycles)
+{
+    float f = in[threadIdx.x];
+    double acc = 0;
+    const long long t0 = clock64();
+    for (int i = 0; i < iters; ++i) {
+        double d;
+        asm volatile("cvt.f64.f32 %0, %1;" : "=d"(d) : "f"(f));
+        acc = fma(d, 1.0000001, acc);
+        f = __double2float_rn(acc) ;
+    }
+    const long long t1 = clock64();
+    if (threadIdx.x == 0) cycles[0] = t1 - t0;
     if (acc == 12345.678) out[0] = acc;
 }
 
@@ -102,6 +139,18 @@ int main()
         const float ms = time_ms([&] { k_f2f<<<blocks, 256>>>(d_out, d_f, iters); });
         const double ops = (double)blocks * 256 * 8 * iters;
         printf("F2F.F64.F32 : %6.1f conversions/clk/SM\n", ops / (ms * 1e-3) / clk / sms);
+    }
+    {
+        const int iters = 20000;
+        const float ms = time_ms([&] { k_f2f_int<<<blocks, 256>>>(d_out, d_f, iters); });
+        const double ops = (double)blocks * 256 * 8 * iters;
+        printf("f32->f64 int: %6.1f conversions/clk/SM (4 integer instructions each)\n", ops / (ms * 1e-3) / clk / sms);
+    }
+    {
+        long long* d_c; cudaMalloc(&d_c, 8);
+        k_chain<<<1, 32>>>(d_out, d_f, 10000, d_c);
+        long long c; cudaMemcpy(&c, d_c, 8, cudaMemcpyDeviceToHost);
+        printf("chain F2F.F64.F32 -> DFMA -> F2F.F32.F64: %.1f clk per round\n", c / 10000.0);
     }
     {
         const int iters = 2000;

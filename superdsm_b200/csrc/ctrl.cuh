@@ -453,7 +453,15 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
                 __syncwarp();
                 if (lane > cc && lane < kw) {
                     const double l = sb.D[lane * CB_LD + cc];
-                    for (int j = cc + 1; j <= lane; ++j) sb.D[lane * CB_LD + j] = fma(-l, sb.D[j * CB_LD + cc], sb.D[lane * CB_LD + j]);
+                    double* row = sb.D + lane * CB_LD;
+                    const double* colc = sb.D + cc;          // column cc (already scaled); never aliases row[j], j > cc
+                    int j = cc + 1;
+                    for (; j + 3 <= lane; j += 4) {          // four independent updates in flight (shared-memory latency)
+                        const double d0 = colc[j * CB_LD], d1 = colc[(j + 1) * CB_LD], d2 = colc[(j + 2) * CB_LD], d3 = colc[(j + 3) * CB_LD];
+                        const double a0 = row[j], a1 = row[j + 1], a2 = row[j + 2], a3 = row[j + 3];
+                        row[j] = fma(-l, d0, a0); row[j + 1] = fma(-l, d1, a1); row[j + 2] = fma(-l, d2, a2); row[j + 3] = fma(-l, d3, a3);
+                    }
+                    for (; j <= lane; ++j) row[j] = fma(-l, colc[j * CB_LD], row[j]);
                 }
                 __syncwarp();
             }

@@ -36,7 +36,7 @@ struct sdsm_ctx {
     bool ctrl_ctas_fixed = false;            // SDSM_CTRL_CTAS given: no adaptation to the batch
     double solo_share = 0.0;                 // share of the last planned batch's pixels in candidates whose chains stay in one CTA
     int ctrl_ctas = 48;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
-    int hi_evals = 200;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
+    int hi_evals = 300;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     std::string err;
 };
 
