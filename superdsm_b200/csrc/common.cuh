@@ -94,7 +94,7 @@ struct WS {
     uint32_t* pix_rc;      // [P]      compacted (row | col << 16) inside the bounding box
     float*    pix_s;       // [P]      float32 row sum of the un-normalised G~ row (dsm.py:192)
     int32_t*  pix_dist;    // [P]      chessboard distance to the sub-sample grid (dsm.py:169-179)
-    float*    gval;        // [28 P]   G~ values: cell -> pixel -> active slot (rows of GROW floats, zero beyond the cell's last active slot)
+    float*    gval;        // [28 P]   G~ values: cell (block at GROW * first pixel) -> pixel -> active slot (rows of na4 floats, zero-padded)
     int32_t*  cell_start;  // [C]      first pixel of each cell (cell_cap + 1 entries per candidate)
     uint32_t* cell_amask;  // [C]      bit s: neighbour cell s holds a grid point with a non-zero weight in this cell
     int32_t*  cellmap;     // [C]      grid index of the cell's grid point or -1

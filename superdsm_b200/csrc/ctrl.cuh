@@ -375,9 +375,19 @@ __device__ __forceinline__ void carve_smem_big(Sm& sm, char* base)
 // the rows below are solved against it.  Global memory (the factor lives in L2) is only touched with coalesced rows, staged
 // through shared-memory tiles: two tiles of A[k-rows, .] shared by the CTA per step, one tile per warp for its own rows.
 // (The right-looking version this replaces spent 1-3 ms per factorisation at N = 300-450 waiting for L2 round trips.)
+#ifdef SDSM_CHOL_TRACE
+__device__ int chol_trace_count = 0;
+#define CHOL_T(k) { const long long now_ = clock64(); ct_[k] += now_ - cl_; cl_ = now_; }
+#else
+#define CHOL_T(k)
+#endif
+
 template <int BLOCK>
 __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
 {
+#ifdef SDSM_CHOL_TRACE
+    long long ct_[5] = {0, 0, 0, 0, 0}, cl_ = clock64();
+#endif
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = BLOCK / 32;
     const int fr = lane >> 2, fk = lane & 3;                 // DMMA fragment coordinates (eval.cuh::dmma884)
@@ -387,6 +397,7 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
         for (int j = lane; j <= i; j += 32) A[(size_t)i * N + j] = H[(size_t)i * N + j];
     if (tid == 0) sb.flag[0] = 0;
     __syncthreads();
+    CHOL_T(0);
     for (int k0 = 0; k0 < N; k0 += CB) {
         const int kw = min(CB, N - k0);
         const int nrb = (N - k0 + CB - 1) / CB;              // row blocks of the panel; block 0 holds the diagonal block
@@ -436,6 +447,7 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
             }
         }
         __syncthreads();
+        CHOL_T(1);
         // (2) diagonal block -> shared memory, factorised by warp 0 (lane = row)
         for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
         __syncthreads();
@@ -467,6 +479,7 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
             }
         }
         __syncthreads();
+        CHOL_T(2);
         if (sb.flag[0]) return false;
         for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) A[(size_t)(k0 + r) * N + k0 + q] = sb.D[r * CB_LD + q]; }
         const int r0 = k0 + kw;
@@ -499,7 +512,15 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
             if (lane < kw) for (int r = 0; r < nr; ++r) A[(size_t)(i0 + r) * N + k0 + lane] = W[r * CB_LD + lane];
         }
         // the next panel's step (1) starts with a CTA barrier
+#ifdef SDSM_CHOL_TRACE
+        __syncthreads();
+#endif
+        CHOL_T(3);
     }
+#ifdef SDSM_CHOL_TRACE
+    if (tid == 0 && atomicAdd(&chol_trace_count, 1) % 500 == 0)
+        printf("cholesky_big N %d: copy %lld update %lld diag %lld solve %lld cycles\n", N, ct_[0], ct_[1], ct_[2], ct_[3]);
+#endif
     return true;
 }
 
@@ -1136,7 +1157,7 @@ k_finish(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS w
                     const double X1 = (double)(cd.r0 + br + 1), X2 = (double)(cd.c0 + bc + 1);
                     double S = (X1 * M11 + X2 * M12) * X1 + (X1 * M12 + X2 * M22) * X2 + 2 * (X1 * mb1 + X2 * mb2) + mc;
                     double sxi = 0;
-                    for (int a = 0; a < na; ++a) sxi += (double)gcell[(size_t)p * GROW + a] * x[6 + slotj[a]];
+                    for (int a = 0; a < na; ++a) sxi += (double)gcell[(size_t)p * ((na + 3) & ~3) + a] * x[6 + slotj[a]];
                     S += sxi;
                     if (S > 0) {
                         fg[(size_t)br * cd.w + bc] = 1;
@@ -1203,7 +1224,7 @@ __global__ void k_export(Par par, const sdsm_cand* __restrict__ cands, int c, WS
                 if (a < na) {
                     const int s = nth_set_bit(am, a);
                     col = ws.cellmap[cd.cell_off + (ca + s / 5 - NC) * ci.cw + (cb + s % 5 - NC)];
-                    v = gv[(size_t)GROW * (st + p) + a];
+                    v = gv[(size_t)GROW * st + (size_t)p * ((na + 3) & ~3) + a];
                 }
                 cols[(size_t)(st + p) * NSLOT + a] = col;
                 vals[(size_t)(st + p) * NSLOT + a] = v;

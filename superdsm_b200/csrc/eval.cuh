@@ -175,7 +175,7 @@ __device__ __noinline__ void stage_chunk(char* stage, const double* __restrict__
     uint32_t* RC = reinterpret_cast<uint32_t*>(stage + GROW * 32 * 4 + 32 * 8);
     cp_async8(Y + lane, py + p);
     cp_async4(RC + lane, prc + p);
-    const float* gp = gcell + (size_t)p * GROW;
+    const float* gp = gcell + (size_t)p * ((na + 3) & ~3);      // rows of the cell's block: na4 floats each
     float* gs = G + lane * GROW;
 #pragma unroll
     for (int a = 0; a < GROW; a += 4)
@@ -278,7 +278,7 @@ __device__ __noinline__ void cell_hessian(const double* __restrict__ py, const u
         double* col = Tt + lane;
         double sx0 = 0, sx1 = 0;
         {
-            const float4* gp = reinterpret_cast<const float4*>(gcell + (size_t)(act ? p : 0) * GROW);
+            const float4* gp = reinterpret_cast<const float4*>(gcell + (size_t)(act ? p : 0) * ((na + 3) & ~3));
 #pragma unroll
             for (int j = 0; j < GROW / 4; ++j) {
                 if (4 * j < na) {                         // (warp-uniform)

@@ -254,8 +254,9 @@ k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int3
         }
         __syncthreads();
 
-        // (f) G~ values per (cell, pixel, active slot) and the active-slot mask of every cell: a pixel's row is GROW floats,
-        //     the active slots first (in slot order), zeros up to the next multiple of four (the evaluation reads 16-byte groups)
+        // (f) G~ values per (cell, pixel, active slot) and the active-slot mask of every cell: the cell's block starts at
+        //     GROW * (first pixel) and holds one row per pixel of na4 = #active slots rounded up to a multiple of four floats
+        //     (the evaluation reads 16-byte groups), the active slots in slot order, zeros behind them
         float* gv = ws.gval + (size_t)GROW * cd.pix_off;
         uint32_t* amask = ws.cell_amask + cd.cell_off;
         for (int cell = cell0 + warp; cell < cell1; cell += BLOCK / 32) {
@@ -264,7 +265,7 @@ k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int3
             if (npix > 0) {
                 const int ca = cell / cw, cb = cell - ca * cw;
                 float* out = gv + (size_t)GROW * st;
-                int na = 0;
+                // active slots: grid points of the 5 x 5 neighbour cells within the kernel radius of some pixel of the cell
                 for (int s = 0; s < NSLOT; ++s) {
                     const int a = ca + s / 5 - NC, b = cb + s % 5 - NC;
                     if (a < 0 || a >= ch || b < 0 || b >= cw) continue;
@@ -275,15 +276,25 @@ k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int3
                     bool any = false;
                     for (int p = lane; p < npix; p += 32) {
                         const uint32_t q = prc[st + p];
-                        const int dr = abs(gr - (int)(q & 0xffffu)), dc = abs(gc - (int)(q >> 16));
-                        float v = 0.f;
-                        if (dr <= R && dc <= R) { v = __fdiv_rn(s_psf[dr * R1 + dc], ps[st + p]); any = true; }
-                        out[(size_t)p * GROW + na] = v;
+                        any |= abs(gr - (int)(q & 0xffffu)) <= R && abs(gc - (int)(q >> 16)) <= R;
                     }
-                    if (__any_sync(0xffffffffu, any)) { am |= 1u << s; ++na; }
+                    if (__any_sync(0xffffffffu, any)) am |= 1u << s;
                 }
-                for (int a = na; a < ((na + 3) & ~3); ++a)
-                    for (int p = lane; p < npix; p += 32) out[(size_t)p * GROW + a] = 0.f;
+                const int na4 = (__popc(am) + 3) & ~3;       // row stride of this cell's block (floats)
+                int rank = 0;
+                for (int s = 0; s < NSLOT; ++s) {
+                    if (!((am >> s) & 1u)) continue;
+                    const uint32_t g = gs[cellmap[(ca + s / 5 - NC) * cw + (cb + s % 5 - NC)]];
+                    const int gr = g & 0xffffu, gc = g >> 16;
+                    for (int p = lane; p < npix; p += 32) {
+                        const uint32_t q = prc[st + p];
+                        const int dr = abs(gr - (int)(q & 0xffffu)), dc = abs(gc - (int)(q >> 16));
+                        out[(size_t)p * na4 + rank] = (dr <= R && dc <= R) ? __fdiv_rn(s_psf[dr * R1 + dc], ps[st + p]) : 0.f;
+                    }
+                    ++rank;
+                }
+                for (int a = rank; a < na4; ++a)
+                    for (int p = lane; p < npix; p += 32) out[(size_t)p * na4 + a] = 0.f;
             }
             if (lane == 0) amask[cell] = am;
         }
