@@ -405,9 +405,22 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
         for (int j0 = 0; j0 < k0; j0 += 2 * CB) {
             const int nt = (j0 + CB < k0) ? 2 : 1;
             __syncthreads();                                 // the tiles of the previous step are no longer in use
-            for (int e = tid; e < nt * CB * CB; e += BLOCK) {
-                const int t = e / (CB * CB), r = (e / CB) % CB, q = e % CB;
-                (t ? sb.Xj : sb.D)[r * TL + q] = r < kw ? A[(size_t)(k0 + r) * N + j0 + t * CB + q] : 0.0;
+            {
+                // all loads first, then the stores (the compiler may not reorder them itself: it cannot rule out aliasing)
+                constexpr int PER = 2 * CB * CB / BLOCK;
+                double v[PER];
+#pragma unroll
+                for (int u = 0; u < PER; ++u) {
+                    const int e = tid + u * BLOCK;
+                    const int t = e / (CB * CB), r = (e / CB) % CB, q = e % CB;
+                    v[u] = (e < nt * CB * CB && r < kw) ? A[(size_t)(k0 + r) * N + j0 + t * CB + q] : 0.0;
+                }
+#pragma unroll
+                for (int u = 0; u < PER; ++u) {
+                    const int e = tid + u * BLOCK;
+                    const int t = e / (CB * CB), r = (e / CB) % CB, q = e % CB;
+                    if (e < nt * CB * CB) (t ? sb.Xj : sb.D)[r * TL + q] = v[u];
+                }
             }
             __syncthreads();
             for (int ib = warp; ib < nrb; ib += NW) {
@@ -420,8 +433,14 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
                 for (int t = 0; t < nt; ++t) {
                     const double* T = t ? sb.Xj : sb.D;
                     __syncwarp();
-#pragma unroll 8
-                    for (int r = 0; r < CB; ++r) W[r * TL + lane] = r < nr ? A[(size_t)(i0 + r) * N + j0 + t * CB + lane] : 0.0;
+#pragma unroll
+                    for (int rb = 0; rb < CB; rb += 16) {
+                        double v[16];
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) v[u] = rb + u < nr ? A[(size_t)(i0 + rb + u) * N + j0 + t * CB + lane] : 0.0;
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) W[(rb + u) * TL + lane] = v[u];
+                    }
                     __syncwarp();
 #pragma unroll 2
                     for (int kk = 0; kk < 8; ++kk) {
@@ -441,9 +460,16 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
 #pragma unroll
                     for (int J = 0; J < 4; ++J) { W[(8 * I + fr) * TL + 8 * J + 2 * fk] = c[I][J][0]; W[(8 * I + fr) * TL + 8 * J + 2 * fk + 1] = c[I][J][1]; }
                 __syncwarp();
-                if (lane < kw)
-                    for (int r = 0; r < nr; ++r)
-                        if (k0 + lane <= i0 + r) A[(size_t)(i0 + r) * N + k0 + lane] -= W[r * TL + lane];      // lower triangle only
+                if (lane < kw) {
+#pragma unroll
+                    for (int rb = 0; rb < CB; rb += 16) {
+                        double v[16];
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) { const int r = rb + u; v[u] = (r < nr && k0 + lane <= i0 + r) ? A[(size_t)(i0 + r) * N + k0 + lane] : 0.0; }
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) { const int r = rb + u; if (r < nr && k0 + lane <= i0 + r) A[(size_t)(i0 + r) * N + k0 + lane] = v[u] - W[r * TL + lane]; }   // lower triangle only
+                    }
+                }
             }
         }
         __syncthreads();
@@ -451,31 +477,29 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
         // (2) diagonal block -> shared memory, factorised by warp 0 (lane = row)
         for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
         __syncthreads();
-        if (warp == 0) {
+        {
+            // right-looking on the shared-memory block, the whole CTA per column: thread (i, s) = (tid / 8, tid % 8) updates
+            // the entries j = cc + 1 + s, + 8, ... <= i of row cc + 1 + i from the UNSCALED column cc; the scaled column
+            // is written after the barrier (nobody reads column cc again), so there is one barrier per column.
+            const int ri = tid >> 3, rs = tid & 7;
             for (int cc = 0; cc < kw; ++cc) {
                 const double dk = sb.D[cc * CB_LD + cc];
-                if (!(dk > 0.0) || !isfinite(dk)) { if (lane == 0) sb.flag[0] = 1; break; }
+                if (!(dk > 0.0) || !isfinite(dk)) { if (tid == 0) sb.flag[0] = 1; break; }      // uniform: every thread reads the same value
                 const double rinv = rsqrt(dk);
-                __syncwarp();
-                if (lane == cc) sb.D[cc * CB_LD + cc] = rinv;
-                if (lane > cc && lane < kw) {
-                    const double l = sb.D[lane * CB_LD + cc] * rinv;
-                    sb.D[lane * CB_LD + cc] = l;
-                }
-                __syncwarp();
-                if (lane > cc && lane < kw) {
-                    const double l = sb.D[lane * CB_LD + cc];
-                    double* row = sb.D + lane * CB_LD;
-                    const double* colc = sb.D + cc;          // column cc (already scaled); never aliases row[j], j > cc
-                    int j = cc + 1;
-                    for (; j + 3 <= lane; j += 4) {          // four independent updates in flight (shared-memory latency)
-                        const double d0 = colc[j * CB_LD], d1 = colc[(j + 1) * CB_LD], d2 = colc[(j + 2) * CB_LD], d3 = colc[(j + 3) * CB_LD];
-                        const double a0 = row[j], a1 = row[j + 1], a2 = row[j + 2], a3 = row[j + 3];
-                        row[j] = fma(-l, d0, a0); row[j + 1] = fma(-l, d1, a1); row[j + 2] = fma(-l, d2, a2); row[j + 3] = fma(-l, d3, a3);
+                const int i = cc + 1 + ri;
+                double li = 0.0;
+                if (i < kw) {
+                    li = sb.D[i * CB_LD + cc] * rinv;
+                    double* row = sb.D + i * CB_LD;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int j = cc + 1 + rs + 8 * u;
+                        if (j <= i) row[j] = fma(-li, sb.D[j * CB_LD + cc] * rinv, row[j]);
                     }
-                    for (; j <= lane; ++j) row[j] = fma(-l, colc[j * CB_LD], row[j]);
                 }
-                __syncwarp();
+                __syncthreads();
+                if (i < kw && rs == 0) sb.D[i * CB_LD + cc] = li;
+                if (tid == 0) sb.D[cc * CB_LD + cc] = rinv;
             }
         }
         __syncthreads();
