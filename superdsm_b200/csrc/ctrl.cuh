@@ -393,8 +393,8 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
     const int fr = lane >> 2, fk = lane & 3;                 // DMMA fragment coordinates (eval.cuh::dmma884)
     double* W = sb.Wt + warp * CB * TL;
     __syncthreads();
-    for (int i = warp; i < N; i += NW)
-        for (int j = lane; j <= i; j += 32) A[(size_t)i * N + j] = H[(size_t)i * N + j];
+    // No copy H -> A up front: whatever touches a panel first (its first update step, or for panel 0 the diagonal block and
+    // the solve below it) reads H and writes A.
     if (tid == 0) sb.flag[0] = 0;
     __syncthreads();
     CHOL_T(0);
@@ -465,7 +465,7 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
                     for (int rb = 0; rb < CB; rb += 16) {
                         double v[16];
 #pragma unroll
-                        for (int u = 0; u < 16; ++u) { const int r = rb + u; v[u] = (r < nr && k0 + lane <= i0 + r) ? A[(size_t)(i0 + r) * N + k0 + lane] : 0.0; }
+                        for (int u = 0; u < 16; ++u) { const int r = rb + u; v[u] = (r < nr && k0 + lane <= i0 + r) ? (j0 == 0 ? H : A)[(size_t)(i0 + r) * N + k0 + lane] : 0.0; }
 #pragma unroll
                         for (int u = 0; u < 16; ++u) { const int r = rb + u; if (r < nr && k0 + lane <= i0 + r) A[(size_t)(i0 + r) * N + k0 + lane] = v[u] - W[r * TL + lane]; }   // lower triangle only
                     }
@@ -475,7 +475,14 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
         __syncthreads();
         CHOL_T(1);
         // (2) diagonal block -> shared memory, factorised by warp 0 (lane = row)
-        for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        {
+            const double* S0 = k0 == 0 ? H : A;
+            double v[CB * CB / BLOCK];
+#pragma unroll
+            for (int u = 0; u < CB * CB / BLOCK; ++u) { const int e = tid + u * BLOCK, r = e / CB, q = e % CB; v[u] = (r < kw && q <= r) ? S0[(size_t)(k0 + r) * N + k0 + q] : 0.0; }
+#pragma unroll
+            for (int u = 0; u < CB * CB / BLOCK; ++u) { const int e = tid + u * BLOCK, r = e / CB, q = e % CB; if (r < kw && q <= r) sb.D[r * CB_LD + q] = v[u]; }
+        }
         __syncthreads();
         {
             // right-looking on the shared-memory block, the whole CTA per column: thread (i, s) = (tid / 8, tid % 8) updates
@@ -514,7 +521,17 @@ __device__ bool cholesky_big(const double* H, int N, double* A, Sm& sb)
         for (int i0 = r0 + warp * CB; i0 < N; i0 += NW * CB) {
             const int nr = min(CB, N - i0);
             __syncwarp();
-            for (int r = 0; r < nr; ++r) W[r * CB_LD + lane] = lane < kw ? A[(size_t)(i0 + r) * N + k0 + lane] : 0.0;
+            {
+                const double* S0 = k0 == 0 ? H : A;
+#pragma unroll
+                for (int rb = 0; rb < CB; rb += 16) {
+                    double v[16];
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) v[u] = (rb + u < nr && lane < kw) ? S0[(size_t)(i0 + rb + u) * N + k0 + lane] : 0.0;
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) if (rb + u < nr) W[(rb + u) * CB_LD + lane] = v[u];
+                }
+            }
             __syncwarp();
             if (lane < nr) {
                 double r[CB];
