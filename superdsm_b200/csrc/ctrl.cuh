@@ -577,12 +577,25 @@ __device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
     // forward: L y = v
     for (int k0 = 0; k0 < N; k0 += CB) {
         const int kw = min(CB, N - k0);
-        for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        {   // diagonal block -> shared memory (loads batched in registers: one L2 round trip instead of four)
+            double dv[CB * CB / BLOCK];
+#pragma unroll
+            for (int u = 0; u < CB * CB / BLOCK; ++u) { const int e = tid + u * BLOCK, r = e / CB, q = e % CB; dv[u] = (r < kw && q <= r) ? A[(size_t)(k0 + r) * N + k0 + q] : 0.0; }
+#pragma unroll
+            for (int u = 0; u < CB * CB / BLOCK; ++u) { const int e = tid + u * BLOCK, r = e / CB, q = e % CB; if (r < kw && q <= r) sb.D[r * CB_LD + q] = dv[u]; }
+        }
         for (int r = warp; r < kw; r += NW) {                // y_k = v_k - L[k-rows, 0:k0] y[0:k0], a warp per row
             const double* ar = A + (size_t)(k0 + r) * N;
             double a = 0;
-            for (int q = lane; q < k0; q += 32) a = fma(ar[q], v[q], a);
-            a = warp_sum(a);
+            double a1 = 0, a2 = 0, a3 = 0;
+            int q = lane;
+            for (; q + 96 < k0; q += 128) {
+                const double l0 = ar[q], l1 = ar[q + 32], l2 = ar[q + 64], l3 = ar[q + 96];
+                const double v0 = v[q], v1 = v[q + 32], v2 = v[q + 64], v3 = v[q + 96];
+                a = fma(l0, v0, a); a1 = fma(l1, v1, a1); a2 = fma(l2, v2, a2); a3 = fma(l3, v3, a3);
+            }
+            for (; q < k0; q += 32) a = fma(ar[q], v[q], a);
+            a = warp_sum((a + a1) + (a2 + a3));
             if (lane == 0) sb.yv[r] = v[k0 + r] - a;
         }
         __syncthreads();
@@ -600,10 +613,26 @@ __device__ void chol_solve_big(const double* A, int N, double* v, Sm& sb)
     // backward: L^T x = y
     for (int k0 = ((N - 1) / CB) * CB; k0 >= 0; k0 -= CB) {
         const int kw = min(CB, N - k0);
-        for (int e = tid; e < kw * kw; e += BLOCK) { const int r = e / kw, q = e - r * kw; if (q <= r) sb.D[r * CB_LD + q] = A[(size_t)(k0 + r) * N + k0 + q]; }
+        {   // diagonal block -> shared memory (loads batched in registers: one L2 round trip instead of four)
+            double dv[CB * CB / BLOCK];
+#pragma unroll
+            for (int u = 0; u < CB * CB / BLOCK; ++u) { const int e = tid + u * BLOCK, r = e / CB, q = e % CB; dv[u] = (r < kw && q <= r) ? A[(size_t)(k0 + r) * N + k0 + q] : 0.0; }
+#pragma unroll
+            for (int u = 0; u < CB * CB / BLOCK; ++u) { const int e = tid + u * BLOCK, r = e / CB, q = e % CB; if (r < kw && q <= r) sb.D[r * CB_LD + q] = dv[u]; }
+        }
         {   // x_k = y_k - L[rows below, k-columns]^T x[rows below]: lane = column (coalesced), the rows dealt to the warps
             double a = 0;
-            if (lane < kw) for (int i = k0 + kw + warp; i < N; i += NW) a = fma(A[(size_t)i * N + k0 + lane], v[i], a);
+            if (lane < kw) {
+                double a1 = 0, a2 = 0, a3 = 0;
+                int i = k0 + kw + warp;
+                for (; i + 3 * NW < N; i += 4 * NW) {
+                    const double l0 = A[(size_t)i * N + k0 + lane], l1 = A[(size_t)(i + NW) * N + k0 + lane];
+                    const double l2 = A[(size_t)(i + 2 * NW) * N + k0 + lane], l3 = A[(size_t)(i + 3 * NW) * N + k0 + lane];
+                    a = fma(l0, v[i], a); a1 = fma(l1, v[i + NW], a1); a2 = fma(l2, v[i + 2 * NW], a2); a3 = fma(l3, v[i + 3 * NW], a3);
+                }
+                for (; i < N; i += NW) a = fma(A[(size_t)i * N + k0 + lane], v[i], a);
+                a = (a + a1) + (a2 + a3);
+            }
             sb.red_part[warp * 32 + lane] = a;
         }
         __syncthreads();
