@@ -406,7 +406,13 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     double* sh = ws.scrH + (size_t)(cell_off + cell) * SCRH;
     if (!rq.use_xi) {
         if (rq.want_h) eval_cell_poly<true>(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
-        else eval_cell_poly<false>(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
+        else {
+            // value + gradient of the polynomial model = the deformable pass without slots: same arithmetic in the same
+            // order as eval_cell_poly (the values of the two must agree bit for bit), but y and row|col arrive through
+            // the cp.async pipeline instead of dependent loads
+            const double tot = cell_value_grad(py, prc, nullptr, npix, 0, xr, xc, rq.x, par.sparsity_tol, reinterpret_cast<char*>(Tt), Tt + XI_OFF);
+            if (lane < 6 || lane == 31) sg[lane] = tot;
+        }
         return;
     }
     const int cw = ci.cw;
