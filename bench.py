@@ -9,15 +9,22 @@ rasterisation) over every candidate of one synthetic 1024 x 1024 image: atoms, c
 adjacent atoms the GEM stage enumerates.  With N > 1 every rank works on its own image (image-sharded, no collective on
 the data path; weak scaling); `value` = candidates of all ranks / max-over-ranks device time.
 """
-import argparse
-import json
 import os
-import subprocess
-import sys
-import tempfile
-import time
 
-import numpy as np
+# One BLAS / OpenMP thread per process, set BEFORE numpy loads its BLAS: the CPU arm runs one worker process per host core
+# (the reference's process-per-candidate model, objects.py:270-281, MKL_NUM_THREADS in examples/*/task.json); a BLAS pool
+# sized to all cores inside every worker would oversubscribe the box and halve the CPU arm's rate.
+for _var in ('OMP_NUM_THREADS', 'OPENBLAS_NUM_THREADS', 'MKL_NUM_THREADS', 'NUMEXPR_NUM_THREADS'):
+    os.environ[_var] = '1'
+
+import argparse                                     # noqa: E402
+import json                                         # noqa: E402
+import subprocess                                   # noqa: E402
+import sys                                          # noqa: E402
+import tempfile                                     # noqa: E402
+import time                                         # noqa: E402
+
+import numpy as np                                  # noqa: E402
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path: sys.path.insert(0, ROOT)
@@ -33,7 +40,7 @@ OTHER_WORKLOADS = {
 
 
 def make_workload(rank, args):
-    from superdsm_b200 import synth
+    from workloads import synth
     global WORKLOAD_DESC
     if args.workload != WORKLOAD:
         WORKLOAD_DESC, kw = OTHER_WORKLOADS[args.workload]
@@ -104,25 +111,69 @@ def _cpu_worker(job):
     y, y_mask, atoms, fp, cfg = job
     from oracle import dsm_oracle as orc
     t0 = time.perf_counter()
-    res = orc.compute_object(y, y_mask, atoms, fp, cfg)
-    return res['energy'], time.perf_counter() - t0
+    try:
+        res = orc.compute_object(y, y_mask, atoms, fp, cfg)
+        energy = res['energy']
+    except orc.CvxprogError:                        # a legitimate outcome of the reference too (objects.py:351-353)
+        energy = float('nan')
+    return energy, time.perf_counter() - t0
 
 
-def cpu_solves_per_second(w, sample, cores):
-    """Times the oracle on `sample` candidates spread over the size range, one worker process per host core (the
-    reference's Ray process-per-candidate model, objects.py:270-281), BLAS threads = 1."""
-    import multiprocessing as mp
-    os.environ.setdefault('OMP_NUM_THREADS', '1')
-    os.environ.setdefault('OPENBLAS_NUM_THREADS', '1')
-    fps = w['footprints']
-    idx = np.unique(np.linspace(0, len(fps) - 1, min(sample, len(fps))).astype(int))
-    jobs = [(w['y'], w['y_mask'], w['atoms'], fps[i], w['dsm_cfg']) for i in idx]
-    ctx = mp.get_context('fork')
-    t0 = time.perf_counter()
-    with ctx.Pool(cores) as pool:
-        out = pool.map(_cpu_worker, jobs, chunksize=1)
-    elapsed = time.perf_counter() - t0
-    return len(jobs) / elapsed, elapsed, len(jobs), float(np.sum([o[1] for o in out]))
+def _blas_threads():
+    """Effective BLAS / OpenMP thread count of a worker process (reported next to the CPU number)."""
+    try:
+        from threadpoolctl import threadpool_info
+        return max([int(p.get('num_threads', 1)) for p in threadpool_info()] or [1])
+    except Exception:
+        return None
+
+
+class CpuArm(object):
+    """The CPU implementation of the path (the oracle port) on all host cores: one worker process per core, one BLAS thread
+    each.  A step times a stratified sample: the candidates are sorted by pixel count and cut into `sample` strata of equal
+    size, step k takes member k (mod size) of every stratum, and every measured time stands for its whole stratum, so that
+    the figure is (time for ALL candidates of the image on `cores` cores, perfectly packed) -- candidates / that time."""
+
+    def __init__(self, w, cores, sample):
+        import multiprocessing as mp
+        self.w, self.cores = w, cores
+        fps = w['footprints']
+        count = np.bincount(np.asarray(w['atoms']).reshape(-1))
+        npix = np.array([sum(int(count[a]) for a in fp) for fp in fps])
+        order = np.argsort(npix, kind='stable')
+        self.strata = [s for s in np.array_split(order, min(sample, len(fps))) if len(s)]
+        self.pool = mp.get_context('fork').Pool(cores)
+        self.blas_threads = self.pool.apply(_blas_threads)
+        self.n = len(fps)
+
+    def step(self, k):
+        """Returns (estimated seconds for the whole candidate list on all cores, wall seconds of this step, core-seconds spent)."""
+        w = self.w
+        picks = [int(s[k % len(s)]) for s in self.strata][::-1]              # largest first: better packing of the pool
+        weights = [len(s) for s in self.strata][::-1]
+        jobs = [(w['y'], w['y_mask'], w['atoms'], w['footprints'][i], w['dsm_cfg']) for i in picks]
+        t0 = time.perf_counter()
+        out = self.pool.map(_cpu_worker, jobs, chunksize=1)
+        wall = time.perf_counter() - t0
+        core_s = float(np.sum([o[1] for o in out]))
+        est_all = float(np.sum([wt * o[1] for wt, o in zip(weights, out)])) / self.cores
+        return est_all, wall, core_s
+
+    def describe(self):
+        return (f'{len(self.strata)} of {self.n} candidates per step, stratified by pixel count (one per stratum, rotating), '
+                f'each weighted by its stratum size: value = candidates / (estimated time for all {self.n} on {self.cores} cores)')
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+def workload_config(w, world, args):
+    """The keys that define the workload: identical in both arms."""
+    return {'workload': WORKLOAD_DESC, 'candidates_per_image': len(w['footprints']), 'images_per_step': world,
+            'candidate_list': f'atoms + universes + adjacent-atom sets up to {args.max_set_size} (oversegment {args.oversegment})',
+            'sharding': 'one image of the same synthetic configuration per rank, no collective',
+            'l2': 'GPU arm: flushed between timed iterations (256 MiB write)'}
 
 
 def run_reference(args):
@@ -130,19 +181,26 @@ def run_reference(args):
     if rank != 0: return
     cores = os.cpu_count() or 1
     w = make_workload(0, args)
-    sample = max(cores, min(2 * cores, 64))
-    rates, times = [], []
+    arm = CpuArm(w, cores, sample=max(16, min(2 * cores, 64)))
+    est, walls = [], []
+    t_begin = time.perf_counter()
     for step in range(args.warmup + args.steps):
-        rate, elapsed, count, _ = cpu_solves_per_second(w, sample, cores)
-        if step >= args.warmup: rates.append(rate); times.append(elapsed)
-        if sum(times) > 240: break
-    value = float(np.mean(rates))
-    desc = f'{sample} of {len(w["footprints"])} candidates spread over the size range, per step'
+        if step < args.warmup:
+            if step == 0: arm.step(10 ** 6)                  # one untimed pass warms the workers (imports, page cache)
+            continue
+        e, wall, _ = arm.step(step - args.warmup)
+        est.append(e); walls.append(wall)
+        if time.perf_counter() - t_begin > 200 and len(est) >= 3: break      # time box: a few minutes in all
+    arm.close()
+    n = len(w['footprints'])
+    value = n * len(est) / float(np.sum(est))
+    desc = arm.describe()
     line = {'impl': 'reference', 'metric': 'dsm_candidate_solves_per_s', 'value': value, 'unit': 'candidate-solves/s',
-            'n_gpus': args.gpus, 'steps': len(rates), 'warmup': args.warmup, 'ms_per_step': 1e3 * float(np.mean(times)),
+            'n_gpus': args.gpus, 'steps': len(est), 'warmup': args.warmup, 'ms_per_step': 1e3 * float(np.mean(walls)),
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': WORKLOAD_DESC, 'candidates_per_image': len(w['footprints']), 'cpu_sample': desc},
-            'cpu_baseline': {'value': value, 'unit': 'candidate-solves/s', 'cores': cores, 'kind': 'port', 'sample': desc,
+            'config': workload_config(w, max(1, args.gpus), args),
+            'cpu_baseline': {'value': value, 'unit': 'candidate-solves/s', 'cores': cores, 'blas_threads_per_process': arm.blas_threads,
+                             'kind': 'port', 'sample': desc,
                              'note': 'numpy/scipy port of dsm.Energy + restated cvxopt cp (oracle/); the reference needs cvxopt + MKL, unavailable on this box'},
             'e2e': {'value': value, 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
@@ -271,10 +329,9 @@ def run_gpu(args):
             'metric': 'dsm_candidate_solves_per_s', 'value': value, 'unit': 'candidate-solves/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': WORKLOAD_DESC, 'candidates_per_image': len(fps), 'images_per_step': world,
-                       'pixels_per_step_per_gpu': int(handle['cands']['n'].sum()), 'parallelism': f'image-sharded x{world} (one image of the same synthetic configuration per rank), no collective',
-                       'l2': 'flushed between timed iterations (256 MiB write)', 'optimal': optimal, 'errors': n_errors,
-                       'images_per_s': world * args.steps / (total_ms_max * 1e-3)},
+            'config': workload_config(w, world, args),
+            'stats': {'pixels_per_step_per_gpu': int(handle['cands']['n'].sum()), 'optimal': optimal, 'errors': n_errors,
+                      'images_per_s': world * args.steps / (total_ms_max * 1e-3)},
             'e2e': {'value': cand_total * e2e_steps / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
                     'd2h_bytes_per_step': int(d2h), 'includes': 'pinned H2D of y, mask, atoms; device EDT + atom statistics; descriptors; solve; D2H of results; Object materialisation'},
             'gpu_launches': int(gpu_launches),
@@ -291,10 +348,12 @@ def run_gpu(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            sample = max(cores, min(2 * cores, 64))
-            rate, elapsed, count, cpu_s = cpu_solves_per_second(w, sample, cores)
-            line['cpu_baseline'] = {'value': rate, 'unit': 'candidate-solves/s', 'cores': cores, 'kind': 'port',
-                                    'sample': f'{count} of {len(fps)} candidates spread over the size range ({elapsed:.1f} s wall, {cpu_s:.1f} core-s)',
+            arm = CpuArm(w, cores, sample=max(16, min(2 * cores, 64)))
+            est_all, wall, cpu_s = arm.step(0)
+            arm.close()
+            line['cpu_baseline'] = {'value': len(w['footprints']) / est_all, 'unit': 'candidate-solves/s', 'cores': cores,
+                                    'blas_threads_per_process': arm.blas_threads, 'kind': 'port',
+                                    'sample': arm.describe() + f' ({wall:.1f} s wall, {cpu_s:.1f} core-s)',
                                     'note': 'numpy/scipy port of dsm.Energy + restated cvxopt cp (oracle/); cvxopt and MKL are unavailable on this box'}
         print(json.dumps(line))
     if world > 1:

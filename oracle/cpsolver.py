@@ -33,6 +33,15 @@ REFINEMENT = 1
 
 RANK_ERROR = 'Rank(A) < p or Rank([H(x); A; Df(x); G]) < n'
 
+# Policy for a factorisation failure while a saved line-search state exists.  cvxopt restores the saved state only for
+# 0 < relaxed_iters < MAX_RELAXED_ITERS and gives up ('unknown') when the failure happens right after the last relaxed
+# step (relaxed_iters == MAX_RELAXED_ITERS).  Whether the factorisation of such a matrix fails at all is decided by the
+# last bits of a numerically singular z * Hess f far away from the optimum (LAPACK, CHOLMOD, numpy and the CUDA solver
+# disagree there), and when it happens to succeed cp restores the saved state one step later anyway (newphi >= phi0).
+# With 'saved' (the policy the CUDA solver implements) the saved state is restored in both cases, so
+# that the outcome no longer depends on those bits; 'cvxopt' is the strict restatement.
+RESTORE_POLICY = 'saved'
+
 
 class _State(object):
     __slots__ = ('x', 't', 's', 'z', 'd', 'lmbda', 'rx_x', 'rx_t', 'rznl', 'dx', 'dt', 'dz', 'ds')
@@ -64,7 +73,7 @@ def _symv_lower(H, u):
     return Hl @ u + np.tril(Hl, -1).T @ u
 
 
-def cp(F, FH, x0, trace=None, maxiters=MAXITERS):
+def cp(F, FH, x0, trace=None, maxiters=MAXITERS, restore_policy=None, events=None):
     """Minimise f.
 
     :param F: ``F(x) -> (f, g)``, value and gradient (1-D array) of f at x.
@@ -74,9 +83,14 @@ def cp(F, FH, x0, trace=None, maxiters=MAXITERS):
     :param x0: start point.
     :param trace: optional list; one dict per iteration is appended (used by the tests to compare
         the CUDA solver's iterates).
+    :param restore_policy: ``'saved'`` or ``'cvxopt'`` (see ``RESTORE_POLICY`` above); default: the module's policy.
+    :param events: optional list; ``('chol_fail', iteration, relaxed_iters)`` is appended for every failed factorisation.
     :return: dict with the keys the reference reads (``objects.py:300,329,397-399``).
     :raises ValueError: with cvxopt's rank message if the first factorisation fails.
     """
+    if restore_policy is None: restore_policy = RESTORE_POLICY
+    assert restore_policy in ('saved', 'cvxopt')
+    restore_upto = MAX_RELAXED_ITERS + 1 if restore_policy == 'saved' else MAX_RELAXED_ITERS
     x = np.array(x0, dtype=float).reshape(-1).copy()
     t = 0.0
     s = 1.0
@@ -149,9 +163,10 @@ def cp(F, FH, x0, trace=None, maxiters=MAXITERS):
             L = _chol_lower(H)
         except ArithmeticError:
             singular_kkt_matrix = False
+            if events is not None: events.append(('chol_fail', iters, relaxed_iters))
             if iters == 0:
                 raise ValueError(RANK_ERROR)
-            elif 0 < relaxed_iters < MAX_RELAXED_ITERS > 0:
+            elif 0 < relaxed_iters < restore_upto:
                 # Restart a standard line search from the last saved state.
                 phi, gap = phi0, gap0
                 d, lmbda = saved.d, saved.lmbda

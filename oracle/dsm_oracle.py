@@ -261,14 +261,14 @@ class CvxprogError(Exception):
     pass
 
 
-def _solve(J, x0, scale, trace=None):
+def _solve(J, x0, scale, trace=None, events=None, restore_policy=None):
     """dsm.CP(...).solve(): cvxopt.solvers.cp on scale * J  (dsm.py:446-490)."""
     def F(x):
         return scale * J(x), scale * J.grad(x)
 
     def FH(x, z):
         return scale * J(x), scale * J.grad(x), z * scale * J.hessian(x)
-    return cpsolver.cp(F, FH, x0, trace=trace)
+    return cpsolver.cp(F, FH, x0, trace=trace, events=events, restore_policy=restore_policy)
 
 
 def estimate_initialization(model, mask):
@@ -326,14 +326,18 @@ def cvxprog(model, mask, scale, epsilon, alpha, smooth_amount, smooth_subsample,
             params = np.zeros(6)
         params = np.concatenate([params, np.zeros(G.shape[1])])
     try:
-        sol = _solve(J, params, scale_cp)
+        trace = [] if info is not None else None
+        events = [] if info is not None else None
+        if info is not None: info['dsm_trace'], info['dsm_events'], info['init'] = trace, events, np.asarray(params, dtype=float).copy()
+        sol = _solve(J, params, scale_cp, trace=trace, events=events, restore_policy=unused.get('restore_policy'))
         solution = sol['x']
         if info is not None: info['dsm'] = (sol['status'], sol['iterations'])
         if sol['status'] == 'unknown' and J(solution) > J(params):
             status = 'fallback'
         else:
             status = 'optimal'
-    except Exception:
+    except Exception as err:
+        if info is not None: info['dsm_error'] = f'{type(err).__name__}: {err}'
         status = 'fallback'
     if status == 'fallback': solution = params
     return J, np.asarray(solution, dtype=float).reshape(-1), status

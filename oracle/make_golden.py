@@ -17,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 from oracle import ref_harness                     # noqa: E402
-from superdsm_b200 import synth                    # noqa: E402
+from workloads import synth                    # noqa: E402
 
 OUT = os.path.join(ROOT, 'tests', 'golden')
 

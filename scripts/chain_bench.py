@@ -1,7 +1,7 @@
 """Link latency of single candidates: solves chosen candidates of the bench workload one at a time (nothing else on the GPU)."""
 import sys, time
 import numpy as np
-from superdsm_b200 import synth
+from workloads import synth
 from superdsm_b200.objects import get_engine
 
 ids = [int(v) for v in sys.argv[1].split(',')] if len(sys.argv) > 1 else [202, 70, 31, 75, 550]

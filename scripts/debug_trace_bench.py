@@ -4,7 +4,7 @@ import numpy as np
 import scipy.sparse
 sys.path.insert(0, '.')
 from oracle import dsm_oracle as orc
-from superdsm_b200 import synth
+from workloads import synth
 from superdsm_b200.objects import get_engine
 
 k = int(sys.argv[1])

@@ -2,7 +2,7 @@
 import sys
 sys.path.insert(0, ".")
 import numpy as np
-from superdsm_b200 import synth
+from workloads import synth
 from superdsm_b200.objects import get_engine
 
 name = sys.argv[1] if len(sys.argv) > 1 else 'gowt1'

@@ -14,7 +14,7 @@ _w = None
 
 def _init():
     global _w
-    from superdsm_b200 import synth
+    from workloads import synth
     os.environ['OMP_NUM_THREADS'] = '1'
     _w = synth.make_workload(name, oversegment=3, max_set_size=4, seed=1)
 
@@ -29,7 +29,8 @@ def _fit(k):
 
 
 if __name__ == '__main__':
-    from superdsm_b200 import synth, _lib
+    from superdsm_b200 import _lib
+    from workloads import synth
     from superdsm_b200.objects import get_engine
     w = synth.make_workload(name, oversegment=3, max_set_size=4, seed=1)
     eng = get_engine(0)

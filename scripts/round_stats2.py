@@ -2,7 +2,7 @@
 import sys, time
 import numpy as np
 sys.path.insert(0, '.')
-from superdsm_b200 import synth
+from workloads import synth
 from superdsm_b200.objects import get_engine
 
 w = synth.make_workload('gowt1', oversegment=3, max_set_size=4, seed=1)

@@ -2,7 +2,7 @@
 import sys
 import numpy as np
 sys.path.insert(0, '.')
-from superdsm_b200 import synth
+from workloads import synth
 from superdsm_b200.objects import get_engine
 path = sys.argv[1]
 w = synth.make_workload('gowt1', oversegment=3, max_set_size=4, seed=1)

@@ -2,7 +2,8 @@
 import sys, time
 import numpy as np
 sys.path.insert(0, '.')
-from superdsm_b200 import synth, _lib
+from superdsm_b200 import _lib
+    from workloads import synth
 from superdsm_b200.objects import get_engine
 side = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 n = int(20000 * (side / 4096) ** 2)

@@ -6,7 +6,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, 'libsuperdsm_b200.so')
+LIB_PATH = os.environ.get('SDSM_LIB') or os.path.join(HERE, 'libsuperdsm_b200.so')      # SDSM_LIB: A/B builds (scripts/)
 
 SDSM_OK = 0
 ST_OPTIMAL, ST_FALLBACK, ST_SKIPPED, ST_ERROR, ST_BADREGION = range(5)

@@ -19,16 +19,25 @@ constexpr int SOLVE_BLOCK = 256;  // k_solve: persistent CTAs, every task is exe
 constexpr int EVAL_BLOCK = SOLVE_BLOCK;   // evaluation task: one warp per pixel cell
 constexpr int EVAL_WARPS = EVAL_BLOCK / 32;
 constexpr int EVAL_CELLS = 32;    // most non-empty pixel cells per evaluation task: the CTA's warps take them one by one
-// per-warp shared memory of the evaluation tasks (doubles): the value + gradient pass stages the pixel data of STAGES
-// chunks of 32 pixels there with cp.async (STAGE_BYTES each: G~ rows [32][28] f32, y [32] f64, rc [32] u32); the Hessian pass
-// reuses the space for its tile T[32][TILE_LD] + dd[32]; then xi[32].
+// per-warp shared memory of the evaluation items: STAGES staging buffers, each one chunk of 32 pixels brought in by three 1-D
+// TMA bulk copies (cp.async.bulk, mbarrier-tracked): the pixels' rows of the G~ panel [32][stride], y [32 (+2)], row|col
+// [32 (+4)]; the Hessian pass reuses the space for its tile T[32][TILE_LD] + dd[32].  Then xi[32] (the xi values the cell
+// sees) and u[32] (-y theta of the chunk's pixels, handed from the pixel lanes to the slot lanes).
 constexpr int SLOTJ_INTS = 64;    // per-warp shared memory of the evaluation items (ints): grid index of the cell's active slots [32], slot of each active entry [32]
 constexpr int STAGES = 3;
-constexpr int STAGE_BYTES = GROW * 32 * 4 + 32 * 8 + 32 * 4;    // 3968: G~ rows [lane][28], y [lane], rc [lane]
-constexpr int WARP_AREA_DOUBLES = STAGES * STAGE_BYTES / 8;      // 1344 >= 32 * TILE_LD + 32
+constexpr int STAGE_G_BYTES = GROW * 32 * 4;                  // 3584
+constexpr int STAGE_Y_BYTES = 34 * 8;                         // 272: the copy starts at an even pixel index (16-byte alignment)
+constexpr int STAGE_RC_BYTES = 36 * 4;                        // 144: ... at a pixel index that is a multiple of four
+constexpr int STAGE_BYTES = STAGE_G_BYTES + STAGE_Y_BYTES + STAGE_RC_BYTES;    // 4000
+static_assert(STAGE_BYTES % 16 == 0 && STAGE_G_BYTES % 16 == 0 && (STAGE_G_BYTES + STAGE_Y_BYTES) % 16 == 0, "TMA destinations are 16-byte aligned");
+constexpr int WARP_AREA_DOUBLES = STAGES * STAGE_BYTES / 8;      // 1500 >= 32 * TILE_LD + 32
 static_assert(WARP_AREA_DOUBLES >= 32 * TILE_LD + 32, "the Hessian tile must fit the staging area");
 constexpr int XI_OFF = WARP_AREA_DOUBLES;
-constexpr int TILE_DOUBLES = WARP_AREA_DOUBLES + 32;
+constexpr int U_OFF = WARP_AREA_DOUBLES + 32;
+constexpr int TILE_DOUBLES = WARP_AREA_DOUBLES + 64;
+// row stride (floats) of a cell's block of the G~ panel with `na` active slots: a multiple of 4 (16-byte groups) that is
+// = 4 mod 8, so that the 16-byte reads of 8 consecutive rows fall into 8 different bank groups
+__host__ __device__ __forceinline__ int grow_stride(int na) { return na <= 4 ? 4 : (na <= 12 ? 12 : (na <= 20 ? 20 : GROW)); }
 constexpr int CTRL_BLOCK = SOLVE_BLOCK;   // control task: one CTA advances one candidate's state machine
 constexpr int CTRL_WARPS = CTRL_BLOCK / 32;
 constexpr int SMEM_L_CAP = 5504;  // doubles of shared memory for the packed Cholesky factor (N <= 104)

@@ -868,7 +868,12 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             hres_alt = false;
             if (ok) { S.pc = PC_KKT; break; }
             if (S.iters == 0) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }                 // ValueError("Rank(A) < p or ...")
-            if (0 < S.relaxed && S.relaxed < MAX_RELAXED) {
+            // cvxopt restores the saved state for 0 < relaxed < MAX_RELAXED only and gives up ('unknown') when the factorisation
+            // fails right after the last relaxed step.  Whether a numerically singular z * Hess f "fails" there is decided by
+            // the last bits of the factorisation (LAPACK / CHOLMOD / numpy / this one all differ), and when it happens to
+            // succeed cp restores the saved state one step later anyway; so the saved state is restored in both cases
+            // (oracle/cpsolver.py RESTORE_POLICY = 'saved').
+            if (0 < S.relaxed && S.relaxed <= MAX_RELAXED) {
                 // Restart a standard line search from the last saved state.  cvxopt re-evaluates F at the restored
                 // point inside the KKT solver only: cpl's residual closures keep the Df and H of the abandoned point.
                 S.phi = S.phi0s; S.gap = S.gap0s;
@@ -1227,7 +1232,7 @@ k_finish(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS w
                     const double X1 = (double)(cd.r0 + br + 1), X2 = (double)(cd.c0 + bc + 1);
                     double S = (X1 * M11 + X2 * M12) * X1 + (X1 * M12 + X2 * M22) * X2 + 2 * (X1 * mb1 + X2 * mb2) + mc;
                     double sxi = 0;
-                    for (int a = 0; a < na; ++a) sxi += (double)gcell[(size_t)p * ((na + 3) & ~3) + a] * x[6 + slotj[a]];
+                    for (int a = 0; a < na; ++a) sxi += (double)gcell[(size_t)p * grow_stride(na) + a] * x[6 + slotj[a]];
                     S += sxi;
                     if (S > 0) {
                         fg[(size_t)br * cd.w + bc] = 1;
@@ -1294,7 +1299,7 @@ __global__ void k_export(Par par, const sdsm_cand* __restrict__ cands, int c, WS
                 if (a < na) {
                     const int s = nth_set_bit(am, a);
                     col = ws.cellmap[cd.cell_off + (ca + s / 5 - NC) * ci.cw + (cb + s % 5 - NC)];
-                    v = gv[(size_t)GROW * st + (size_t)p * ((na + 3) & ~3) + a];
+                    v = gv[(size_t)GROW * st + (size_t)p * grow_stride(na) + a];
                 }
                 cols[(size_t)(st + p) * NSLOT + a] = col;
                 vals[(size_t)(st + p) * NSLOT + a] = v;

@@ -54,6 +54,31 @@ __device__ __forceinline__ void warp_sum_transposed_step(double (&v)[32], int la
     if constexpr (O > 1) warp_sum_transposed_step<O / 2>(v, lane);
 }
 
+template <int O>
+__device__ __forceinline__ void warp_sum_transposed_step8(double (&v)[8], int lane)
+{
+    const bool up = (lane & O) != 0;
+#pragma unroll
+    for (int k = 0; k < O; ++k) {
+        const double send = up ? v[k] : v[k + O];
+        const double recv = __shfl_xor_sync(0xffffffffu, send, O);
+        v[k] = (up ? v[k + O] : v[k]) + recv;
+    }
+    if constexpr (O > 1) warp_sum_transposed_step8<O / 2>(v, lane);
+}
+
+// Sum over the warp of 8 per-lane values at once (the 6 theta-gradient entries and the value): on return every lane l holds
+// the warp total of v[l & 7].  9 shuffles instead of 40; fixed order.
+__device__ __forceinline__ double warp_sum8(double (&v)[8])
+{
+    const int lane = threadIdx.x & 31;
+    warp_sum_transposed_step8<4>(v, lane);
+    double r = v[0];
+    r += __shfl_xor_sync(0xffffffffu, r, 8);
+    r += __shfl_xor_sync(0xffffffffu, r, 16);
+    return r;
+}
+
 __device__ __forceinline__ double warp_sum_transposed(double (&v)[32])
 {
     warp_sum_transposed_step<16>(v, threadIdx.x & 31);
@@ -86,16 +111,20 @@ __device__ __forceinline__ double cell_S(const double (&th)[6], double x1, doubl
 // polynomial-only model (6 parameters): each lane keeps its pixels' sums in registers, one warp reduction per cell.
 // scrG[0..5] = gradient, scrG[31] = value, scrH[0..20] = packed lower triangle of the 6 x 6 block.
 
-template <bool HESS>
-__device__ __noinline__ void eval_cell_poly(const double* __restrict__ py, const uint32_t* __restrict__ prc, int npix,
-                                               const double* __restrict__ xr, const double* __restrict__ xc, const double* x,
-                                               double tol, double* sg, double* sh)
+// Value, gradient and Hessian of the polynomial model over one cell (evaluations WITH Hessian; those without go through
+// cell_value_grad with no slots).  Value and gradient are accumulated and reduced exactly as cell_value_grad does it --
+// same per-lane order (pixels lane, lane + 32, ...), same warp_sum8 -- so that the two agree bit for bit.
+__device__ __noinline__ void eval_cell_poly_h(const double* __restrict__ py, const uint32_t* __restrict__ prc, int npix,
+                                                 const double* __restrict__ xr, const double* __restrict__ xc, const double* x,
+                                                 double tol, double* sg, double* sh)
 {
     const int lane = threadIdx.x & 31;
     const double th[6] = {x[0], x[1], x[2], x[3], x[4], x[5]};
-    double acc[32];
+    double acc[8], hs[24];
 #pragma unroll
-    for (int k = 0; k < 32; ++k) acc[k] = 0;
+    for (int k = 0; k < 8; ++k) acc[k] = 0;
+#pragma unroll
+    for (int k = 0; k < 24; ++k) hs[k] = 0;
     for (int i = lane; i < npix; i += 32) {
         const uint32_t rc = prc[i];
         const double x1 = xr[rc & 0xffffu], x2 = xc[rc >> 16], y = py[i];
@@ -104,24 +133,31 @@ __device__ __noinline__ void eval_cell_poly(const double* __restrict__ py, const
         logistic(y, S, phi, theta);
         const double u = -y * theta;
         const double q[6] = {x1 * x1, x2 * x2, 2 * (x1 * x2), 2 * x1, 2 * x2, 1.0};
-        acc[31] += phi;
+        acc[6] += phi;
 #pragma unroll
-        for (int k = 0; k < 6; ++k) acc[k] = fma(u, q[k], acc[k]);
-        if (HESS) {
-            double kappa = theta - theta * theta;
-            if (kappa < tol) kappa = 0;
-            const double dd = kappa * y * y;
+        for (int k = 0; k < 5; ++k) acc[k] = fma(u, q[k], acc[k]);
+        acc[5] += u;
+        double kappa = theta - theta * theta;
+        if (kappa < tol) kappa = 0;
+        const double dd = kappa * y * y;
 #pragma unroll
-            for (int a = 0; a < 6; ++a) {
-                const double da = dd * q[a];
+        for (int a = 0; a < 6; ++a) {
+            const double da = dd * q[a];
 #pragma unroll
-                for (int b = 0; b <= a; ++b) acc[6 + a * (a + 1) / 2 + b] = fma(da, q[b], acc[6 + a * (a + 1) / 2 + b]);
-            }
+            for (int b = 0; b <= a; ++b) hs[a * (a + 1) / 2 + b] = fma(da, q[b], hs[a * (a + 1) / 2 + b]);
         }
     }
-    const double tot = warp_sum_transposed(acc);     // lane: 0..5 gradient, 6..26 Hessian, 31 value
-    if (lane < 6 || lane == 31) sg[lane] = tot;
-    if (HESS && lane >= 6 && lane < 27) sh[lane - 6] = tot;
+    const double tot = warp_sum8(acc);                // lane: 0..5 gradient, 6 value
+    if (lane < 6) sg[lane] = tot;
+    if (lane == 6) sg[31] = tot;
+#pragma unroll
+    for (int g = 0; g < 3; ++g) {
+        double v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = hs[8 * g + k];
+        const double t = warp_sum8(v);
+        if (lane < 8 && 8 * g + lane < 21) sh[8 * g + lane] = t;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -135,119 +171,204 @@ __device__ __noinline__ void eval_cell_poly(const double* __restrict__ py, const
 // cell_hessian: the local Hessian  sum_p dd_p row_p row_p^T: the lanes stage their rows in a shared-memory tile
 // T[parameter][pixel] and the warp multiplies the 8 x 8 output tiles of the lower triangle on the FP64 tensor cores.
 
-// cp.async (LDGSTS): 4 / 8 bytes global -> shared without passing through registers
-__device__ __forceinline__ void cp_async4(void* smem, const void* gmem)
+// ---- 1-D TMA bulk copies (cp.async.bulk, SASS: UBLKCP) tracked by mbarriers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(void* bar, uint32_t count)
 {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
-__device__ __forceinline__ void cp_async8(void* smem, const void* gmem)
+__device__ __forceinline__ void mbar_expect_tx(void* bar, uint32_t bytes)
 {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, void* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void* bar, uint32_t parity)
+{
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done, polls = 0;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (!done && ++polls > (1u << 24)) __trap();      // a copy that never arrives must not hang the device
+    } while (!done);
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem)
+// Every warp owns STAGES mbarriers and the word with their phase bits, behind the SLOTJ_INTS ints of its slot tables
+// (static shared memory: it survives whatever the dynamic shared memory is used for between two items).
+constexpr int SYNC_INTS = 8;      // 3 x 8-byte mbarriers + phase bits + pad
+constexpr int WARP_INTS = SLOTJ_INTS + SYNC_INTS;
+__device__ __forceinline__ void eval_sync_init(int* s_slotj /* [EVAL_WARPS * WARP_INTS], 16-byte aligned */)
 {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
-}
-
-// a shared-memory load the compiler may not merge with an earlier load of the same address
-__device__ __forceinline__ float4 lds128_again(const float4* p)
-{
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"((uint32_t)__cvta_generic_to_shared(p)));
-    return v;
-}
-
-// Stages chunk k (32 pixels from p0 = 32 k) of the cell into shared memory: every lane copies its own pixel's y, rc and the
-// first na4 entries of its row of G~ in 16-byte pieces (a lane only ever reads back what it copied itself, so no warp
-// synchronisation is needed; rows are GROW = 28 floats apart in shared memory too, which makes both the 16-byte copies
-// and the 16-byte reads conflict-free).  Lanes beyond the cell's last pixel copy the chunk's first pixel: finite data
-// that the caller masks out.
-__device__ __noinline__ void stage_chunk(char* stage, const double* __restrict__ py, const uint32_t* __restrict__ prc,
-                                            const float* __restrict__ gcell, int npix, int na, int p0, int lane)
-{
-    const int p = (p0 + lane < npix) ? p0 + lane : p0;
-    float* G = reinterpret_cast<float*>(stage);
-    double* Y = reinterpret_cast<double*>(stage + GROW * 32 * 4);
-    uint32_t* RC = reinterpret_cast<uint32_t*>(stage + GROW * 32 * 4 + 32 * 8);
-    cp_async8(Y + lane, py + p);
-    cp_async4(RC + lane, prc + p);
-    const float* gp = gcell + (size_t)p * ((na + 3) & ~3);      // rows of the cell's block: na4 floats each
-    float* gs = G + lane * GROW;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int* w = s_slotj + warp * WARP_INTS + SLOTJ_INTS;
+    if (lane == 0) {
 #pragma unroll
-    for (int a = 0; a < GROW; a += 4)
-        if (a < na) cp_async16(gs + a, gp + a);          // warp-uniform
+        for (int k = 0; k < STAGES; ++k) mbar_init(w + 2 * k, 1);
+        w[2 * STAGES] = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        fence_proxy_async();
+    }
+    __syncthreads();
 }
 
-// Returns, in lane e, the cell's local gradient entry e (e < 6 + na), and in lane 31 its value.
-__device__ __noinline__ double cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
-                                               int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
-                                               const double* x, double tol, char* stages, const double* XI)
+// true in exactly one lane of the (converged) warp
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
+// Phase 2 of cell_value_grad for a panel whose rows are GS floats apart (a compile-time stride: every shared-memory read has
+// an immediate offset).  Lane = active slot: g[p & 3] += u[p] * G~[p][slot] over the chunk's pixels, in this order.
+template <int GS>
+__device__ __forceinline__ void grad_phase2(const float* __restrict__ Gs, const double* __restrict__ U, int cnt,
+                                            double& g0, double& g1, double& g2, double& g3)
+{
+    const double2* U2 = reinterpret_cast<const double2*>(U);
+#ifndef SDSM_P2_UNROLL
+#define SDSM_P2_UNROLL 8          // full unrolling (32) is 6 % faster in the stand-alone sweep and 2 % slower in the solver (code size)
+#endif
+    if (cnt == 32) {
+#pragma unroll 1
+        for (int q = 0; q < 32; q += SDSM_P2_UNROLL) {
+            const float* Gq = Gs + q * GS;
+            const double2* Uq = U2 + (q >> 1);
+#pragma unroll
+            for (int p = 0; p < SDSM_P2_UNROLL; p += 4) {
+                const float f0 = Gq[p * GS], f1 = Gq[(p + 1) * GS], f2 = Gq[(p + 2) * GS], f3 = Gq[(p + 3) * GS];
+                const double2 ua = Uq[p >> 1], ub = Uq[(p >> 1) + 1];
+                g0 = fma(ua.x, (double)f0, g0); g1 = fma(ua.y, (double)f1, g1);
+                g2 = fma(ub.x, (double)f2, g2); g3 = fma(ub.y, (double)f3, g3);
+            }
+        }
+        return;
+    }
+    int p = 0;
+    for (; p + 4 <= cnt; p += 4) {
+        const float f0 = Gs[p * GS], f1 = Gs[(p + 1) * GS], f2 = Gs[(p + 2) * GS], f3 = Gs[(p + 3) * GS];
+        const double2 ua = U2[p >> 1], ub = U2[(p >> 1) + 1];
+        g0 = fma(ua.x, (double)f0, g0); g1 = fma(ua.y, (double)f1, g1);
+        g2 = fma(ub.x, (double)f2, g2); g3 = fma(ub.y, (double)f3, g3);
+    }
+    if (p < cnt) g0 = fma(U[p], (double)Gs[p * GS], g0);
+    if (p + 1 < cnt) g1 = fma(U[p + 1], (double)Gs[(p + 1) * GS], g1);
+    if (p + 2 < cnt) g2 = fma(U[p + 2], (double)Gs[(p + 2) * GS], g2);
+}
+
+// one lane: brings chunk k (pixels 32 k .. of the cell) into `stage`: G~ rows, y, row|col.  py / prc point at the cell's first
+// pixel; a TMA source must be 16-byte aligned, so the y copy starts ay = 0/1 and the row|col copy arc = 0..3 pixels early
+// (and both are rounded up to 16 bytes: the arrays are padded to multiples of 32 pixels per candidate).
+__device__ __forceinline__ void stage_issue(char* stage, void* bar, const double* __restrict__ py, const uint32_t* __restrict__ prc,
+                                            const float* __restrict__ gcell, int npix, int gstride, int ay, int arc, int k)
+{
+    const int p0 = 32 * k, cnt = min(32, npix - p0);
+    const uint32_t by = (uint32_t)((cnt + ay + 1) & ~1) * 8u, brc = (uint32_t)((cnt + arc + 3) & ~3) * 4u;
+    const uint32_t bg = (uint32_t)(cnt * gstride) * 4u;               // gstride = 0: polynomial model, no panel
+    mbar_expect_tx(bar, by + brc + bg);
+    tma_bulk_g2s(stage + STAGE_G_BYTES, py + p0 - ay, by, bar);
+    tma_bulk_g2s(stage + STAGE_G_BYTES + STAGE_Y_BYTES, prc + p0 - arc, brc, bar);
+    if (bg) tma_bulk_g2s(stage, gcell + (size_t)p0 * gstride, bg, bar);
+}
+
+// Value and gradient of one cell.  Two phases per chunk of 32 pixels:
+//   (1) lane = pixel: S = polynomial + sum_a G~[p][a] xi[a], logistic loss -> phi, theta; the value and the six theta-gradient
+//       entries accumulate in registers (7 per lane); u = -y theta goes to shared memory;
+//   (2) lane = active slot a: xi-gradient entry a += sum_p u[p] G~[p][a], straight from the staged panel (one float per pixel:
+//       consecutive lanes read consecutive words), four independent partial sums in a fixed order.
+// So a lane never carries 32 accumulators (the 128-register budget of two resident CTAs is left to the logistic function's
+// two FMA chains), and no transposed 32-value reduction ends the cell.  Both kinds of evaluation (with / without Hessian)
+// call this one function, and every multiply-add in it is an explicit fma (no context-dependent contraction): the line
+// searches of cp compare merit values of evaluations with and without Hessian at the same point and rely on equal bits.
+// Returns (.x) in lane e < 6 the theta-gradient entry e and in lane 6 the value (lanes 8.. repeat them), (.y) in lane
+// a < na the xi-gradient entry of the cell's a-th active slot.
+__device__ __noinline__ double2 cell_value_grad(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
+                                                int npix, int na, const double* __restrict__ xr, const double* __restrict__ xc,
+                                                const double* x, double tol, char* stages, double* XI, int* sync)
 {
     const int lane = threadIdx.x & 31;
     const double th[6] = {x[0], x[1], x[2], x[3], x[4], x[5]};
-    double acc[32];                                   // acc[e] = local gradient entry e, acc[31] = value
+    double acc[8];                                    // 0..5 theta gradient, 6 value
 #pragma unroll
-    for (int k = 0; k < 32; ++k) acc[k] = 0;
+    for (int k = 0; k < 8; ++k) acc[k] = 0;
+    double g0 = 0, g1 = 0, g2 = 0, g3 = 0;            // xi-gradient entry of slot `lane`: partial sums over the pixels p = 0, 1, 2, 3 mod 4
+    double* U = XI + 32;
     const int nchunks = (npix + 31) >> 5;
-    // software pipeline: chunk k + STAGES - 1 is in flight while chunk k is evaluated
+    const int gstride = na > 0 ? grow_stride(na) : 0;
+    const int ay = (int)((reinterpret_cast<uintptr_t>(py) >> 3) & 1u), arc = (int)((reinterpret_cast<uintptr_t>(prc) >> 2) & 3u);
+    uint32_t phase = (uint32_t)sync[2 * STAGES];
+    __syncwarp();
+    if (elect_one()) {
+        fence_proxy_async();                          // the staging area may have been written with ordinary stores (Hessian tile)
 #pragma unroll
-    for (int k = 0; k < STAGES - 1; ++k) {
-        if (k < nchunks) stage_chunk(stages + k * STAGE_BYTES, py, prc, gcell, npix, na, 32 * k, lane);
-        cp_async_commit();
+        for (int k = 0; k < STAGES - 1; ++k)
+            if (k < nchunks) stage_issue(stages + k * STAGE_BYTES, sync + 2 * k, py, prc, gcell, npix, gstride, ay, arc, k);
     }
     int slot = 0, slot_in = STAGES - 1;
+    const int la = lane < gstride ? lane : 0;         // lanes beyond the panel's row read slot 0 (and drop the result)
     for (int k = 0; k < nchunks; ++k) {
-        if (k + STAGES - 1 < nchunks) stage_chunk(stages + slot_in * STAGE_BYTES, py, prc, gcell, npix, na, 32 * (k + STAGES - 1), lane);
-        cp_async_commit();
-        cp_async_wait<STAGES - 1>();                  // this lane's copies of chunk k have landed
+        __syncwarp();                                 // everybody is done with chunk k - 1: its buffer and U are free
+        if (k + STAGES - 1 < nchunks && elect_one())
+            stage_issue(stages + slot_in * STAGE_BYTES, sync + 2 * slot_in, py, prc, gcell, npix, gstride, ay, arc, k + STAGES - 1);
+        mbar_wait(sync + 2 * slot, (phase >> slot) & 1u);
+        phase ^= 1u << slot;
         const char* stage = stages + slot * STAGE_BYTES;
-        const float4* G4 = reinterpret_cast<const float4*>(stage) + lane * (GROW / 4);
-        const bool act = 32 * k + lane < npix;
-        const uint32_t rc = reinterpret_cast<const uint32_t*>(stage + GROW * 32 * 4 + 32 * 8)[lane];
-        const double y = act ? reinterpret_cast<const double*>(stage + GROW * 32 * 4)[lane] : 0.0;
+        const int cnt = min(32, npix - 32 * k);
+        const bool act = lane < cnt;
+        // ---- phase 1: lane = pixel ----
+        const uint32_t rc = act ? reinterpret_cast<const uint32_t*>(stage + STAGE_G_BYTES + STAGE_Y_BYTES)[arc + lane] : 0u;
+        const double y = act ? reinterpret_cast<const double*>(stage + STAGE_G_BYTES)[ay + lane] : 0.0;
+        // (tried: the cell's rows / columns of the coordinate tables in shared memory -- the sweep gained 5 %, the solver lost
+        //  4 %: one more dependent global load in front of every cell)
         const double x1 = xr[rc & 0xffffu], x2 = xc[rc >> 16];
         double S = cell_S(th, x1, x2);
-        double sx0 = 0, sx1 = 0, sx2 = 0, sx3 = 0;        // XI is zero beyond the cell's last active slot, and so is the row
+        if (na > 0) {                                 // (warp-uniform)
+            const float4* G4 = reinterpret_cast<const float4*>(stage) + lane * (gstride >> 2);
+            double sx0 = 0, sx1 = 0, sx2 = 0, sx3 = 0;    // XI is zero beyond the cell's last active slot, and so is the row
 #pragma unroll
-        for (int j = 0; j < GROW / 4; ++j) {
-            if (4 * j < na) {                             // (warp-uniform)
-                const float4 g = G4[j];
-                const double2 xa = reinterpret_cast<const double2*>(XI)[2 * j], xb = reinterpret_cast<const double2*>(XI)[2 * j + 1];
-                sx0 = fma((double)g.x, xa.x, sx0); sx1 = fma((double)g.y, xa.y, sx1);
-                sx2 = fma((double)g.z, xb.x, sx2); sx3 = fma((double)g.w, xb.y, sx3);
+            for (int j = 0; j < GROW / 4; ++j) {
+                if (4 * j < na) {                         // (warp-uniform)
+                    const float4 g = G4[j];
+                    const double2 xa = reinterpret_cast<const double2*>(XI)[2 * j], xb = reinterpret_cast<const double2*>(XI)[2 * j + 1];
+                    sx0 = fma((double)g.x, xa.x, sx0); sx1 = fma((double)g.y, xa.y, sx1);
+                    sx2 = fma((double)g.z, xb.x, sx2); sx3 = fma((double)g.w, xb.y, sx3);
+                }
             }
+            S += (sx0 + sx1) + (sx2 + sx3);
         }
-        S += (sx0 + sx1) + (sx2 + sx3);
         double phi = 0, theta = 0;
-        if (act) logistic(y, S, phi, theta);
-        const double u = -y * theta;                  // 0 for the lanes beyond the cell's last pixel (y = 0)
-        const double q[6] = {x1 * x1, x2 * x2, 2 * (x1 * x2), 2 * x1, 2 * x2, 1.0};
-        acc[31] += phi;
+        if (act) logistic(y, S, phi, theta);          // lanes beyond the cell's last pixel: S may be garbage, never used
+        const double u = -y * theta;                  // 0 for those lanes (y = 0)
+        const double q[5] = {x1 * x1, x2 * x2, 2 * (x1 * x2), 2 * x1, 2 * x2};
+        acc[6] += phi;
 #pragma unroll
-        for (int e = 0; e < 6; ++e) acc[e] = fma(u, q[e], acc[e]);
-        // the xi part of the gradient drops |u| < sparsity_tol (dsm.py:346); the theta part does not
-        const double ux = (tol > 0 && fabs(u) < tol) ? 0.0 : u;
-        // the row of G~ is read from shared memory a second time instead of living in 25 registers across the logistic
-        // function: with the 32 accumulators that would not fit the 128 registers two resident CTAs per SM allow
-#pragma unroll
-        for (int j = 0; j < GROW / 4; ++j) {
-            if (4 * j < na) {                             // (warp-uniform) nothing is issued for the slots beyond the cell's last one
-                const float4 g = lds128_again(G4 + j);
-                acc[6 + 4 * j] = fma(ux, (double)g.x, acc[6 + 4 * j]);
-                if (4 * j + 1 < NSLOT) acc[7 + 4 * j] = fma(ux, (double)g.y, acc[7 + 4 * j]);
-                if (4 * j + 2 < NSLOT) acc[8 + 4 * j] = fma(ux, (double)g.z, acc[8 + 4 * j]);
-                if (4 * j + 3 < NSLOT) acc[9 + 4 * j] = fma(ux, (double)g.w, acc[9 + 4 * j]);
-            }
+        for (int e = 0; e < 5; ++e) acc[e] = fma(u, q[e], acc[e]);
+        acc[5] += u;
+        if (na > 0) {
+            // the xi part of the gradient drops |u| < sparsity_tol (dsm.py:346); the theta part does not
+            U[lane] = (tol > 0 && fabs(u) < tol) ? 0.0 : u;
+            __syncwarp();
+            // ---- phase 2: lane = active slot ----
+            const float* Gs = reinterpret_cast<const float*>(stage) + la;
+            if (gstride == GROW) grad_phase2<GROW>(Gs, U, cnt, g0, g1, g2, g3);
+            else if (gstride == 20) grad_phase2<20>(Gs, U, cnt, g0, g1, g2, g3);
+            else if (gstride == 12) grad_phase2<12>(Gs, U, cnt, g0, g1, g2, g3);
+            else grad_phase2<4>(Gs, U, cnt, g0, g1, g2, g3);
         }
         slot = (slot + 1 == STAGES) ? 0 : slot + 1;
         slot_in = (slot_in + 1 == STAGES) ? 0 : slot_in + 1;
     }
-    cp_async_wait<0>();
-    return warp_sum_transposed(acc);                 // lane: local gradient entry, 31: value
+    __syncwarp();
+    if (lane == 0) sync[2 * STAGES] = (int)phase;
+    double2 r;
+    r.x = warp_sum8(acc);
+    r.y = (g0 + g1) + (g2 + g3);
+    return r;
 }
 
 __device__ __noinline__ void cell_hessian(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
@@ -278,7 +399,7 @@ __device__ __noinline__ void cell_hessian(const double* __restrict__ py, const u
         double* col = Tt + lane;
         double sx0 = 0, sx1 = 0;
         {
-            const float4* gp = reinterpret_cast<const float4*>(gcell + (size_t)(act ? p : 0) * ((na + 3) & ~3));
+            const float4* gp = reinterpret_cast<const float4*>(gcell + (size_t)(act ? p : 0) * grow_stride(na));
 #pragma unroll
             for (int j = 0; j < GROW / 4; ++j) {
                 if (4 * j < na) {                         // (warp-uniform)
@@ -338,7 +459,7 @@ __device__ __noinline__ void cell_hessian(const double* __restrict__ py, const u
 template <bool HESS>
 __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
                                              int npix, uint32_t am, const double* __restrict__ xr, const double* __restrict__ xc,
-                                             const double* x, double tol, double* Tt, const int* slotj,
+                                             const double* x, double tol, double* Tt, int* slotj,
                                              double* sg, double* xig, double* sh)
 {
     const int lane = threadIdx.x & 31;
@@ -347,15 +468,13 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
     __syncwarp();
     XI[lane] = lane < na ? x[6 + slotj[lane]] : 0.0;  // the xi values this cell sees (zero-padded: rows are read in groups of four)
     __syncwarp();
-    const double tot = cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI);
-    if (lane < 6 || lane == 31) sg[lane] = tot;
-    else if (lane < 6 + na) {
-        // xi gradient: straight into the slot that grid point slotj[a] keeps for this cell (seen from the grid point's cell,
-        // this cell sits at the mirrored neighbour position), so that the control task sums 25 contiguous numbers per
-        // grid point instead of chasing cell -> mask -> scratch entry
-        const int a = lane - 6;
-        xig[(size_t)slotj[a] * NSLOT + (NSLOT - 1 - slotj[32 + a])] = tot;
-    }
+    const double2 tot = cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI, slotj + SLOTJ_INTS);
+    if (lane < 6) sg[lane] = tot.x;
+    if (lane == 6) sg[31] = tot.x;
+    // xi gradient: straight into the slot that grid point slotj[a] keeps for this cell (seen from the grid point's cell, this
+    // cell sits at the mirrored neighbour position), so that the control task sums 25 contiguous numbers per grid point
+    // instead of chasing cell -> mask -> scratch entry
+    if (lane < na) xig[(size_t)slotj[lane] * NSLOT + (NSLOT - 1 - slotj[32 + lane])] = tot.y;
     __syncwarp();
     if (HESS) cell_hessian(py, prc, gcell, npix, na, xr, xc, x, tol, Tt, XI, sh);
     __syncwarp();
@@ -383,7 +502,7 @@ __device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __res
         if (lane == 0) i = atomicAdd(s_next, 1);
         i = __shfl_sync(0xffffffffu, i, 0);
         if (i >= count) break;
-        eval_cell(par, cands, ws, c, ci, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * SLOTJ_INTS);
+        eval_cell(par, cands, ws, c, ci, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * WARP_INTS);
     }
 }
 
@@ -404,21 +523,22 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     const double* xc = xr + h;
     double* sg = ws.scrG + (size_t)(cell_off + cell) * SCRG;
     double* sh = ws.scrH + (size_t)(cell_off + cell) * SCRH;
+    const int cw = ci.cw;
+    const int ca = cell / cw, cb = cell - ca * cw;
     if (!rq.use_xi) {
-        if (rq.want_h) eval_cell_poly<true>(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
+        if (rq.want_h) eval_cell_poly_h(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);
         else {
             // value + gradient of the polynomial model = the deformable pass without slots: same arithmetic in the same
-            // order as eval_cell_poly (the values of the two must agree bit for bit), but y and row|col arrive through
-            // the cp.async pipeline instead of dependent loads
-            const double tot = cell_value_grad(py, prc, nullptr, npix, 0, xr, xc, rq.x, par.sparsity_tol, reinterpret_cast<char*>(Tt), Tt + XI_OFF);
-            if (lane < 6 || lane == 31) sg[lane] = tot;
+            // order as eval_cell_poly_h (the values of the two must agree bit for bit), with y and row|col arriving through
+            // the TMA pipeline instead of dependent loads
+            const double2 tot = cell_value_grad(py, prc, nullptr, npix, 0, xr, xc, rq.x, par.sparsity_tol, reinterpret_cast<char*>(Tt), Tt + XI_OFF, slotj + SLOTJ_INTS);
+            if (lane < 6) sg[lane] = tot.x;
+            if (lane == 6) sg[31] = tot.x;
         }
         return;
     }
-    const int cw = ci.cw;
     const uint32_t am = ws.cell_amask[cell_off + cell];
     const int na = __popc(am);
-    const int ca = cell / cw, cb = cell - ca * cw;
     __syncwarp();
     if (lane < NSLOT && ((am >> lane) & 1u)) slotj[32 + __popc(am & ((1u << lane) - 1u))] = lane;     // slot of the cell's e-th active entry
     __syncwarp();

@@ -255,8 +255,9 @@ k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int3
         __syncthreads();
 
         // (f) G~ values per (cell, pixel, active slot) and the active-slot mask of every cell: the cell's block starts at
-        //     GROW * (first pixel) and holds one row per pixel of na4 = #active slots rounded up to a multiple of four floats
-        //     (the evaluation reads 16-byte groups), the active slots in slot order, zeros behind them
+        //     GROW * (first pixel) and holds one row per pixel of grow_stride(#active slots) floats (16-byte groups, a stride
+        //     that keeps the evaluation's 16-byte shared-memory reads free of bank conflicts), the active slots in slot
+        //     order, zeros behind them
         float* gv = ws.gval + (size_t)GROW * cd.pix_off;
         uint32_t* amask = ws.cell_amask + cd.cell_off;
         for (int cell = cell0 + warp; cell < cell1; cell += BLOCK / 32) {
@@ -280,7 +281,7 @@ k_grid_rows(Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int3
                     }
                     if (__any_sync(0xffffffffu, any)) am |= 1u << s;
                 }
-                const int na4 = (__popc(am) + 3) & ~3;       // row stride of this cell's block (floats)
+                const int na4 = grow_stride(__popc(am));     // row stride of this cell's block (floats)
                 int rank = 0;
                 for (int s = 0; s < NSLOT; ++s) {
                     if (!((am >> s) & 1u)) continue;

@@ -126,7 +126,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
 {
     constexpr int BLOCK = SOLVE_BLOCK;
     extern __shared__ __align__(16) char smem_solve[];
-    __shared__ int s_slotj[EVAL_WARPS * SLOTJ_INTS];
+    __shared__ __align__(16) int s_slotj[EVAL_WARPS * WARP_INTS];
     __shared__ uint2 s_task;
     __shared__ int s_flag, s_next;
     __shared__ unsigned long long s_base[2];
@@ -134,11 +134,12 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
     const unsigned long long n_target = (unsigned long long)args.n_target;
     const unsigned long long t_start = globaltimer_ns();
     const long long c_begin = clock64();
+    eval_sync_init(s_slotj);
 
     if ((int)blockIdx.x >= args.n_ctrl_ctas) {
         // ---- evaluation warps: independent consumers of ws.qe ----
         double* Tt = (double*)smem_solve + warp * TILE_DOUBLES;      // TILE_DOUBLES >= HG_ACC
-        int* slotj = s_slotj + warp * SLOTJ_INTS;
+        int* slotj = s_slotj + warp * WARP_INTS;
         unsigned long long cyc_idle = 0, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0}, cyc_hg = 0, n_hg = 0, cyc_fin = 0;
         unsigned n_popped = 0;
         for (;;) {
@@ -303,8 +304,9 @@ __global__ void __launch_bounds__(SOLVE_BLOCK)
 k_diag_eval_cells(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws)
 {
     extern __shared__ __align__(16) char smem_solve[];
-    __shared__ int s_slotj[EVAL_WARPS * SLOTJ_INTS];
+    __shared__ __align__(16) int s_slotj[EVAL_WARPS * WARP_INTS];
     __shared__ int s_next;
+    eval_sync_init(s_slotj);
     const int n_ne = ws.cinfo[c].n_ne;
     for (int first = blockIdx.x * EVAL_CELLS; first < n_ne; first += gridDim.x * EVAL_CELLS) {
         if (threadIdx.x == 0) s_next = 0;
@@ -416,8 +418,9 @@ __global__ void __launch_bounds__(SOLVE_BLOCK, 2)
 k_sweep(Par par, const sdsm_cand* __restrict__ cands, WS ws, int rows)
 {
     extern __shared__ __align__(16) char smem_solve[];
-    __shared__ int s_slotj[EVAL_WARPS * SLOTJ_INTS];
+    __shared__ __align__(16) int s_slotj[EVAL_WARPS * WARP_INTS];
     __shared__ int s_next;
+    eval_sync_init(s_slotj);
     const unsigned long long n_tasks = ws.counters[Q_TAIL];
     for (unsigned long long i = blockIdx.x; i < n_tasks; i += gridDim.x) {
         const uint2 task = ws.qe.task[i];

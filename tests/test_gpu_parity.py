@@ -92,7 +92,7 @@ def test_fit_results_match_reference_driver(solved):
 def test_compute_objects_api_against_oracle(eng):
     """The drop-in seam compute_objects() on the synthetic toy workload, every candidate against the oracle."""
     from oracle import dsm_oracle as orc
-    from superdsm_b200 import synth
+    from workloads import synth
     from superdsm_b200.image import Image
     from superdsm_b200.objects import Object, compute_objects
     w = synth.make_workload('toy', oversegment=2, max_set_size=3)
@@ -179,7 +179,8 @@ def test_cvxprog_seam_without_deformations(eng):
 
 def test_full_size_properties(eng):
     """BASELINE config 1 (GOWT1-shaped 1024 x 1024): size-independent properties of the solves."""
-    from superdsm_b200 import synth, _lib
+    from superdsm_b200 import _lib
+    from workloads import synth
     w = synth.make_workload('gowt1', max_set_size=2)
     eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
     eng.set_params(w['dsm_cfg'])
@@ -237,7 +238,8 @@ def test_other_baseline_configs(eng, name, kw):
     """BASELINE configs 0, 2 and 4 (BBBC039-shaped with the default configuration, NIH3T3-shaped, a crop of the 4096 x 4096
     tiled field): the whole candidate list through the C ABI; properties for all, the oracle's fit for a few."""
     from oracle import dsm_oracle as orc
-    from superdsm_b200 import synth, _lib
+    from superdsm_b200 import _lib
+    from workloads import synth
     w = synth.make_workload(name, oversegment=2, max_set_size=3, max_candidates=400, **kw)
     eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
     eng.set_params(w['dsm_cfg'])
@@ -262,7 +264,8 @@ def test_other_baseline_configs(eng, name, kw):
 def test_device_image_preparation_bit_exact(eng, name, margin):
     """sdsm_prepare_image (windowed exact EDT on the device) against the numpy/scipy statement of objects.py:126-127:
     masked atoms map, per-atom pixel counts and bounding boxes -- bit-exact."""
-    from superdsm_b200 import synth, engine
+    from superdsm_b200 import engine
+    from workloads import synth
     w = synth.make_workload(name, oversegment=2, max_set_size=1)
     ref_atoms, ref_count, ref_box = engine.prepare_image(w['y'], w['y_mask'], w['atoms'], margin)
     eng.set_image(w['y'], w['y_mask'], w['atoms'], margin)
@@ -275,7 +278,8 @@ def test_large_system_against_oracle(eng):
     """A candidate whose KKT system is larger than the shared-memory factor (6 + m > 104: blocked DMMA Cholesky in L2,
     blocked substitutions) against the oracle's fit of the same region."""
     from oracle import dsm_oracle as orc
-    from superdsm_b200 import synth, _lib
+    from superdsm_b200 import _lib
+    from workloads import synth
     w = synth.make_workload('gowt1', oversegment=3, max_set_size=4, seed=1)
     eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
     eng.set_params(w['dsm_cfg'])
