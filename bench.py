@@ -221,8 +221,8 @@ def run_gpu(args):
         dist.init_process_group('nccl', device_id=device)
 
     from superdsm_b200 import _lib
-    from superdsm_b200.image import Image
-    from superdsm_b200.objects import Object, compute_objects, get_engine, _image_cache
+    from tests.compat.refshim import Image, Object
+    from superdsm_b200.objects import compute_objects, forget_images, get_engine
     w = make_workload(rank, args)
     fps = w['footprints']
     eng = get_engine(local_rank)
@@ -258,7 +258,7 @@ def run_gpu(args):
     total_ms = float(np.sum(step_ms))
 
     # results of the last step (for the work model and a sanity check)
-    stats = eng.solver_stats(handle['ws'])
+    stats = eng.solver_stats(handle['ws'], handle['plan'])
     if stats['abort'] or stats['done'] != handle['n']:
         raise SystemExit(f'persistent solver did not finish: {stats}')
     o = handle['out']
@@ -278,13 +278,13 @@ def run_gpu(args):
         fps = [fp for fp, st in zip(fps, status) if st < _lib.ST_ERROR]
 
     # ---- end to end through the public API (`e2e`): host arrays in, Objects out ----
-    y_img = Image.create_from_array(w['y'], normalize=False, mask=w['y_mask'])
+    y_img = Image(w['y'], w['y_mask'])
 
     def e2e_step():
         objs = []
         for fp in fps:
             ob = Object(); ob.footprint = set(fp); objs.append(ob)
-        _image_cache.clear()                                                # every step uploads its image again
+        forget_images()                                                # every step uploads its image again
         compute_objects(objs, y_img, w['atoms'], w['dsm_cfg'], None)
         return objs
     e2e_step()

@@ -27,7 +27,8 @@
  *   SDSM_TASK_SMALL_CELLS (512)  candidates with at most this many cells get evaluation items of one cell (else 4)
  *   SDSM_HI_FRAC (0.02)   share of the batch (most expensive candidates first) whose tasks are urgent from the start
  *   SDSM_HI_EVALS (300)   a candidate that has needed more evaluations than this becomes urgent
- *   SDSM_TIMEOUT_S (60)   watchdog of the persistent solver kernel
+ *   SDSM_TIMEOUT_S (60)   watchdog of the persistent solver kernel: it is aborted when no control task has finished anywhere
+ *                         for this long (lack of progress, not total run time: batches may run for minutes)
  */
 #ifndef SUPERDSM_B200_H
 #define SUPERDSM_B200_H
@@ -39,7 +40,8 @@
 extern "C" {
 #endif
 
-#define SDSM_ABI_VERSION 4
+#define SDSM_ABI_VERSION 5
+#define SDSM_MAX_IMAGES  32   /* images one batch can draw its candidates from (sdsm_set_images) */
 
 /* return codes */
 #define SDSM_OK              0
@@ -68,16 +70,20 @@ typedef struct sdsm_params {
     const float* h_psf;      /* HOST pointer, (radius+1)^2 floats: psf32[|dr|][|dc|], the float32 Gaussian kernel of
                                 dsm.py:137-142,226 (quarter of the symmetric box); may be NULL if !has_smooth */
     int32_t maxiters;        /* cvxopt default 100 */
-    int32_t reserved;
+    int32_t skip_single_fg;  /* 1: a region with exactly one foreground pixel is not fitted (SDSM_ST_SKIPPED) -- the rule of
+                                _compute_object (objects.py:184-191); 0: it is fitted like any other, as cvxprog itself does
+                                (objects.py:361-412, the c2f seam) */
     double abstol, reltol, feastol;   /* cvxopt defaults 1e-7, 1e-6, 1e-7 */
 } sdsm_params;
 
-/* one candidate region.  The caller fills the first 8 fields; sdsm_plan_batch() fills the offsets. */
+/* one candidate region.  The caller fills r0 .. n and img; sdsm_plan_batch() fills the offsets. */
 typedef struct sdsm_cand {
     int32_t r0, c0, h, w;    /* bounding box (image coordinates) of the usable pixels of the footprint's atoms */
-    int32_t fp_off, fp_len;  /* footprint = footprints[fp_off : fp_off + fp_len] (atom labels) */
+    int32_t fp_off, fp_len;  /* footprint = footprints[fp_off : fp_off + fp_len] (atom labels of image `img`) */
     int32_t n;               /* number of pixels of the region (sum of the atoms' usable-pixel counts) */
     int32_t cell_cap;        /* out: upper bound of the number of pixel cells */
+    int32_t img;             /* index of the candidate's image in the set given to sdsm_set_images() (0 with sdsm_set_image) */
+    int32_t reserved;
     int64_t pix_off;         /* out: offset into the per-pixel workspace arrays */
     int64_t cell_off;        /* out: offset into the per-cell workspace arrays */
     int64_t tab_off;         /* out: offset into the per-row/column tables */
@@ -93,8 +99,12 @@ typedef struct sdsm_plan {
     int64_t fgmask_len;      /* bytes in out.fgmask */
     int32_t n_max;           /* largest 6 + cell_cap of the batch */
     int32_t cells_max;       /* largest cell_cap of the batch */
-    int32_t reserved0;
-    int32_t reserved1;
+    int32_t n_cand;          /* candidates of the batch */
+    int32_t reserved;
+    int64_t totals[6];       /* sizes of the workspace's per-pixel / per-cell / per-table / per-vector / per-matrix arrays and of the
+                                task queues: the workspace layout is a pure function of these (every call that takes a plan and a
+                                workspace derives the layout from the plan it is given, not from the context) */
+    double  solo_share;      /* share of the batch's pixels in candidates whose chains stay inside one control CTA (scheduling hint) */
 } sdsm_plan;
 
 /* device output arrays of one batch, all caller-owned */
@@ -107,6 +117,8 @@ typedef struct sdsm_out {
     int32_t* d_fgbox;        /* [n_cand*4] rmin, rmax, cmin, cmax of the foreground inside the bounding box, -1 if none */
     uint8_t* d_onboundary;   /* [n_cand]   objects.py:209 */
     uint8_t* d_fgmask;       /* [fgmask_len] (S > 0) AND omega over the candidate's bounding box (objects.py:200-204) */
+    uint64_t* d_solver;      /* [2] or NULL: candidates the persistent solver finished, and its abort flag (non-zero: the watchdog
+                                fired, results invalid) -- copied with the results, so that checking them costs no extra round trip */
 } sdsm_out;
 
 typedef struct sdsm_ctx sdsm_ctx;
@@ -119,6 +131,11 @@ const char* sdsm_last_error(const sdsm_ctx* ctx);
 /* y: float64 HxW offset image (Image.model); atoms: int32 HxW atom labels with every pixel outside
  * y_mask AND (EDT(y <= 0) <= background_margin) set to 0 (objects.py:126-127, candidate-independent part). */
 int sdsm_set_image(sdsm_ctx* ctx, const double* d_y, const int32_t* d_atoms, int32_t H, int32_t W);
+
+/* The same for a set of images (batch mode, batch.py:288-361: the candidates of several images are solved by one launch, so
+ * that the long dependency chains of one image overlap the bulk of the next).  sdsm_cand.img selects a candidate's image. */
+typedef struct sdsm_image { const double* d_y; const int32_t* d_atoms; int32_t H, W; } sdsm_image;
+int sdsm_set_images(sdsm_ctx* ctx, const sdsm_image* h_images, int32_t n_images);
 int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* params);
 
 /* Per-image preparation on the device (the candidate-independent part of Object.get_cvxprog_region, objects.py:126-127):
@@ -164,7 +181,7 @@ int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flo
 /* Diagnostics: h_us[2 * n_cand] receives, for every candidate of the last sdsm_solve_batch() on this workspace, the time (in
  * microseconds after the solver kernel started) at which its fit finished, then [n_cand ..] the time it spent in control
  * tasks (microseconds); SYNCHRONISES the stream. */
-int sdsm_finish_times(sdsm_ctx* ctx, const void* d_workspace, int32_t* h_us, void* stream);
+int sdsm_finish_times(sdsm_ctx* ctx, const sdsm_plan* plan, const void* d_workspace, int32_t* h_us, void* stream);
 
 /* Measurement aid: `repeats` sweeps of the evaluation tasks (rows = 0; value + gradient, plus the per-cell Hessians if
  * want_h) or of the Hessian-row tasks (rows = 1) over EVERY candidate of the last solved batch at its solution, outside
@@ -180,7 +197,7 @@ int64_t sdsm_launch_count(const sdsm_ctx* ctx);
  * [4..7] busy clock cycles summed over CTAs in evaluation / Hessian-row / control tasks and idle, [8..10] number of
  * evaluation / Hessian-row / control tasks, [11] CTA lifetime cycles summed over CTAs, [16..19] / [20..23] cycles / number of
  * the queued evaluation tasks by kind (polynomial model: value+gradient, +Hessian; deformable model: value+gradient, +Hessian). */
-int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_t* h_stats, void* stream);
+int sdsm_solver_stats(sdsm_ctx* ctx, const sdsm_plan* plan, const void* d_workspace, uint64_t* h_stats, void* stream);
 
 #ifdef __cplusplus
 }

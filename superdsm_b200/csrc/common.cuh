@@ -56,10 +56,11 @@ struct Queue {
 };
 
 struct Img { const double* y; const int32_t* atoms; int32_t H, W; };
+struct ImgSet { Img v[SDSM_MAX_IMAGES]; };      // passed to the kernels by value (constant bank): no device-side table to maintain
 
 struct Par {
     double alpha, epsilon, scale, sparsity_tol, abstol, reltol, feastol;
-    int32_t sub, R, has_smooth, init_elliptical, maxiters;
+    int32_t sub, R, has_smooth, init_elliptical, maxiters, skip_single_fg;
     const float* psf;   // device, (R+1)^2
 };
 
@@ -141,6 +142,7 @@ struct Layout {
 };
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+constexpr int N_GLOB_LINES = 4;   // >= N_GLOB (common.cuh, queue section): cache lines of the solver's global flags
 
 // P, C, T, V, M: totals of the per-pixel, per-cell, per-table, per-vector and per-matrix arrays of the batch
 // K = upper bound of the number of tasks that can be in flight (sdsm_plan_batch: sum over candidates of the tasks of one stage)
@@ -184,7 +186,7 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_qe_hot = take(sizeof(unsigned long long) * 8 * 16);
     L.o_pending = take(sizeof(int32_t) * (size_t)n_cand);
     L.o_prio = take(sizeof(int32_t) * (size_t)n_cand);
-    L.o_glob = take(sizeof(unsigned long long) * 2 * 16);
+    L.o_glob = take(sizeof(unsigned long long) * N_GLOB_LINES * 16);
     L.o_counters = take(sizeof(unsigned long long) * N_COUNTERS);
     L.C = C;
     L.qc_cap = qc_cap;
@@ -331,7 +333,7 @@ enum { Q_HEAD = 0, Q_TAIL = 1, Q_DONE = 2, Q_ABORT = 3, Q_CYC_EVAL = 4, Q_CYC_HG
        Q_HEAD_HI = 24, Q_TAIL_HI = 25, Q_N_PROMOTED = 26, Q_CYC_CTRL_BIG = 27 /* control tasks of systems > SMALL_N_MAX */, Q_N_CTRL_BIG = 28, Q_CYC_CHOL_BIG = 29, Q_N_CHOL_BIG = 30, Q_CYC_SOLVE_BIG = 31 /* first of the two solves per iteration */ };
 constexpr int HOT_STRIDE = 16;   // unsigned long longs = 128 bytes
 enum { H_EV_HEAD = 0, H_EV_TAIL = 1, H_HEAD_LO = 2, H_TAIL_LO = 3, H_HEAD_HI = 4, H_TAIL_HI = 5, H_AVAIL_LO = 6, H_AVAIL_HI = 7, N_HOT = 8 };
-enum { G_DONE = 0, G_ABORT = 1, N_GLOB = 2 };
+enum { G_DONE = 0, G_ABORT = 1, G_PROGRESS = 2 /* globaltimer of the last finished control task */, N_GLOB = 3 };
 enum { T_CTRL = 0, T_EVAL = 1, T_HG = 2 };
 constexpr uint32_t T_SHIFT = 28, T_CMASK = (1u << T_SHIFT) - 1u;
 
@@ -357,6 +359,23 @@ __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long
 __device__ __forceinline__ bool q_aborted(const WS& ws) { return ld_relaxed_u64(ws.glob + G_ABORT * HOT_STRIDE) != 0ull; }
 __device__ __forceinline__ void q_abort(const WS& ws) { atomicExch(ws.glob + G_ABORT * HOT_STRIDE, 1ull); }
 __device__ __forceinline__ unsigned long long q_done(const WS& ws) { return ld_relaxed_u64(ws.glob + G_DONE * HOT_STRIDE); }
+
+// Watchdog: the solver is aborted when NO control task has finished anywhere for `timeout_ns` (a lost task, a chain that
+// never ends) -- not when a long but healthy batch simply takes longer than that.
+__device__ __forceinline__ void q_progress(const WS& ws)
+{
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(ws.glob + G_PROGRESS * HOT_STRIDE), "l"(now) : "memory");
+}
+__device__ __forceinline__ bool q_stalled(const WS& ws, unsigned long long t_start, unsigned long long timeout_ns)
+{
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+    const unsigned long long last = ld_relaxed_u64(ws.glob + G_PROGRESS * HOT_STRIDE);
+    const unsigned long long since = last > t_start ? last : t_start;
+    return now > since && now - since > timeout_ns;
+}
 
 // one thread: publishes one task under ticket `t` of `ring` and its arrival event under event ticket `e`
 __device__ __forceinline__ void q_put(const WS& ws, const Queue& q, int ring, unsigned long long t, unsigned long long e, uint32_t type, uint32_t c, uint32_t first)
@@ -420,7 +439,7 @@ __device__ __forceinline__ void q_push_one(const WS& ws, const Queue& q, int rin
 }
 
 // one thread: takes the next task of the queue, urgent ring first.  Returns false when every candidate is finished, or when
-// the watchdog fired: a consumer that has been idle since `timeout_ns` after its start sets the abort flag and everybody leaves.
+// the watchdog fired: an idle consumer that sees no control task finish anywhere for `timeout_ns` sets the abort flag and everybody leaves.
 __device__ __forceinline__ bool q_pop(const WS& ws, const Queue& q, unsigned long long n_target, unsigned long long timeout_ns,
                                       unsigned long long t_start, uint2* task)
 {
@@ -431,11 +450,7 @@ __device__ __forceinline__ bool q_pop(const WS& ws, const Queue& q, unsigned lon
     while (ld_acquire_u32(q.ev + es) != (uint32_t)e + 1u) {
         if (q_done(ws) >= n_target) return false;
         if (q_aborted(ws)) return false;
-        if ((++spins & 1023u) == 0) {
-            unsigned long long now;
-            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
-            if (now - t_start > timeout_ns) { q_abort(ws); return false; }
-        }
+        if ((++spins & 1023u) == 0 && q_stalled(ws, t_start, timeout_ns)) { q_abort(ws); return false; }
         __nanosleep(ns);
         if (ns < 512) ns <<= 1;
     }

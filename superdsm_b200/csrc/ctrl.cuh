@@ -818,7 +818,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             S.status = SDSM_ST_OPTIMAL; S.bits = 0; S.it1 = S.it2 = S.it3 = -1; S.nf = S.nh = 0; S.have1 = 0; S.r_ipm = 0;
             S.val1 = 0; S.psi_last = 0; S.energy = 0;
             if (ci.flags) { S.status = SDSM_ST_BADREGION; if (tid == 0) out.d_status[c] = S.status; S.pc = PC_DONE; yield = true; break; }
-            if (ci.n_fg == 1) { S.status = SDSM_ST_SKIPPED; if (tid == 0) out.d_status[c] = S.status; S.pc = PC_DONE; yield = true; break; }   // objects.py:184-191
+            if (ci.n_fg == 1 && par.skip_single_fg) { S.status = SDSM_ST_SKIPPED; if (tid == 0) out.d_status[c] = S.status; S.pc = PC_DONE; yield = true; break; }   // objects.py:184-191
             for (int i = tid; i < P.N; i += BLOCK) x[i] = 0.0;
             __syncthreads();
             if (par.init_elliptical) { S.stage = STG_ELL1; S.use_xi = 0; S.pc = PC_IPMSTART; }
@@ -1177,17 +1177,22 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
 // Result rasterisation (objects.py:198-211): foreground inside omega, its bounding box, on_boundary.  One CTA per candidate.
 constexpr int FIN_BLOCK = 256;
 __global__ void __launch_bounds__(FIN_BLOCK)
-k_finish(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, sdsm_out out)
+k_finish(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, sdsm_out out)
 {
     constexpr int BLOCK = FIN_BLOCK;
     __shared__ int s_box[4];
     __shared__ int s_any;
     __shared__ int s_slotj[(BLOCK / 32) * 32];
     const int tid = threadIdx.x;
+    if (blockIdx.x == 0 && tid == 0 && out.d_solver) {
+        out.d_solver[0] = ws.glob[G_DONE * HOT_STRIDE];
+        out.d_solver[1] = ws.glob[G_ABORT * HOT_STRIDE];
+    }
     for (int c = blockIdx.x; c < n_cand; c += gridDim.x) {
         const int status = out.d_status[c];
         if (status != SDSM_ST_OPTIMAL && status != SDSM_ST_FALLBACK) continue;
         const sdsm_cand cd = cands[c];
+        const Img img = imgs.v[cd.img];
         const CInfo ci = ws.cinfo[c];
         const double* x = out.d_params + cd.par_off;
         const bool use_xi = ci.m > 0;

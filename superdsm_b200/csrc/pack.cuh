@@ -62,7 +62,7 @@ __device__ int excl_scan_i32(int32_t* a, int len, int* s_scan)
 }
 
 __global__ void __launch_bounds__(PACK_BLOCK)
-k_pack(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* __restrict__ footprints, WS ws)
+k_pack(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const int32_t* __restrict__ footprints, WS ws)
 {
     constexpr int BLOCK = PACK_BLOCK;
     __shared__ int32_t s_fp[256];
@@ -73,6 +73,7 @@ k_pack(Img img, Par par, const sdsm_cand* __restrict__ cands, int n_cand, const 
 
     for (int c = blockIdx.x; c < n_cand; c += gridDim.x) {
         const sdsm_cand cd = cands[c];
+        const Img img = imgs.v[cd.img];
         const int h = cd.h, w = cd.w;
         const int32_t* fp = footprints + cd.fp_off;
         const int nfp = cd.fp_len;

@@ -36,7 +36,7 @@ struct SolveArgs {
     int task_small_cells;    // candidates with at most this many non-empty cells get one cell per evaluation item
     int hi_evals;            // a candidate that has needed more evaluations of F than this becomes urgent (ring 1)
     int n_ctrl_ctas;         // CTAs [0, n_ctrl_ctas) run control tasks, the warps of the others evaluation / Hessian-row items
-    unsigned long long timeout_ns;   // watchdog: idle consumers abort the kernel after this long
+    unsigned long long timeout_ns;   // watchdog: the kernel is aborted when no control task has finished for this long
     double* trace;           // diagnostics (STG_TRACE) or nullptr
 };
 
@@ -122,7 +122,7 @@ __device__ __forceinline__ void finish_item(const WS& ws, uint32_t type, int c)
 }
 
 __global__ void __launch_bounds__(SOLVE_BLOCK, 2)
-k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out out, SolveArgs args)
+k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out out, SolveArgs args)
 {
     constexpr int BLOCK = SOLVE_BLOCK;
     extern __shared__ __align__(16) char smem_solve[];
@@ -147,7 +147,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
             int ok = 0;
             const long long c0 = clock64();
             if (lane == 0) {
-                if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) q_abort(ws);
+                if ((++n_popped & 255u) == 0 && q_stalled(ws, t_start, args.timeout_ns)) q_abort(ws);
                 ok = q_pop(ws, ws.qe, n_target, args.timeout_ns, t_start, &task) ? 1 : 0;
             }
             ok = __shfl_sync(0xffffffffu, ok, 0);
@@ -188,7 +188,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         if (tid == 0) {
             const long long c0 = clock64();
             uint2 task;
-            if ((++n_popped & 255u) == 0 && globaltimer_ns() - t_start > args.timeout_ns) q_abort(ws);
+            if ((++n_popped & 255u) == 0 && q_stalled(ws, t_start, args.timeout_ns)) q_abort(ws);
             const bool ok = q_pop(ws, ws.qc, n_target, args.timeout_ns, t_start, &task);
             cyc_idle += (unsigned long long)(clock64() - c0);
             s_task = task;
@@ -204,10 +204,11 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
         const long long c0 = clock64();
         {
             const sdsm_cand cd = cands[c];
+            const Img img = imgs.v[cd.img];
             const CInfo ci = ws.cinfo[c];
             for (unsigned link = 1;; ++link) {
                 if ((link & 63u) == 0) {                    // watchdog of a chain that never leaves this CTA
-                    if (tid == 0) s_flag = (globaltimer_ns() - t_start > args.timeout_ns || q_aborted(ws)) ? 1 : 0;
+                    if (tid == 0) s_flag = q_aborted(ws) ? 1 : 0;       // (a chain inside one CTA makes progress by definition: every link is a finished control task)
                     __syncthreads();
                     const bool stop = s_flag != 0;
                     __syncthreads();
@@ -219,7 +220,7 @@ k_solve(Img img, Par par, const sdsm_cand* __restrict__ cands, WS ws, sdsm_out o
                 bool requested;
                 if (big) { carve_smem_big(sm, smem_solve); requested = ctrl_step<BLOCK, true>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
                 else { carve_smem(sm, smem_solve, args.lcap); requested = ctrl_step<BLOCK, false>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
-                if (tid == 0) ws.cstate[c].ns_ctrl += globaltimer_ns() - t_link;
+                if (tid == 0) { ws.cstate[c].ns_ctrl += globaltimer_ns() - t_link; q_progress(ws); }
                 if (!requested) {
                     if (tid == 0) {
                         ws.pending[c] = (int32_t)((globaltimer_ns() - ws.counters[Q_T0]) / 1000ull);   // diagnostics: finish time, us
@@ -398,7 +399,7 @@ k_sweep_prep(Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, in
     for (int c = blockIdx.x; c < n_cand; c += gridDim.x) {
         const sdsm_cand cd = cands[c];
         const CInfo ci = ws.cinfo[c];
-        const bool live = !ci.flags && ci.n_fg != 1 && ws.cstate[c].pc == PC_DONE;
+        const bool live = !ci.flags && !(ci.n_fg == 1 && par.skip_single_fg) && ws.cstate[c].pc == PC_DONE;
         const int count = !live ? 0 : (rows ? (ci.m + HG_WARPS - 1) / HG_WARPS : (ci.n_ne + EVAL_CELLS - 1) / EVAL_CELLS);
         __syncthreads();
         if (threadIdx.x == 0) {

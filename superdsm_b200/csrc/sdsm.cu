@@ -19,22 +19,19 @@ using namespace sdsm;
 struct sdsm_ctx {
     int device = 0;
     int sm_count = 148;
-    Img img{nullptr, nullptr, 0, 0};
+    ImgSet imgs{};
+    int n_images = 0;
     Par par{};
     bool have_par = false;
     float* d_psf = nullptr;
     size_t psf_cap = 0;
     int64_t launches = 0;
-    // totals of the last plan (the layout is a pure function of these)
-    int64_t P = 0, C = 0, T = 0, V = 0, M = 0, K = 0;
-    int32_t n_cand = 0;
     int solve_ctas_per_sm = 1;               // resident CTAs of k_solve per SM (occupancy query)
     int solo_cells = 0;                      // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
     int task_small_cells = 512;              // SDSM_TASK_SMALL_CELLS: candidates up to this many cells get one cell per warp
     double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
     double hi_frac = 0.02;                   // SDSM_HI_FRAC: this share of the batch (the most expensive candidates) is urgent from the start
     bool ctrl_ctas_fixed = false;            // SDSM_CTRL_CTAS given: no adaptation to the batch
-    double solo_share = 0.0;                 // share of the last planned batch's pixels in candidates whose chains stay in one CTA
     int ctrl_ctas = 48;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
     int hi_evals = 300;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     std::string err;
@@ -100,12 +97,24 @@ extern "C" const char* sdsm_last_error(const sdsm_ctx* ctx) { return ctx ? ctx->
 
 extern "C" int64_t sdsm_launch_count(const sdsm_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
+extern "C" int sdsm_set_images(sdsm_ctx* ctx, const sdsm_image* h_images, int32_t n_images)
+{
+    if (!ctx || !h_images || n_images < 1) return SDSM_E_ARG;
+    if (n_images > SDSM_MAX_IMAGES) { ctx->err = "more than SDSM_MAX_IMAGES images in one set"; return SDSM_E_UNSUPPORTED; }
+    for (int32_t i = 0; i < n_images; ++i) {
+        const sdsm_image& im = h_images[i];
+        if (!im.d_y || !im.d_atoms || im.H < 2 || im.W < 2) return SDSM_E_ARG;
+        if (im.H > 65535 || im.W > 65535) { ctx->err = "image larger than 65535 pixels in a dimension"; return SDSM_E_UNSUPPORTED; }
+    }
+    for (int32_t i = 0; i < n_images; ++i) ctx->imgs.v[i] = Img{h_images[i].d_y, h_images[i].d_atoms, h_images[i].H, h_images[i].W};
+    ctx->n_images = n_images;
+    return SDSM_OK;
+}
+
 extern "C" int sdsm_set_image(sdsm_ctx* ctx, const double* d_y, const int32_t* d_atoms, int32_t H, int32_t W)
 {
-    if (!ctx || !d_y || !d_atoms || H < 2 || W < 2) return SDSM_E_ARG;
-    if (H > 65535 || W > 65535) { ctx->err = "image larger than 65535 pixels in a dimension"; return SDSM_E_UNSUPPORTED; }
-    ctx->img = Img{d_y, d_atoms, H, W};
-    return SDSM_OK;
+    const sdsm_image im{d_y, d_atoms, H, W};
+    return sdsm_set_images(ctx, &im, 1);
 }
 
 extern "C" int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_t* d_ymask, const int32_t* d_atoms, int32_t H, int32_t W,
@@ -141,6 +150,7 @@ extern "C" int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* p)
     par.abstol = p->abstol; par.reltol = p->reltol; par.feastol = p->feastol;
     par.sub = p->subsample; par.R = p->radius; par.has_smooth = p->has_smooth; par.init_elliptical = p->init_elliptical;
     par.maxiters = p->maxiters;
+    par.skip_single_fg = p->skip_single_fg ? 1 : 0;
     par.psf = nullptr;
     if (p->has_smooth) {
         if (!p->h_psf || p->radius < 1) return SDSM_E_ARG;
@@ -174,14 +184,16 @@ extern "C" int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* p)
 extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, sdsm_plan* plan)
 {
     if (!ctx || !cands || !plan || n_cand < 1) return SDSM_E_ARG;
-    if (!ctx->have_par || !ctx->img.y) { ctx->err = "sdsm_set_image / sdsm_set_params must precede sdsm_plan_batch"; return SDSM_E_ARG; }
+    if (!ctx->have_par || ctx->n_images < 1) { ctx->err = "sdsm_set_image(s) / sdsm_set_params must precede sdsm_plan_batch"; return SDSM_E_ARG; }
     const int sub = ctx->par.sub;
     int64_t P = 0, C = 0, T = 0, V = 0, M = 0, PAR = 0, FG = 0, K = 0;
     int32_t n_max = 6, cells_max = 1;
     double work_all = 0, work_solo = 0;
     for (int32_t i = 0; i < n_cand; ++i) {
         sdsm_cand& c = cands[i];
-        if (c.h < 1 || c.w < 1 || c.n < 1 || c.r0 < 0 || c.c0 < 0 || c.r0 + c.h > ctx->img.H || c.c0 + c.w > ctx->img.W || c.fp_len < 1) {
+        if (c.img < 0 || c.img >= ctx->n_images) { ctx->err = "candidate " + std::to_string(i) + ": image index outside the image set"; return SDSM_E_ARG; }
+        const Img& im = ctx->imgs.v[c.img];
+        if (c.h < 1 || c.w < 1 || c.n < 1 || c.r0 < 0 || c.c0 < 0 || c.r0 + c.h > im.H || c.c0 + c.w > im.W || c.fp_len < 1) {
             ctx->err = "candidate " + std::to_string(i) + ": empty region or bounding box outside the image";
             return SDSM_E_ARG;
         }
@@ -208,17 +220,25 @@ extern "C" int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* cands, int32_t n_cand, 
     plan->fgmask_len = FG;
     plan->n_max = n_max;
     plan->cells_max = cells_max;
-    plan->reserved0 = 0;
-    plan->reserved1 = 0;
-    ctx->solo_share = work_all > 0 ? work_solo / work_all : 0.0;
-    ctx->P = P; ctx->C = C; ctx->T = T; ctx->V = V; ctx->M = M; ctx->K = K; ctx->n_cand = n_cand;
+    plan->n_cand = n_cand;
+    plan->reserved = 0;
+    plan->totals[0] = P; plan->totals[1] = C; plan->totals[2] = T; plan->totals[3] = V; plan->totals[4] = M; plan->totals[5] = K;
+    plan->solo_share = work_all > 0 ? work_solo / work_all : 0.0;
     return SDSM_OK;
 }
 
-static int check_plan(sdsm_ctx* ctx, int32_t n_cand, size_t workspace_bytes, Layout* L)
+// the workspace layout of a planned batch: a pure function of the plan (no hidden context state)
+static Layout plan_layout(const sdsm_plan* plan)
 {
-    if (n_cand != ctx->n_cand) { ctx->err = "batch does not match the last sdsm_plan_batch"; return SDSM_E_ARG; }
-    *L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, n_cand);
+    return make_layout(plan->totals[0], plan->totals[1], plan->totals[2], plan->totals[3], plan->totals[4], plan->totals[5], plan->n_cand);
+}
+
+static int check_plan(sdsm_ctx* ctx, const sdsm_plan* plan, int32_t n_cand, size_t workspace_bytes, Layout* L)
+{
+    if (n_cand != plan->n_cand || plan->n_cand < 1) { ctx->err = "batch does not match its plan"; return SDSM_E_ARG; }
+    for (int k = 0; k < 6; ++k) if (plan->totals[k] < 0) { ctx->err = "corrupt plan"; return SDSM_E_ARG; }
+    *L = plan_layout(plan);
+    if (L->total != plan->workspace_bytes) { ctx->err = "corrupt plan"; return SDSM_E_ARG; }
     if (L->total > workspace_bytes) { ctx->err = "workspace too small"; return SDSM_E_WORKSPACE; }
     return SDSM_OK;
 }
@@ -226,7 +246,7 @@ static int check_plan(sdsm_ctx* ctx, int32_t n_cand, size_t workspace_bytes, Lay
 // Seeds the task queue with the control tasks that start `n_first` candidates (order, or the single candidate `single`)
 // and launches the persistent solver: one grid of resident CTAs that runs until every seeded candidate has finished.
 static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_cands, const WS& ws, const sdsm_out& out, int lcap,
-                      const int32_t* d_order, int n_first, int single, double* trace)
+                      const int32_t* d_order, int n_first, int single, double* trace, double solo_share)
 {
     // urgent from the start: the candidates at the head of the processing order (most expensive first); 0 for single solves
     int n_hi = d_order ? (int)(ctx->hi_frac * n_first) : 0;
@@ -243,10 +263,10 @@ static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_can
     args.trace = trace;
     const int grid = ctx->sm_count * ctx->solve_ctas_per_sm;
     // batches of small candidates keep their chains inside control CTAs: give those the share of the grid their work has
-    if (!ctx->ctrl_ctas_fixed && d_order) args.n_ctrl_ctas += (int)(0.65 * (grid - 8 - args.n_ctrl_ctas) * ctx->solo_share);
+    if (!ctx->ctrl_ctas_fixed && d_order) args.n_ctrl_ctas += (int)(0.65 * (grid - 8 - args.n_ctrl_ctas) * solo_share);
     if (args.n_ctrl_ctas < 1) args.n_ctrl_ctas = 1;
     if (args.n_ctrl_ctas > grid - 1) args.n_ctrl_ctas = grid - 1;
-    k_solve<<<grid, SOLVE_BLOCK, solve_smem_bytes(lcap), stream>>>(ctx->img, ctx->par, d_cands, ws, out, args);
+    k_solve<<<grid, SOLVE_BLOCK, solve_smem_bytes(lcap), stream>>>(ctx->imgs, ctx->par, d_cands, ws, out, args);
     ctx->launches += 2;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
@@ -259,7 +279,7 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     if (!ctx || !plan || !d_cands || !d_footprints || !d_order || !d_workspace || !out) return SDSM_E_ARG;
     if (!out->d_energy || !out->d_status || !out->d_info || !out->d_params || !out->d_fgbox || !out->d_onboundary || !out->d_fgmask) return SDSM_E_ARG;
     Layout L;
-    int rc = check_plan(ctx, n_cand, workspace_bytes, &L);
+    int rc = check_plan(ctx, plan, n_cand, workspace_bytes, &L);
     if (rc) return rc;
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -269,7 +289,7 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     CUDA_TRY(ctx, cudaMemsetAsync(out->d_fgmask, 0, (size_t)plan->fgmask_len, stream));
 
     const int pack_grid = n_cand < 8 * ctx->sm_count ? n_cand : 8 * ctx->sm_count;
-    k_pack<<<pack_grid, PACK_BLOCK, 0, stream>>>(ctx->img, ctx->par, d_cands, n_cand, d_footprints, ws);
+    k_pack<<<pack_grid, PACK_BLOCK, 0, stream>>>(ctx->imgs, ctx->par, d_cands, n_cand, d_footprints, ws);
     ctx->launches++;
     if (ctx->par.has_smooth) {
         const size_t psf_bytes = sizeof(float) * (size_t)(ctx->par.R + 1) * (ctx->par.R + 1);
@@ -280,10 +300,10 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
         ctx->launches += 2;
     }
     const int lcap = ctrl_lcap(plan->n_max);
-    rc = run_solver(ctx, stream, d_cands, ws, *out, lcap, d_order, n_cand, 0, nullptr);
+    rc = run_solver(ctx, stream, d_cands, ws, *out, lcap, d_order, n_cand, 0, nullptr, plan->solo_share);
     if (rc) return rc;
     const int fin_grid = n_cand < 16 * ctx->sm_count ? n_cand : 16 * ctx->sm_count;
-    k_finish<<<fin_grid, FIN_BLOCK, 0, stream>>>(ctx->img, ctx->par, d_cands, n_cand, ws, *out);
+    k_finish<<<fin_grid, FIN_BLOCK, 0, stream>>>(ctx->imgs, ctx->par, d_cands, n_cand, ws, *out);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
@@ -292,8 +312,8 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
 extern "C" int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, const double* d_x,
                                    double* d_value, double* d_grad, double* d_H, void* d_workspace, void* stream_)
 {
-    if (!ctx || !plan || !d_cands || !d_x || !d_value || !d_grad || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    if (!ctx || !plan || !d_cands || !d_x || !d_value || !d_grad || !d_workspace || c < 0 || c >= plan->n_cand) return SDSM_E_ARG;
+    const Layout L = plan_layout(plan);
     WS ws = make_ws(d_workspace, L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -311,8 +331,8 @@ extern "C" int sdsm_eval_candidate(sdsm_ctx* ctx, const sdsm_plan* plan, const s
 extern "C" int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, uint32_t* d_rc,
                                   int32_t* d_cols, float* d_vals, uint32_t* d_grid, void* d_workspace, void* stream_)
 {
-    if (!ctx || !plan || !d_cands || !d_rc || !d_cols || !d_vals || !d_grid || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    if (!ctx || !plan || !d_cands || !d_rc || !d_cols || !d_vals || !d_grid || !d_workspace || c < 0 || c >= plan->n_cand) return SDSM_E_ARG;
+    const Layout L = plan_layout(plan);
     WS ws = make_ws(d_workspace, L);
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     k_export<<<64, 128, 0, (cudaStream_t)stream_>>>(ctx->par, d_cands, c, ws, d_rc, d_cols, d_vals, d_grid);
@@ -324,8 +344,8 @@ extern "C" int sdsm_export_smooth(sdsm_ctx* ctx, const sdsm_plan* plan, const sd
 extern "C" int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t c, int32_t use_xi,
                                 const double* d_x0, double* d_trace, double* d_xout, int32_t* d_status_iters, void* d_workspace, void* stream_)
 {
-    if (!ctx || !plan || !d_cands || !d_x0 || !d_trace || !d_xout || !d_status_iters || !d_workspace || c < 0 || c >= ctx->n_cand) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    if (!ctx || !plan || !d_cands || !d_x0 || !d_trace || !d_xout || !d_status_iters || !d_workspace || c < 0 || c >= plan->n_cand) return SDSM_E_ARG;
+    const Layout L = plan_layout(plan);
     WS ws = make_ws(d_workspace, L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -333,7 +353,7 @@ extern "C" int sdsm_trace_solve(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     k_diag_trace_begin<<<1, SOLVE_BLOCK, 0, stream>>>(ctx->par, d_cands, c, use_xi, ws, d_x0);
     ctx->launches++;
     sdsm_out none{};   // STG_TRACE never writes results
-    int rc = run_solver(ctx, stream, d_cands, ws, none, lcap, nullptr, 1, c, d_trace);
+    int rc = run_solver(ctx, stream, d_cands, ws, none, lcap, nullptr, 1, c, d_trace, 0.0);
     if (rc) return rc;
     k_diag_trace_end<<<1, 128, 0, stream>>>(ctx->par, d_cands, c, ws, d_xout, d_status_iters);
     ctx->launches++;
@@ -353,10 +373,10 @@ extern "C" int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, i
     return SDSM_OK;
 }
 
-extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_t* h_stats, void* stream_)
+extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const sdsm_plan* plan, const void* d_workspace, uint64_t* h_stats, void* stream_)
 {
-    if (!ctx || !d_workspace || !h_stats) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    if (!ctx || !plan || !d_workspace || !h_stats) return SDSM_E_ARG;
+    const Layout L = plan_layout(plan);
     WS ws = make_ws(const_cast<void*>(d_workspace), L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -377,8 +397,8 @@ extern "C" int sdsm_solver_stats(sdsm_ctx* ctx, const void* d_workspace, uint64_
 extern "C" int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_cand* d_cands, int32_t n_cand, int32_t want_h,
                                int32_t rows, int32_t repeats, void* d_workspace, void* stream_)
 {
-    if (!ctx || !plan || !d_cands || !d_workspace || n_cand != ctx->n_cand || repeats < 1) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    if (!ctx || !plan || !d_cands || !d_workspace || n_cand != plan->n_cand || repeats < 1) return SDSM_E_ARG;
+    const Layout L = plan_layout(plan);
     WS ws = make_ws(d_workspace, L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -393,15 +413,15 @@ extern "C" int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_
     return SDSM_OK;
 }
 
-extern "C" int sdsm_finish_times(sdsm_ctx* ctx, const void* d_workspace, int32_t* h_us, void* stream_)
+extern "C" int sdsm_finish_times(sdsm_ctx* ctx, const sdsm_plan* plan, const void* d_workspace, int32_t* h_us, void* stream_)
 {
-    if (!ctx || !d_workspace || !h_us) return SDSM_E_ARG;
-    const Layout L = make_layout(ctx->P, ctx->C, ctx->T, ctx->V, ctx->M, ctx->K, ctx->n_cand);
+    if (!ctx || !plan || !d_workspace || !h_us) return SDSM_E_ARG;
+    const Layout L = plan_layout(plan);
     WS ws = make_ws(const_cast<void*>(d_workspace), L);
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    CUDA_TRY(ctx, cudaMemcpyAsync(h_us, ws.pending, sizeof(int32_t) * (size_t)ctx->n_cand, cudaMemcpyDeviceToHost, stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(h_us + ctx->n_cand, ws.prio, sizeof(int32_t) * (size_t)ctx->n_cand, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_us, ws.pending, sizeof(int32_t) * (size_t)plan->n_cand, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(h_us + plan->n_cand, ws.prio, sizeof(int32_t) * (size_t)plan->n_cand, cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(stream));
     return SDSM_OK;
 }

@@ -117,6 +117,17 @@ class BatchResult(object):
         return np.array([int(cd['r0']) + rmin, int(cd['c0']) + cmin]), box[rmin:rmax + 1, cmin:cmax + 1].astype(bool)
 
 
+class DeviceImage(object):
+    """One image resident on the device: y, its mask, the atoms map, the masked atoms map the kernels read
+    (``sdsm_prepare_image``) and, on the host, the per-atom usable-pixel counts and bounding boxes."""
+
+    def __init__(self, shape):
+        self.shape = tuple(shape)
+        self.d_y = self.d_mask = self.d_atoms_in = self.d_atoms = self.d_count = self.d_box = self.d_scratch = None
+        self.atom_count = self.atom_box = None
+        self.n_labels = 0
+
+
 class Engine(object):
     """One device context of the CUDA solver."""
 
@@ -132,10 +143,12 @@ class Engine(object):
         rc = self.lib.sdsm_create(ctypes.byref(self.ctx), device)
         self._check(rc)
         self.stream = torch.cuda.Stream(device=self.device)
-        self._image_key = None
         self._params_key = None
         self._bufs = {}
+        self._staged = {}
         self._last = None
+        self._image = None             # the DeviceImage of set_image()
+        self._bound = []               # the images the context currently solves on
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
@@ -161,11 +174,11 @@ class Engine(object):
     STAT_NAMES = ('q_head', 'q_tail', 'done', 'abort', 'cyc_eval', 'cyc_hrows', 'cyc_ctrl', 'cyc_idle', 'n_eval', 'n_hrows',
                   'n_ctrl', 'cyc_total', 't0', 'cyc_widle', 'cyc_wtotal', 'cyc_wfin')
 
-    def solver_stats(self, ws=None):
+    def solver_stats(self, ws=None, plan=None):
         """Counters of the persistent solver kernel of the last batch (synchronises): see ``sdsm_solver_stats``."""
-        if ws is None: ws = self._last[2]
+        if ws is None: plan, ws = self._last[0], self._last[2]
         st = np.zeros(32, dtype=np.uint64)
-        self._check(self.lib.sdsm_solver_stats(self.ctx, ws.data_ptr(), st.ctypes.data, self.stream.cuda_stream))
+        self._check(self.lib.sdsm_solver_stats(self.ctx, ctypes.byref(plan), ws.data_ptr(), st.ctypes.data, self.stream.cuda_stream))
         out = {k: int(st[i]) for i, k in enumerate(self.STAT_NAMES)}
         for j, kind in enumerate(('poly_f', 'poly_h', 'xi_f', 'xi_h')):
             out['cyc_' + kind], out['n_' + kind] = int(st[16 + j]), int(st[20 + j])
@@ -174,19 +187,13 @@ class Engine(object):
         out['cyc_chol_big'], out['n_chol_big'], out['cyc_solve_big'] = int(st[29]), int(st[30]), int(st[31])
         return out
 
-    def finish_times_us(self, ws=None, n=None):
+    def finish_times_us(self, ws=None, n=None, plan=None):
         """Per-candidate finish time of the last batch, microseconds after the solver kernel started (synchronises)."""
-        if ws is None: ws, n = self._last[2], len(self._last[3])
+        if ws is None: plan, ws, n = self._last[0], self._last[2], len(self._last[3])
         out = np.zeros(2 * n, dtype=np.int32)
-        self._check(self.lib.sdsm_finish_times(self.ctx, ws.data_ptr(), out.ctypes.data, self.stream.cuda_stream))
+        self._check(self.lib.sdsm_finish_times(self.ctx, ctypes.byref(plan), ws.data_ptr(), out.ctypes.data, self.stream.cuda_stream))
         self.control_times_us = out[n:]
         return out[:n]
-
-    def _check_solved(self, ws, n):
-        """Raises if the watchdog of the persistent solver fired or a candidate did not finish."""
-        st = self.solver_stats(ws)
-        if st['abort'] or st['done'] != n:
-            raise SolverError(f"persistent solver did not finish: {st['done']} of {n} candidates done, abort={st['abort']}")
 
     # -- buffers -------------------------------------------------------------------------------------------------
 
@@ -201,67 +208,102 @@ class Engine(object):
             self._bufs[name] = cur
         return cur
 
-    def _upload(self, name, array):
-        """numpy -> pinned staging -> device, on the engine's stream.  Returns the device byte tensor."""
+    def _to_device(self, name, array, dev=None):
+        """numpy -> pinned staging -> device tensor `dev` (or the grow-only buffer 'd_' + name), on the engine's stream.
+        The staging buffer of a name is reused only after the copy that last read it has finished (an event per name: no
+        stream-wide synchronisation)."""
         torch = self.torch
         array = np.ascontiguousarray(array)
         nbytes = array.nbytes
-        self.stream.synchronize()                      # the staging buffer may still feed an earlier copy
+        ev = self._staged.get(name)
+        if ev is not None: ev.synchronize()
         host = self._buf('h_' + name, nbytes, pinned=True)
         host[:nbytes].numpy()[:] = array.reshape(-1).view(np.uint8)
-        dev = self._buf('d_' + name, nbytes)
+        if dev is None: dev = self._buf('d_' + name, nbytes)
         with torch.cuda.stream(self.stream):
             dev[:nbytes].copy_(host[:nbytes], non_blocking=True)
+            if ev is None: ev = self._staged[name] = torch.cuda.Event()
+            ev.record(self.stream)
         self.h2d_bytes += nbytes
         return dev
 
-    # -- per image -----------------------------------------------------------------------------------------------
+    # -- images --------------------------------------------------------------------------------------------------
 
-    def set_image(self, y_model, y_mask, atoms, background_margin):
-        """Uploads the offset image, its mask and the atoms map; the usable pixels (``objects.py:126-127``: mask and
-        ``EDT(y <= 0) <= background_margin``), the masked atoms map and the per-atom pixel counts / bounding boxes are
-        computed on the device (``sdsm_prepare_image``; :func:`prepare_image` is the numpy statement of the same thing)."""
+    def upload_image(self, y_model, y_mask, atoms, background_margin, image=None):
+        """Uploads the offset image, its mask and the atoms map into a :class:`DeviceImage` (a new one, or `image` to reuse
+        its buffers); the usable pixels (``objects.py:126-127``: mask and ``EDT(y <= 0) <= background_margin``), the masked
+        atoms map and the per-atom pixel counts / bounding boxes are computed on the device (``sdsm_prepare_image``;
+        :func:`prepare_image` is the numpy statement of the same thing)."""
         torch = self.torch
         y_model = np.ascontiguousarray(y_model, dtype=np.float64)
+        assert y_model.ndim == 2
+        H, W = y_model.shape
+        if image is None or image.shape != (H, W):
+            image = DeviceImage((H, W))
+            dev = lambda n: torch.empty(n, dtype=torch.uint8, device=self.device)
+            image.d_y, image.d_mask, image.d_atoms_in, image.d_atoms, image.d_scratch = dev(8 * H * W), dev(H * W), dev(4 * H * W), dev(4 * H * W), dev(H * W)
+        self._to_device('y', y_model, image.d_y)
+        return self.update_labels(image, y_mask, atoms, background_margin)
+
+    def update_labels(self, image, y_mask, atoms, background_margin):
+        """New mask / atoms map for an image whose y stays resident (the rounds of the level-synchronous c2f scheduler):
+        re-runs ``sdsm_prepare_image``."""
+        torch = self.torch
+        H, W = image.shape
         atoms = np.ascontiguousarray(atoms, dtype=np.int32)
         y_mask = np.ascontiguousarray(y_mask, dtype=np.bool_)
-        assert y_model.ndim == 2 and atoms.shape == y_model.shape and y_mask.shape == y_model.shape
-        H, W = y_model.shape
-        self.shape = (H, W)
+        assert atoms.shape == (H, W) and y_mask.shape == (H, W)
         n_labels = int(atoms.max()) if atoms.size else 0
-        d_y = self._upload('y', y_model)
-        d_mask = self._upload('ymask', y_mask.view(np.uint8))
-        d_atoms_in = self._upload('atoms_in', atoms)
-        d_atoms = self._buf('d_atoms', 4 * H * W)
-        d_count = self._buf('d_atom_count', 8 * (n_labels + 1))
-        d_box = self._buf('d_atom_box', 16 * (n_labels + 1))
-        d_scratch = self._buf('d_edt', H * W)
+        self._to_device('ymask', y_mask.view(np.uint8), image.d_mask)
+        self._to_device('atoms_in', atoms, image.d_atoms_in)
+        if image.d_count is None or image.d_count.numel() < 8 * (n_labels + 1):
+            image.d_count = torch.empty(8 * (n_labels + 1) * 2, dtype=torch.uint8, device=self.device)
+            image.d_box = torch.empty(16 * (n_labels + 1) * 2, dtype=torch.uint8, device=self.device)
         margin = float(background_margin)
-        self._check(self.lib.sdsm_prepare_image(self.ctx, d_y.data_ptr(), d_mask.data_ptr(), d_atoms_in.data_ptr(), H, W,
-                                                margin if np.isfinite(margin) else 1e308 * 10, n_labels, d_atoms.data_ptr(),
-                                                d_count.data_ptr(), d_box.data_ptr(), d_scratch.data_ptr(), self.stream.cuda_stream))
+        self._check(self.lib.sdsm_prepare_image(self.ctx, image.d_y.data_ptr(), image.d_mask.data_ptr(), image.d_atoms_in.data_ptr(), H, W,
+                                                margin if np.isfinite(margin) else 1e308 * 10, n_labels, image.d_atoms.data_ptr(),
+                                                image.d_count.data_ptr(), image.d_box.data_ptr(), image.d_scratch.data_ptr(), self.stream.cuda_stream))
         nb_c, nb_b = 8 * (n_labels + 1), 16 * (n_labels + 1)
         h_c, h_b = self._buf('h_atom_count', nb_c, pinned=True), self._buf('h_atom_box', nb_b, pinned=True)
         with torch.cuda.stream(self.stream):
-            h_c[:nb_c].copy_(d_count[:nb_c], non_blocking=True)
-            h_b[:nb_b].copy_(d_box[:nb_b], non_blocking=True)
-        self.stream.synchronize()
+            h_c[:nb_c].copy_(image.d_count[:nb_c], non_blocking=True)
+            h_b[:nb_b].copy_(image.d_box[:nb_b], non_blocking=True)
+        self.stream.synchronize()                      # the descriptors of the candidates need the counts and boxes
         self.d2h_bytes += nb_c + nb_b
-        self.atom_count = h_c[:nb_c].numpy().view(np.int64).copy()
+        image.n_labels = n_labels
+        image.atom_count = h_c[:nb_c].numpy().view(np.int64).copy()
         box = h_b[:nb_b].numpy().view(np.int32).reshape(-1, 4).astype(np.int64)
-        box[self.atom_count == 0] = 0
-        self.atom_box = box
-        self._check(self.lib.sdsm_set_image(self.ctx, d_y.data_ptr(), d_atoms.data_ptr(), H, W))
+        box[image.atom_count == 0] = 0
+        image.atom_box = box
+        return image
+
+    def bind_images(self, images):
+        """The images the following batches draw their candidates from (``sdsm_set_images``)."""
+        images = list(images)
+        if not 1 <= len(images) <= _lib.MAX_IMAGES: raise SolverError(f'1 .. {_lib.MAX_IMAGES} images per batch')
+        arr = (_lib.ImageDesc * len(images))()
+        for k, im in enumerate(images):
+            arr[k].d_y, arr[k].d_atoms, arr[k].H, arr[k].W = im.d_y.data_ptr(), im.d_atoms.data_ptr(), im.shape[0], im.shape[1]
+        self._check(self.lib.sdsm_set_images(self.ctx, arr, len(images)))
+        self._bound = images
         self._last = None
 
-    def masked_atoms(self):
-        """The masked atoms map of the current image (device -> host; diagnostics and tests)."""
-        H, W = self.shape
-        self.stream.synchronize()
-        return self._bufs['d_atoms'][:4 * H * W].cpu().numpy().view(np.int32).reshape(H, W)
+    def set_image(self, y_model, y_mask, atoms, background_margin):
+        """Single-image convenience: uploads and binds one image (the engine keeps and reuses its device buffers)."""
+        self._image = self.upload_image(y_model, y_mask, atoms, background_margin, image=self._image)
+        self.shape, self.atom_count, self.atom_box = self._image.shape, self._image.atom_count, self._image.atom_box
+        self.bind_images([self._image])
 
-    def set_params(self, dsm_cfg):
-        """``dsm_cfg`` is the dictionary of ``dsmcfg.py:82-89``."""
+    def masked_atoms(self, image=None):
+        """The masked atoms map of an image (device -> host; diagnostics and tests)."""
+        image = image or self._bound[0]
+        H, W = image.shape
+        self.stream.synchronize()
+        return image.d_atoms[:4 * H * W].cpu().numpy().view(np.int32).reshape(H, W)
+
+    def set_params(self, dsm_cfg, skip_single_fg=True):
+        """``dsm_cfg`` is the dictionary of ``dsmcfg.py:82-89``.  ``skip_single_fg``: the rule of ``_compute_object``
+        (objects.py:184-191); ``cvxprog`` itself (the c2f seam) fits such regions, so it passes False."""
         cfg = dict(dsm_cfg)
         if cfg.get('smooth_mat_dtype', 'float32') != 'float32':
             raise SolverError('only dsm/smooth_mat_dtype = float32 (the default) is implemented')
@@ -269,7 +311,7 @@ class Engine(object):
             raise SolverError('callable dsm/init is not implemented on the device')
         key = tuple(sorted((k, str(v)) for k, v in cfg.items() if k in
                            ('alpha', 'epsilon', 'scale', 'sparsity_tol', 'smooth_amount', 'smooth_subsample',
-                            'gaussian_shape_multiplier', 'init')))
+                            'gaussian_shape_multiplier', 'init'))) + (bool(skip_single_fg),)
         if key == self._params_key: return
         p = _lib.Params()
         p.alpha, p.epsilon, p.scale = float(cfg['alpha']), float(cfg['epsilon']), float(cfg['scale'])
@@ -277,6 +319,7 @@ class Engine(object):
         p.subsample = int(cfg['smooth_subsample']) if np.isfinite(cfg['smooth_subsample']) else 16
         p.init_elliptical = 1 if cfg.get('init', 'elliptical') == 'elliptical' else 0
         p.maxiters, p.abstol, p.reltol, p.feastol = 100, 1e-7, 1e-6, 1e-7      # cvxopt defaults (never changed by the reference)
+        p.skip_single_fg = 1 if skip_single_fg else 0
         self._psf = None
         if cfg['smooth_amount'] < np.inf:
             self._psf, R = gaussian_psf32(cfg['smooth_amount'], cfg['gaussian_shape_multiplier'])
@@ -290,29 +333,60 @@ class Engine(object):
 
     # -- per batch -----------------------------------------------------------------------------------------------
 
-    def describe(self, footprints):
-        return describe_candidates(self.atom_count, self.atom_box, footprints)
+    def describe(self, footprints, image=None):
+        image = image or self._bound[0]
+        return describe_candidates(image.atom_count, image.atom_box, footprints)
 
-    def solve(self, footprints, keep_device_state=False, borrow=False):
-        """Fits every candidate of the batch; returns a :class:`BatchResult`.  ``borrow=True``: the foreground masks of the
-        result are a view of the engine's pinned staging buffer (valid until the next ``solve``) instead of a copy."""
-        torch, lib = self.torch, self.lib
-        t0 = time.perf_counter()
-        cands, flat = self.describe(footprints)
-        n = len(cands)
+    def describe_multi(self, footprints_per_image):
+        """Descriptors of a batch over the bound images: ``footprints_per_image[i]`` are the candidates of image i."""
+        if len(footprints_per_image) != len(self._bound): raise SolverError('one footprint list per bound image')
+        parts, flats, off = [], [], 0
+        for i, (image, fps) in enumerate(zip(self._bound, footprints_per_image)):
+            if len(fps) == 0: continue
+            cands, flat = describe_candidates(image.atom_count, image.atom_box, fps)
+            cands['img'] = i
+            cands['fp_off'] += off
+            off += len(flat)
+            parts.append(cands); flats.append(flat)
+        if not parts: raise SolverError('empty batch')
+        return np.concatenate(parts), np.concatenate(flats)
+
+    def _plan(self, cands):
         plan = _lib.Plan()
-        self._check(lib.sdsm_plan_batch(self.ctx, cands.ctypes.data, n, ctypes.byref(plan)))
+        self._check(self.lib.sdsm_plan_batch(self.ctx, cands.ctypes.data, len(cands), ctypes.byref(plan)))
         # most expensive first: the persistent solver pulls candidates from a queue
         cost = cands['n'].astype(np.float64) * (1.0 + 0.02 * cands['cell_cap'])
-        order = np.argsort(-cost, kind='stable').astype(np.int32)
-        d_cands = self._upload('cands', cands)
-        d_fp = self._upload('fp', flat)
-        d_order = self._upload('order', order)
+        return plan, np.argsort(-cost, kind='stable').astype(np.int32)
+
+    @staticmethod
+    def _out_sizes(n, plan):
+        return dict(energy=8 * n, status=4 * n, info=32 * n, params=8 * plan.params_len, fgbox=16 * n, onb=n, fgmask=plan.fgmask_len, solver=16)
+
+    def solve(self, footprints, keep_device_state=False, borrow=False):
+        """Fits every candidate of the batch (candidates of the first bound image); returns a :class:`BatchResult`.
+        ``borrow=True``: the foreground masks of the result are a view of the engine's pinned staging buffer (valid until
+        the next ``solve``) instead of a copy."""
+        cands, flat = self.describe(footprints)
+        return self._solve_described(cands, flat, borrow)
+
+    def solve_multi(self, footprints_per_image, borrow=False):
+        """One batch over all bound images (``bind_images``); ``result.cands['img']`` tells the candidates apart."""
+        cands, flat = self.describe_multi(footprints_per_image)
+        return self._solve_described(cands, flat, borrow)
+
+    def _solve_described(self, cands, flat, borrow):
+        torch, lib = self.torch, self.lib
+        t0 = time.perf_counter()
+        n = len(cands)
+        plan, order = self._plan(cands)
+        d_cands = self._to_device('cands', cands)
+        d_fp = self._to_device('fp', flat)
+        d_order = self._to_device('order', order)
         ws = self._buf('d_ws', plan.workspace_bytes)
-        sizes = dict(energy=8 * n, status=4 * n, info=32 * n, params=8 * plan.params_len, fgbox=16 * n, onb=n, fgmask=plan.fgmask_len)
+        sizes = self._out_sizes(n, plan)
         dev = {k: self._buf('d_out_' + k, v) for k, v in sizes.items()}
         out = _lib.Out(dev['energy'].data_ptr(), dev['status'].data_ptr(), dev['info'].data_ptr(), dev['params'].data_ptr(),
-                       dev['fgbox'].data_ptr(), dev['onb'].data_ptr(), dev['fgmask'].data_ptr())
+                       dev['fgbox'].data_ptr(), dev['onb'].data_ptr(), dev['fgmask'].data_ptr(), dev['solver'].data_ptr())
         self._check(lib.sdsm_solve_batch(self.ctx, ctypes.byref(plan), d_cands.data_ptr(), n, d_fp.data_ptr(), d_order.data_ptr(),
                                          ws.data_ptr(), ws.numel(), ctypes.byref(out), self.stream.cuda_stream))
         host = {}
@@ -322,7 +396,10 @@ class Engine(object):
                 h[:v].copy_(dev[k][:v], non_blocking=True)
                 host[k] = h
                 self.d2h_bytes += v
-        self._check_solved(ws, n)
+        self.stream.synchronize()
+        done, abort = (int(v) for v in host['solver'][:16].numpy().view(np.uint64))
+        if abort or done != n:
+            raise SolverError(f'persistent solver did not finish: {done} of {n} candidates done, abort={abort}')
         res = BatchResult(cands,
                           host['energy'][:sizes['energy']].numpy().view(np.float64).copy(),
                           host['status'][:sizes['status']].numpy().view(np.int32).copy(),
@@ -337,23 +414,21 @@ class Engine(object):
 
     # -- device-resident variant used by bench.py: inputs already in HBM, outputs stay there -------------------------
 
-    def prepare(self, footprints):
-        """Uploads a batch and returns a handle for :meth:`run_prepared` (no host work inside the timed region)."""
-        cands, flat = self.describe(footprints)
+    def prepare(self, footprints, multi=False):
+        """Uploads a batch and returns a handle for :meth:`run_prepared` (no host work inside the timed region).  The handle owns
+        its workspace and carries its plan: it stays valid whatever is planned or solved afterwards (on the same images)."""
+        cands, flat = self.describe_multi(footprints) if multi else self.describe(footprints)
         n = len(cands)
-        plan = _lib.Plan()
-        self._check(self.lib.sdsm_plan_batch(self.ctx, cands.ctypes.data, n, ctypes.byref(plan)))
-        cost = cands['n'].astype(np.float64) * (1.0 + 0.02 * cands['cell_cap'])
-        order = np.argsort(-cost, kind='stable').astype(np.int32)
+        plan, order = self._plan(cands)
         torch = self.torch
         to_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a).reshape(-1).view(np.uint8).copy()).to(self.device)
         h = dict(plan=plan, n=n, cands=cands, d_cands=to_dev(cands), d_fp=to_dev(flat), d_order=to_dev(order))
         h['ws'] = torch.empty(plan.workspace_bytes, dtype=torch.uint8, device=self.device)
-        sizes = dict(energy=8 * n, status=4 * n, info=32 * n, params=8 * plan.params_len, fgbox=16 * n, onb=n, fgmask=plan.fgmask_len)
+        sizes = self._out_sizes(n, plan)
         h['out'] = {k: torch.empty(max(v, 8), dtype=torch.uint8, device=self.device) for k, v in sizes.items()}
         o = h['out']
         h['out_struct'] = _lib.Out(o['energy'].data_ptr(), o['status'].data_ptr(), o['info'].data_ptr(), o['params'].data_ptr(),
-                                   o['fgbox'].data_ptr(), o['onb'].data_ptr(), o['fgmask'].data_ptr())
+                                   o['fgbox'].data_ptr(), o['onb'].data_ptr(), o['fgmask'].data_ptr(), o['solver'].data_ptr())
         torch.cuda.synchronize(self.device)
         return h
 

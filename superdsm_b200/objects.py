@@ -1,20 +1,24 @@
 """Drop-in for the hot path of the reference's ``superdsm/objects.py``.
 
 Same names, arguments and result fields as the reference; the per-candidate Python/Ray/cvxopt/MKL work of
-``objects.py:177-284,361-412`` is replaced by one batched call into the CUDA library.
+``objects.py:177-284,361-412`` is replaced by batched calls into the CUDA library.
 
     compute_objects(objects, y, atoms, dsm_cfg, log_root_dir, status_line, out)      objects.py:243-267
     _compute_objects(objects, y, atoms, x_map, lock, dsm_cfg, log_root_dir)          objects.py:270-284  (the seam)
     cvxprog(region, scale, epsilon, alpha, smooth_amount, ...)                       objects.py:361-412
+    compute_objects_multi(jobs, dsm_cfg)                                             several images in one launch (batch mode)
 
-``INTEGRATION.md`` shows how a maintainer binds these into the reference.
+The functions work on the caller's own classes: an image is anything with ``.model`` (float64 H x W) and ``.mask``, an
+object anything with ``.footprint`` and ``.set(state)``; the states handed to ``set`` carry the fields the reference's
+``Object.set`` copies (``objects.py:130-140``).  ``INTEGRATION.md`` shows how a maintainer binds these into the reference.
 """
+import hashlib
 import time
 
 import numpy as np
 
 from . import _lib
-from .dsm import DeformableShapeModel, Energy
+from .dsm import Energy, ModelParams
 from .engine import Engine, SolverError
 
 _engines = {}
@@ -28,96 +32,57 @@ def get_engine(device=None):
     return _engines[device]
 
 
-class BaseObject:
-    """Segmentation mask = foreground fragment + offset (reference ``objects.py:12-50``)."""
-
-    def __init__(self):
-        self.fg_offset = None
-        self.fg_fragment = None
-
-    def fill_foreground(self, out, value=True):
-        assert self.fg_offset is not None
-        assert self.fg_fragment is not None
-        sel = np.s_[self.fg_offset[0]:self.fg_offset[0] + self.fg_fragment.shape[0],
-                    self.fg_offset[1]:self.fg_offset[1] + self.fg_fragment.shape[1]]
-        out[sel] = value * self.fg_fragment
-        return sel
-
-
-class Object(BaseObject):
-    """A set of atomic image regions and, once computed, its fitted segmentation (reference ``objects.py:53-145``)."""
-
-    def __init__(self):
-        self.footprint = set()
-        self.energy = np.nan
-        self.on_boundary = np.nan
-        self.is_optimal = np.nan
-        self.processing_time = np.nan
-
-    def get_mask(self, atoms):
-        return np.isin(atoms, list(self.footprint)).reshape(atoms.shape)
-
-    def get_cvxprog_region(self, y, atoms, background_margin):
-        import scipy.ndimage as ndi
-        region = y.get_region(self.get_mask(atoms))
-        region.mask = np.logical_and(region.mask, ndi.distance_transform_edt(y.model <= 0) <= background_margin)
-        return region
-
-    def set(self, state):
-        self.fg_fragment = state.fg_fragment.copy() if state.fg_fragment is not None else None
-        self.fg_offset = state.fg_offset.copy() if state.fg_offset is not None else None
-        self.footprint = set(state.footprint)
-        self.energy = state.energy
-        self.on_boundary = state.on_boundary
-        self.is_optimal = state.is_optimal
-        self.processing_time = state.processing_time
-        return self
-
-    def copy(self):
-        return Object().set(self)
-
-
-def extract_foreground_fragment(fg_mask):
-    """Minimal rectangle of the foreground and its offset (reference ``objects.py:148-174``)."""
-    if fg_mask.any():
-        rows, cols = fg_mask.any(axis=1), fg_mask.any(axis=0)
-        rmin, rmax = np.where(rows)[0][[0, -1]]
-        cmin, cmax = np.where(cols)[0][[0, -1]]
-        return np.array([rmin, cmin]), fg_mask[rmin:rmax + 1, cmin:cmax + 1]
-    return np.zeros(2, int), np.zeros((1, 1), bool)
-
-
 class CvxprogError(Exception):
-    def __init__(self, *args, cidx=None, cause=None):
+    """Both elliptical passes failed (the reference raises its own ``CvxprogError``, ``objects.py:351-353``)."""
+
+    def __init__(self, *args, cidx=None):
         super().__init__(*args)
         self.cidx = cidx
 
     def __str__(self):
-        messages = [str(arg) for arg in self.args]
-        if self.cidx is not None: messages.append(f'cidx: {self.cidx}')
-        return ', '.join(messages)
+        return ', '.join([str(a) for a in self.args] + ([f'cidx: {self.cidx}'] if self.cidx is not None else []))
+
+
+class ObjectState(object):
+    """Result of one candidate: the fields ``Object.set`` reads (``objects.py:130-140``)."""
+    __slots__ = ('footprint', 'energy', 'on_boundary', 'is_optimal', 'processing_time', 'fg_offset', 'fg_fragment')
 
 
 DEFAULT_COMPUTING_STATUS_LINE = ('Computing objects', 'Computed objects')
 
-_image_cache = {}
+
+def _digest(*arrays):
+    h = hashlib.blake2b(digest_size=16)
+    for a in arrays:
+        a = np.ascontiguousarray(a)
+        h.update(str((a.shape, a.dtype.str)).encode())
+        h.update(a.view(np.uint8).reshape(-1))
+    return h.digest()
+
+
+_bound = {}
 
 
 def _bind_image(engine, y, atoms, background_margin):
-    """Uploads (y, atoms) unless the engine already holds exactly these arrays for this margin."""
-    key = (id(y.model), id(y.mask), id(atoms), y.model.shape, float(background_margin),
-           float(y.model.reshape(-1)[::997].sum()), int(np.asarray(atoms).reshape(-1)[::997].sum()))
-    if _image_cache.get(id(engine)) != key:
+    """Uploads (y, atoms) unless the engine already holds exactly these contents for this margin (the stages call
+    ``compute_objects`` once per generation on the same image): the key is a hash of the full contents, ~2 ms per megapixel."""
+    key = (_digest(y.model, y.mask, atoms), float(background_margin))
+    if _bound.get(id(engine)) != key or engine._bound != [engine._image]:
         engine.set_image(y.model, y.mask, atoms, background_margin)
-        _image_cache[id(engine)] = key
+        _bound[id(engine)] = key
 
 
-def _result_to_object(res, k, obj, dt):
+def forget_images():
+    """Drops the record of what is resident (the next call uploads again)."""
+    _bound.clear()
+
+
+def _state(res, k, footprint, dt):
     st = int(res.status[k])
     if st == _lib.ST_ERROR: raise CvxprogError('elliptical initialisation failed', cidx=k)
     if st == _lib.ST_BADREGION: raise SolverError(f'candidate {k}: region mismatch between host and device (flags in info)')
-    state = Object()
-    state.footprint = set(obj.footprint)
+    state = ObjectState()
+    state.footprint = set(footprint)
     if st == _lib.ST_SKIPPED:                                   # objects.py:184-191
         state.fg_offset, state.fg_fragment = np.zeros(2, int), np.zeros((1, 1), bool)
         state.energy, state.on_boundary, state.is_optimal, state.processing_time = 0., False, False, 0
@@ -130,8 +95,12 @@ def _result_to_object(res, k, obj, dt):
     return state, st == _lib.ST_FALLBACK
 
 
+def _check_cfg(cfg):
+    if cfg.get('hessian_sparsity_tol', 0) != 0: raise SolverError('hessian_sparsity_tol != 0 is not implemented')
+
+
 def _compute_objects(objects, y, atoms, x_map, lock, dsm_cfg, log_root_dir):
-    """Yields ``(cidx, Object, fallback)`` for every object, like the reference's generator (``objects.py:270-284``).
+    """Yields ``(cidx, state, fallback)`` for every object, like the reference's generator (``objects.py:270-284``).
 
     ``x_map``, ``lock`` and ``log_root_dir`` are accepted for signature compatibility; the padded coordinate map is not
     needed (the result is rasterised on the device), there is no host-side matrix allocation to lock, and there are no
@@ -141,14 +110,15 @@ def _compute_objects(objects, y, atoms, x_map, lock, dsm_cfg, log_root_dir):
     if len(objects) == 0: return
     cfg = dict(dsm_cfg)
     cfg.pop('smooth_mat_max_allocations', None)
+    _check_cfg(cfg)
     engine = get_engine()
     _bind_image(engine, y, atoms, cfg['background_margin'])
-    engine.set_params(cfg)
+    engine.set_params(cfg, skip_single_fg=True)
     t0 = time.time()
     res = engine.solve([obj.footprint for obj in objects], borrow=True)
     dt = (time.time() - t0) / len(objects)
     # all states are built before the first one is handed out: the masks are views of the engine's staging buffer
-    states = [_result_to_object(res, cidx, obj, dt) for cidx, obj in enumerate(objects)]
+    states = [_state(res, cidx, obj.footprint, dt) for cidx, obj in enumerate(objects)]
     for cidx, (state, fallback) in enumerate(states):
         yield cidx, state, fallback
 
@@ -168,28 +138,71 @@ def compute_objects(objects, y, atoms, dsm_cfg, log_root_dir, status_line=DEFAUL
         if ret[2]: fallbacks += 1
     if out is not None and hasattr(out, 'write'):
         out.write(f'{status_line[1]}: {len(objects)} ({fallbacks}x fallback)')
+    return fallbacks
+
+
+class ImageBatch(object):
+    """Several images resident on one device at once (batch mode, ``batch.py:288-361``): the candidates of all of them go
+    through ONE launch of the persistent solver, so that the long dependency chains of one image overlap the bulk of the
+    others.  ``images``: a list of ``(y, atoms)`` as ``compute_objects`` takes them."""
+
+    def __init__(self, images, background_margin, engine=None):
+        self.engine = engine or get_engine()
+        self.handles = [self.engine.upload_image(y.model, y.mask, atoms, background_margin) for y, atoms in images]
+
+    def compute_objects(self, objects_per_image, dsm_cfg):
+        """``objects_per_image[i]``: the objects of image i (may be empty).  Sets their fields in place; returns the number
+        of fallbacks per image."""
+        cfg = dict(dsm_cfg)
+        cfg.pop('smooth_mat_max_allocations', None)
+        _check_cfg(cfg)
+        eng = self.engine
+        eng.bind_images(self.handles)
+        _bound.pop(id(eng), None)
+        eng.set_params(cfg, skip_single_fg=True)
+        lists = [list(objs) for objs in objects_per_image]
+        t0 = time.time()
+        res = eng.solve_multi([[o.footprint for o in objs] for objs in lists], borrow=True)
+        dt = (time.time() - t0) / max(1, len(res))
+        fallbacks, k = [0] * len(lists), 0
+        states = []
+        for i, objs in enumerate(lists):
+            for o in objs:
+                states.append((i, o, _state(res, k, o.footprint, dt)))
+                k += 1
+        for i, o, (state, fb) in states:
+            o.set(state)
+            fallbacks[i] += int(fb)
+        return fallbacks
+
+
+def compute_objects_multi(jobs, dsm_cfg):
+    """``jobs``: list of ``(objects, y, atoms)``, one per image (at most 32).  All candidates of all images in one launch."""
+    batch = ImageBatch([(y, atoms) for _, y, atoms in jobs], dict(dsm_cfg)['background_margin'])
+    return batch.compute_objects([objs for objs, _, _ in jobs], dsm_cfg)
 
 
 def cvxprog(region, scale, epsilon, alpha, smooth_amount, smooth_subsample, gaussian_shape_multiplier, smooth_mat_allocation_lock=None,
             smooth_mat_dtype='float32', sparsity_tol=0, hessian_sparsity_tol=0, init=None, cachesize=0, cachetest=None, cp_timeout=None):
     """Fits a deformable shape model to one image region (reference ``objects.py:361-412``).
 
-    Returns ``(J, DeformableShapeModel, status)`` with ``status`` in ``('optimal', 'fallback')``.
+    Returns ``(J, model, status)`` with ``status`` in ``('optimal', 'fallback')``; ``model.array`` holds (theta, xi).
+    A region with a single foreground pixel is fitted like any other: the skip of such regions is a rule of
+    ``_compute_object`` (``objects.py:184-191``), not of ``cvxprog``.
     """
     if hessian_sparsity_tol != 0: raise SolverError('hessian_sparsity_tol != 0 is not implemented')
     engine = get_engine()
     mask = np.asarray(region.mask, dtype=bool)
     # a one-atom image whose usable pixels are exactly the region (margin = inf keeps every masked pixel)
     engine.set_image(region.model, mask, mask.astype(np.int32), np.inf)
-    _image_cache.pop(id(engine), None)
+    _bound.pop(id(engine), None)
     engine.set_params(dict(scale=scale, epsilon=epsilon, alpha=alpha, smooth_amount=smooth_amount, smooth_subsample=smooth_subsample,
                            gaussian_shape_multiplier=gaussian_shape_multiplier, smooth_mat_dtype=smooth_mat_dtype,
-                           sparsity_tol=sparsity_tol, init=init))
+                           sparsity_tol=sparsity_tol, init=init), skip_single_fg=False)
     res = engine.solve([{1}])
     st = int(res.status[0])
     if st == _lib.ST_ERROR: raise CvxprogError('elliptical initialisation failed')
     if st == _lib.ST_BADREGION: raise SolverError('region mismatch between host and device')
-    if st == _lib.ST_SKIPPED: raise SolverError('cvxprog on a region with a single foreground pixel (callers skip these, objects.py:184)')
     params = res.params(0)
     J = Energy(engine, 0, int(mask.sum()), res.m(0), params, res.energy[0])
-    return J, DeformableShapeModel(params), 'optimal' if st == _lib.ST_OPTIMAL else 'fallback'
+    return J, ModelParams(params), 'optimal' if st == _lib.ST_OPTIMAL else 'fallback'

@@ -93,13 +93,13 @@ def test_compute_objects_api_against_oracle(eng):
     """The drop-in seam compute_objects() on the synthetic toy workload, every candidate against the oracle."""
     from oracle import dsm_oracle as orc
     from workloads import synth
-    from superdsm_b200.image import Image
-    from superdsm_b200.objects import Object, compute_objects
+    from tests.compat.refshim import Image, Object
+    from superdsm_b200.objects import compute_objects
     w = synth.make_workload('toy', oversegment=2, max_set_size=3)
     objs = []
     for fp in w['footprints']:
         o = Object(); o.footprint = set(fp); objs.append(o)
-    y = Image.create_from_array(w['y'], normalize=False, mask=w['y_mask'])
+    y = Image(w['y'], w['y_mask'])
     compute_objects(objs, y, w['atoms'], w['dsm_cfg'], None)
     worst = 0
     for o in objs:
@@ -161,7 +161,7 @@ def test_cvxprog_seam_without_deformations(eng):
     """objects.cvxprog as c2f calls it (smooth_amount = inf, c2freganal.py:126): a 6-parameter fit; optimality certificate
     and agreement with the oracle."""
     from oracle import dsm_oracle as orc
-    from superdsm_b200.image import Image
+    from tests.compat.refshim import Image, Object
     from superdsm_b200.objects import cvxprog
     case = GoldenCase('hand')
     mask = case.mask(0)
@@ -206,31 +206,32 @@ def test_full_size_properties(eng):
 
 
 def test_c2f_normalized_energy_computer(eng):
-    """c2freganal.py:58-79 on the mirror: cluster crop -> full-frame buffer -> 6-parameter fit -> J(model) / n, cached by mask
-    hash; the value agrees with the oracle's fit of the same region."""
+    """c2freganal.py:58-79: cluster crop -> full-frame region -> 6-parameter fit -> J(model) / n, cached by the region mask; the
+    value agrees with the oracle's fit of the same region.  (The level-synchronous scheduler: tests/test_gpu_round2.py.)"""
     from oracle import dsm_oracle as orc
-    from superdsm_b200 import c2freganal
-    from superdsm_b200.image import Image
-    from superdsm_b200.objects import Object
+    from superdsm_b200.c2f import NormalizedEnergyComputer, RegionRequest
+    from tests.compat.refshim import Image, Object
     case = GoldenCase('toy')
     y = Image(case.y, case.y_mask)
     atoms = case.atoms
     fp = sorted(case.footprints[0])
-    cluster_mask = np.isin(atoms, fp)
-    cluster = y.get_region(cluster_mask, shrink=True)
-    crop = np.s_[cluster.offset[0]:cluster.offset[0] + cluster.mask.shape[0], cluster.offset[1]:cluster.offset[1] + cluster.mask.shape[1]]
-    cfg = dict(case.dsm_cfg); cfg['smooth_amount'] = np.inf
-    compute = c2freganal._get_cached_normalized_energy_computer(y, cluster)
-    obj = Object(); obj.footprint = set(fp)
-    e1 = compute(obj, cluster, atoms[crop], cfg)
-    e2 = compute(obj, cluster, atoms[crop], cfg)                 # cache hit
-    assert e1 == e2 and np.isfinite(e1)
+    cluster = y.get_region(np.isin(atoms, fp), shrink=True)
+    crop = cluster.window()
+    cfg = dict(case.dsm_cfg)
+    computer = NormalizedEnergyComputer(case.y, cfg, eng)
+    cp_region = Object(fp).get_cvxprog_region(cluster, atoms[crop], cfg['background_margin'])
+    rq = RegionRequest(cluster.offset, cp_region.mask)
+    (e1,) = computer.compute([rq])
+    (e2,) = computer.compute([rq])                               # cache hit: no second launch
+    assert e1 == e2 and np.isfinite(e1) and computer.launches == 1
     # the oracle on the same region, in the full frame
-    cp_region = obj.get_cvxprog_region(cluster, atoms[crop], cfg['background_margin'])
-    full = np.zeros(case.y.shape, bool); full[cluster.full_mask] = cp_region.mask[cluster.mask]
-    keys = ('scale', 'epsilon', 'alpha', 'smooth_amount', 'smooth_subsample', 'gaussian_shape_multiplier', 'smooth_mat_dtype', 'init')
-    Jo, po, so = orc.cvxprog(case.y, full, **{k: cfg[k] for k in keys})
+    full = np.zeros(case.y.shape, bool); full[crop] = cp_region.mask
+    keys = ('scale', 'epsilon', 'alpha', 'smooth_subsample', 'gaussian_shape_multiplier', 'smooth_mat_dtype', 'init')
+    Jo, po, so = orc.cvxprog(case.y, full, smooth_amount=np.inf, **{k: cfg[k] for k in keys})
     assert e1 == pytest.approx(Jo(po) / full.sum(), rel=1e-6)
+    # all-positive / all-negative regions have no energy (c2freganal.py:68-69)
+    neg = np.zeros(case.y.shape, bool); neg[np.unravel_index(np.argsort(case.y, axis=None)[:50], case.y.shape)] = True
+    assert computer.compute([RegionRequest((0, 0), neg)]) == [None]
 
 
 @pytest.mark.parametrize('name,kw', [('bbbc039', dict()), ('nih3t3', dict()), ('tiled4k', dict(shape=(768, 768), n=700))])

@@ -1,0 +1,153 @@
+"""Round-2 rows of the hot-path scope table on the device (through the C ABI): several images per launch, the level-synchronous
+c2f scheduler, cvxprog on a single-foreground-pixel region, plan-carrying handles.  -m gpu."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def eng():
+    from superdsm_b200.objects import get_engine
+    return get_engine(0)
+
+
+def _toy(seed):
+    from workloads import synth
+    return synth.make_workload('toy', oversegment=2, max_set_size=3, seed=seed)
+
+
+def test_multi_image_batch_is_bitwise_the_single_image_result(eng):
+    """Candidates of three images in ONE launch (sdsm_set_images / sdsm_cand.img): every result bit-identical to the image solved
+    alone -- energies, parameters, statuses, foreground masks."""
+    ws = [_toy(s) for s in (7, 8, 9)]
+    cfg = ws[0]['dsm_cfg']
+    singles = []
+    for w in ws:
+        eng.set_image(w['y'], w['y_mask'], w['atoms'], cfg['background_margin'])
+        eng.set_params(cfg)
+        singles.append(eng.solve(w['footprints']))
+    handles = [eng.upload_image(w['y'], w['y_mask'], w['atoms'], cfg['background_margin']) for w in ws]
+    eng.bind_images(handles)
+    eng.set_params(cfg)
+    res = eng.solve_multi([w['footprints'] for w in ws])
+    assert len(res) == sum(len(w['footprints']) for w in ws)
+    k = 0
+    for i, (w, single) in enumerate(zip(ws, singles)):
+        for j in range(len(single)):
+            assert int(res.cands['img'][k]) == i
+            assert res.status[k] == single.status[j] and res.energy[k] == single.energy[j], (i, j)
+            assert np.array_equal(res.params(k), single.params(j))
+            (o1, f1), (o2, f2) = res.foreground(k), single.foreground(j)
+            assert np.array_equal(o1, o2) and np.array_equal(f1, f2)
+            k += 1
+    # an empty image in the set is allowed, and the seam-level helper sets the callers' objects in place
+    from superdsm_b200.objects import compute_objects_multi
+    from tests.compat.refshim import Image, Object
+    jobs = [([Object(fp) for fp in w['footprints'][:5]], Image(w['y'], w['y_mask']), w['atoms']) for w in ws]
+    jobs[1] = ([], jobs[1][1], jobs[1][2])
+    fallbacks = compute_objects_multi(jobs, cfg)
+    assert len(fallbacks) == 3 and fallbacks[1] == 0
+    for j, ob in enumerate(jobs[2][0]): assert ob.energy == singles[2].energy[j]
+
+
+def test_prepared_handles_stay_valid_across_plans(eng):
+    """A handle of Engine.prepare carries its own plan (the workspace layout is a function of the plan, not of hidden context
+    state): planning another batch in between does not disturb it."""
+    import torch
+    w = _toy(7)
+    eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
+    eng.set_params(w['dsm_cfg'])
+    h1 = eng.prepare(w['footprints'][:10])
+    eng.run_prepared(h1); torch.cuda.synchronize()
+    e1 = h1['out']['energy'][:80].cpu().numpy().view(np.float64).copy()
+    h2 = eng.prepare(w['footprints'][3:])           # replans
+    eng.run_prepared(h2); torch.cuda.synchronize()
+    eng.run_prepared(h1); torch.cuda.synchronize()
+    assert np.array_equal(h1['out']['energy'][:80].cpu().numpy().view(np.float64), e1)
+    st = eng.solver_stats(h1['ws'], h1['plan'])
+    assert st['done'] == 10 and not st['abort']
+    assert np.array_equal(h1['out']['solver'][:16].cpu().numpy().view(np.uint64), [10, 0])
+
+
+def test_cvxprog_fits_a_region_with_one_foreground_pixel(eng):
+    """cvxprog itself fits such a region (objects.py:361-412); only _compute_object skips it (objects.py:184-191)."""
+    from oracle import dsm_oracle as orc
+    from superdsm_b200.objects import cvxprog, compute_objects
+    from tests.compat.refshim import Image, Object
+    rng = np.random.default_rng(3)
+    y = -0.2 + 0.05 * rng.standard_normal((40, 48))
+    y[20, 24] = 0.4                                   # the only positive pixel
+    mask = np.zeros(y.shape, bool); mask[8:32, 10:40] = True
+    assert (y[mask] > 0).sum() == 1
+    kw = dict(scale=1000, epsilon=1.0, alpha=0.5, smooth_amount=np.inf, smooth_subsample=20, gaussian_shape_multiplier=2,
+              smooth_mat_dtype='float32', init='elliptical')
+    J, model, status = cvxprog(Image(y, mask), smooth_mat_allocation_lock=None, **kw)
+    Jo, po, so = orc.cvxprog(y, mask, **kw)
+    assert status == so
+    assert J(model) == pytest.approx(Jo(po), rel=1e-6, abs=2e-7 * mask.sum() / 1000)
+    # ... while the batch seam skips it: energy 0, not optimal
+    ob = Object({1})
+    cfg = dict(kw, background_margin=1e9, smooth_amount=4, smooth_subsample=8, cachesize=1, cachetest=None, sparsity_tol=0, cp_timeout=300)
+    compute_objects([ob], Image(y, np.ones(y.shape, bool)), mask.astype(np.int32), cfg, None)
+    assert ob.energy == 0.0 and ob.is_optimal is False
+
+
+def test_c2f_level_synchronous_scheduler(eng):
+    """c2freganal.py:193-287 with every cluster's split state machine advanced in lock-step: the regions of a round (<= 2 per
+    live cluster) go through ONE batch with no deformation parameters; the image is uploaded once.  Every normalised energy
+    of every split attempt equals the oracle's serial run of the same state machines (1e-6)."""
+    from oracle import dsm_oracle as orc
+    from superdsm_b200.c2f import NormalizedEnergyComputer, run_level_synchronous
+    from tests.compat.c2f_cluster import cluster_task
+    from tests.compat.refshim import Image
+    import scipy.ndimage as ndi
+    from workloads import synth
+    w = synth.make_workload('toy', oversegment=1, max_set_size=1, seed=21, shape=(200, 240), n=9)
+    y = Image(w['y'], np.ones(w['y'].shape, bool))
+    comp, ncomp = ndi.label(w['y'] > 0)
+    sizes = ndi.sum(w['y'] > 0, comp, index=np.arange(1, ncomp + 1))
+    keep = [k + 1 for k in range(ncomp) if sizes[k] >= 80]
+    markers = np.where(np.isin(comp, keep), comp, 0)
+    idx = ndi.distance_transform_edt(markers == 0, return_distances=False, return_indices=True)
+    clusters = markers[idx[0], idx[1]]
+    cfg = dict(w['dsm_cfg'])
+    args = dict(dsm_cfg=cfg, max_atom_norm_energy=0.05, min_atom_radius=4, min_norm_energy_improvement=0.1)
+
+    logs = {lab: [] for lab in keep}
+    computer = NormalizedEnergyComputer(w['y'], cfg, eng)
+    out = run_level_synchronous([cluster_task(y, clusters, lab, y.mask, log=logs[lab], **args) for lab in keep], computer)
+    n_requests = sum(1 if e[0] == 'root' else 2 for lg in logs.values() for e in lg)
+    assert computer.uploads == 1                                       # one upload of y per image
+    assert computer.launches == run_level_synchronous.last_rounds < n_requests      # batched across the clusters
+    assert len(out) == len(keep) and any(len(lg) > 1 for lg in logs.values()), 'no cluster was split: the test image is too easy'
+
+    # the oracle, serially: the same generators, one region at a time
+    keys = ('scale', 'epsilon', 'alpha', 'smooth_subsample', 'gaussian_shape_multiplier', 'smooth_mat_dtype', 'init')
+
+    def oracle_energy(rq):
+        full = np.zeros(w['y'].shape, bool)
+        (r, c), (h, ww) = rq.offset, rq.mask.shape
+        full[r:r + h, c:c + ww] = rq.mask
+        v = w['y'][full]
+        if (v > 0).all() or (v < 0).all(): return None
+        J, p, _ = orc.cvxprog(w['y'], full, smooth_amount=np.inf, **{k: cfg[k] for k in keys})
+        return J(p) / full.sum()
+    worst = 0.0
+    for lab in keep:
+        ref_log = []
+        gen = cluster_task(y, clusters, lab, y.mask, log=ref_log, **args)
+        try:
+            reqs = next(gen)
+            while True: reqs = gen.send([oracle_energy(rq) for rq in reqs])
+        except StopIteration:
+            pass
+        assert len(ref_log) == len(logs[lab]), (lab, len(ref_log), len(logs[lab]))
+        for a, b in zip(logs[lab], ref_log):
+            assert a[0] == b[0]
+            for ea, eb in zip(a[2:], b[2:]):
+                assert (ea is None) == (eb is None)
+                if ea is not None:
+                    assert ea == pytest.approx(eb, rel=1e-6, abs=2e-10)
+                    worst = max(worst, abs(ea - eb) / abs(eb))
+    print('clusters', len(keep), 'requests', n_requests, 'rounds', run_level_synchronous.last_rounds, 'worst relative error', worst)

@@ -6,7 +6,8 @@ import re
 import numpy as np
 import pytest
 
-from superdsm_b200 import _lib, engine, image, objects, dsm, dsmcfg
+from superdsm_b200 import _lib, engine, objects, dsm
+from tests.compat import refshim
 from tests.golden_util import CASES, GoldenCase
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -18,12 +19,21 @@ def test_library_exports_every_declared_symbol():
     assert declared == set(_lib.EXPORTS)
     lib = _lib.load()
     for name in declared: assert hasattr(lib, name), name
-    assert lib.sdsm_abi_version() == 4
+    assert lib.sdsm_abi_version() == _lib.ABI_VERSION == 5
 
 
 def test_struct_layouts_match_the_header():
-    assert _lib.CAND_DTYPE.itemsize == 88 and _lib.CAND_DTYPE.fields['pix_off'][1] == 32
-    assert ctypes.sizeof(_lib.Params) == 88 and ctypes.sizeof(_lib.Plan) == 40 and ctypes.sizeof(_lib.Out) == 56
+    assert _lib.CAND_DTYPE.itemsize == 96 and _lib.CAND_DTYPE.fields['pix_off'][1] == 40 and _lib.CAND_DTYPE.fields['img'][1] == 32
+    assert ctypes.sizeof(_lib.Params) == 88 and ctypes.sizeof(_lib.Plan) == 96 and ctypes.sizeof(_lib.Out) == 64
+    assert ctypes.sizeof(_lib.ImageDesc) == 24
+    # the header's own sizes, from a C compiler
+    import subprocess, tempfile
+    src = '#include <stdio.h>\n#include "superdsm_b200.h"\nint main(){printf("%zu %zu %zu %zu %zu", sizeof(sdsm_cand), sizeof(sdsm_params), sizeof(sdsm_plan), sizeof(sdsm_out), sizeof(sdsm_image));return 0;}'
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, 't.c'), 'w').write(src)
+        subprocess.run(['gcc', '-I', os.path.join(ROOT, 'include'), '-o', os.path.join(d, 't'), os.path.join(d, 't.c')], check=True)
+        sizes = subprocess.run([os.path.join(d, 't')], capture_output=True, text=True).stdout.split()
+    assert [int(v) for v in sizes] == [96, 88, 96, 64, 24]
 
 
 @pytest.mark.parametrize('name', CASES)
@@ -68,30 +78,33 @@ def test_lpt_shards_balance_and_cover():
     assert loads.max() / loads.mean() < 1.02
 
 
-def test_reference_unit_fixtures_on_the_mirror():
-    """tests/test_objects.py and tests/test_image.py of the reference, run on the mirrored classes."""
-    obj = objects.BaseObject()
+def test_caller_side_shim_matches_the_reference_fixtures():
+    """tests/test_objects.py and tests/test_image.py of the reference on the caller-side stand-ins the GPU tests use
+    (tests/compat/refshim.py), and the light model container the seam returns."""
+    obj = refshim.Object()
     obj.fg_fragment = np.array([[False, True], [True, True], [True, False]])
     obj.fg_offset = (1, 2)
     actual = np.zeros((4, 5), bool)
     obj.fill_foreground(actual)
     expected = np.array([[0, 0, 0, 0, 0], [0, 0, 0, 1, 0], [0, 0, 1, 1, 0], [0, 0, 1, 0, 0]], bool)
     assert np.array_equal(actual, expected)
-    off, frag = objects.extract_foreground_fragment(expected)
-    assert np.array_equal(off, [1, 2]) and np.array_equal(frag, obj.fg_fragment)
-    o = objects.Object(); o.footprint = {2, 3}
+    o = refshim.Object({2, 3})
     assert np.array_equal(o.get_mask(np.array([[1, 1, 2], [1, 3, 2], [3, 3, 3]])), np.array([[0, 0, 1], [0, 1, 1], [1, 1, 1]], bool))
     y = np.array([[-1] * 5] * 3 + [[-1, 1, -1, -1, -1], [-1, 1, -1, -1, 1], [-1, 1, -1, -1, 1]])
     atoms = np.array([[1] * 5, [1] * 5, [1, 1, 1, 1, 2], [1, 1, 1, 2, 2], [1, 1, 1, 2, 2], [1, 1, 1, 2, 2]])
-    o = objects.Object(); o.footprint = {1}
-    region = o.get_cvxprog_region(image.Image(y), atoms, background_margin=2)
-    assert np.array_equal(region.mask, np.array([[0] * 5, [0, 1, 0, 0, 0]] + [[1, 1, 1, 0, 0]] * 4, bool))
-    assert np.allclose(image.get_pixel_map((6, 3), normalized=True)[0][:, 0], np.arange(6) / 5)
-    b, sel = image.bbox(expected)
-    assert np.array_equal(b, [[1, 4], [2, 4]])
-    m = dsm.DeformableShapeModel(np.arange(8.))
-    assert np.array_equal(m.A, [[0, 2], [2, 1]]) and np.array_equal(m.ξ, [6, 7])
-    assert dsmcfg.get_dsm_cfg({'alpha': 3})['alpha'] == 3 and dsmcfg.get_dsm_cfg()['smooth_subsample'] == 20
+    region = refshim.Object({1}).get_cvxprog_region(refshim.Image(y), atoms, background_margin=2)
+    assert np.array_equal(region.mask, np.array([[0] * 5, [0, 1, 0, 0, 0]] + [[1, 1, 1, 0, 0]] * 4, bool))     # tests/test_objects.py:50-74
+    big = np.zeros(y.shape, bool); big[1:4, 2:4] = expected[1:4, 2:4]
+    crop = refshim.Image(y.astype(float)).get_region(big, shrink=True)
+    assert crop.offset == (1, 2) and crop.mask.shape == (3, 2) and crop.full_mask.shape == y.shape
+    m = dsm.ModelParams(np.arange(8.))
+    assert np.array_equal(m.A, [[0, 2], [2, 1]]) and np.array_equal(m.ξ, [6, 7]) and m.c == 5
+    with pytest.raises(ValueError): dsm.ModelParams(np.arange(5.))
+    st = objects.ObjectState()
+    st.footprint, st.energy, st.on_boundary, st.is_optimal, st.processing_time = {4}, 1.5, False, True, 0.1
+    st.fg_offset, st.fg_fragment = np.array([1, 2]), np.ones((2, 2), bool)
+    o = refshim.Object().set(st)
+    assert o.footprint == {4} and o.energy == 1.5 and o.fg_fragment.shape == (2, 2)
 
 
 def test_engine_fails_loudly_without_gpu():
@@ -111,12 +124,12 @@ def _gloo_worker(rank, world, port, out_path):
     fps = [set(rng.choice(np.arange(1, 40), size=int(rng.integers(1, 4)), replace=False).tolist()) for _ in range(57)]
     objs = []
     for fp in fps:
-        o = objects.Object(); o.footprint = fp; objs.append(o)
+        o = refshim.Object(fp); objs.append(o)
     solved_here = []
 
     def fake_solve(shard, y, atoms_, cfg, log):        # stands in for the CUDA engine: a state that depends on the footprint only
         for k, o in enumerate(shard):
-            st = objects.Object(); st.footprint = set(o.footprint)
+            st = refshim.Object(o.footprint)
             st.energy = float(sum(o.footprint)) * cfg['scale']; st.on_boundary = False; st.is_optimal = True; st.processing_time = 0.0
             st.fg_offset = np.array([min(o.footprint), 0]); st.fg_fragment = np.ones((1, len(o.footprint)), bool)
             solved_here.append(sorted(o.footprint))
