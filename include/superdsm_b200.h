@@ -143,7 +143,7 @@ int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* params);
  * sdsm_set_image() expects -- computed with an exact windowed Euclidean distance transform (bit-equal to the scipy
  * expression).  d_count[n_labels + 1] / d_box[4 (n_labels + 1)] receive, per atom label, the number of usable pixels and
  * their bounding box (r0, r1, c0, c1; end-exclusive; r0 = H, r1 = 0 if none).  background_margin = +inf keeps every masked
- * pixel.  d_scratch: H * W bytes.  d_ymask: one byte per pixel (numpy bool). */
+ * pixel.  d_scratch: 2 * H * W bytes.  d_ymask: one byte per pixel (numpy bool). */
 int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_t* d_ymask, const int32_t* d_atoms, int32_t H, int32_t W,
                        double background_margin, int32_t n_labels, int32_t* d_atoms_out, uint64_t* d_count, int32_t* d_box,
                        uint8_t* d_scratch, void* stream);

@@ -3,7 +3,7 @@
 // scipy's EDT gives, for a pixel with y <= 0, the Euclidean distance to the nearest pixel with y > 0 (0 for the others),
 // as sqrt of the exact integer squared distance.  Only the comparison with the margin M is needed, so the exact
 // two-pass separable algorithm is run on windows of +-floor(M):
-//   k_edt_cols:  g(r, c)  = min |r - r'| over r' with y(r', c) > 0, |r - r'| <= floor(M)   (255: none)
+//   k_edt_cols:  g(r, c)  = min |r - r'| over r' with y(r', c) > 0, |r - r'| <= floor(M)   (65535: none)
 //   k_edt_rows:  d2(r, c) = min over |dc| <= floor(M) of dc^2 + g(r, c + dc)^2;  usable iff sqrt((double) d2) <= M
 // -- every pixel whose true distance is <= M has its nearest y > 0 pixel inside both windows, so the thresholded result is
 // exact (bit-equal to the scipy expression).  k_edt_rows also writes the masked atoms map and gathers, per atom label, the
@@ -13,13 +13,13 @@
 
 namespace sdsm {
 
-constexpr int EDT_MAX_MARGIN = 254;
+constexpr int EDT_MAX_MARGIN = 65534;     // vertical distances are kept in 16 bits (65535: no foreground within the window)
 
-__global__ void k_edt_cols(const double* __restrict__ y, int H, int W, int Mi, uint8_t* __restrict__ g)
+__global__ void k_edt_cols(const double* __restrict__ y, int H, int W, int Mi, uint16_t* __restrict__ g)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
     if (c >= W) return;
-    int best = 255;
+    int best = 65535;
     if (!(y[(size_t)r * W + c] <= 0)) best = 0;              // scipy: the zero elements of (y <= 0)
     else {
         for (int d = 1; d <= Mi; ++d) {
@@ -28,11 +28,11 @@ __global__ void k_edt_cols(const double* __restrict__ y, int H, int W, int Mi, u
             if (up || dn) { best = d; break; }
         }
     }
-    g[(size_t)r * W + c] = (uint8_t)best;
+    g[(size_t)r * W + c] = (uint16_t)best;
 }
 
 // margin < 0 stands for +inf (every masked pixel is usable)
-__global__ void k_edt_rows(const uint8_t* __restrict__ g, const uint8_t* __restrict__ ymask, const int32_t* __restrict__ atoms, int H, int W,
+__global__ void k_edt_rows(const uint16_t* __restrict__ g, const uint8_t* __restrict__ ymask, const int32_t* __restrict__ atoms, int H, int W,
                            int Mi, double margin, int n_labels, int32_t* __restrict__ atoms_out, unsigned long long* __restrict__ count,
                            int32_t* __restrict__ box)
 {
@@ -46,7 +46,7 @@ __global__ void k_edt_rows(const uint8_t* __restrict__ g, const uint8_t* __restr
             const int cc = c + dc;
             if (cc < 0 || cc >= W) continue;
             const int gv = g[(size_t)r * W + cc];
-            if (gv == 255) continue;
+            if (gv == 65535) continue;
             const long long d2 = (long long)dc * dc + (long long)gv * gv;
             if (best < 0 || d2 < best) best = d2;
         }

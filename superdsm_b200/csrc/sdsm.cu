@@ -124,14 +124,15 @@ extern "C" int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_
     if (!ctx || !d_y || !d_ymask || !d_atoms || !d_atoms_out || !d_count || !d_box || !d_scratch || H < 2 || W < 2 || n_labels < 0) return SDSM_E_ARG;
     if (background_margin != background_margin || background_margin < 0) { ctx->err = "background_margin must be >= 0"; return SDSM_E_ARG; }
     const bool unbounded = background_margin > 1e300;
-    if (!unbounded && background_margin > EDT_MAX_MARGIN) { ctx->err = "background_margin > 254 is not implemented"; return SDSM_E_UNSUPPORTED; }
+    // a margin beyond the image's extent reaches every pixel that has any foreground pixel at all: the window is the image
+    const int Mi = unbounded ? 0 : (int)(background_margin < (double)(H + W) ? background_margin : (double)(H + W));            // floor
+    if (Mi > EDT_MAX_MARGIN) { ctx->err = "background_margin > 65534 on an image that large is not implemented"; return SDSM_E_UNSUPPORTED; }
     cudaStream_t stream = (cudaStream_t)stream_;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-    const int Mi = unbounded ? 0 : (int)background_margin;            // floor
     const dim3 block(128), grid((W + 127) / 128, H);
     k_edt_init<<<(n_labels + 256) / 256, 256, 0, stream>>>(n_labels, H, W, (unsigned long long*)d_count, d_box);
-    if (!unbounded) { k_edt_cols<<<grid, block, 0, stream>>>(d_y, H, W, Mi, d_scratch); ctx->launches++; }
-    k_edt_rows<<<grid, block, 0, stream>>>(d_scratch, d_ymask, d_atoms, H, W, Mi, unbounded ? -1.0 : background_margin, n_labels, d_atoms_out,
+    if (!unbounded) { k_edt_cols<<<grid, block, 0, stream>>>(d_y, H, W, Mi, (uint16_t*)d_scratch); ctx->launches++; }
+    k_edt_rows<<<grid, block, 0, stream>>>((const uint16_t*)d_scratch, d_ymask, d_atoms, H, W, Mi, unbounded ? -1.0 : background_margin, n_labels, d_atoms_out,
                                            (unsigned long long*)d_count, d_box);
     ctx->launches += 2;
     CUDA_TRY(ctx, cudaGetLastError());

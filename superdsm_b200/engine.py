@@ -241,7 +241,7 @@ class Engine(object):
         if image is None or image.shape != (H, W):
             image = DeviceImage((H, W))
             dev = lambda n: torch.empty(n, dtype=torch.uint8, device=self.device)
-            image.d_y, image.d_mask, image.d_atoms_in, image.d_atoms, image.d_scratch = dev(8 * H * W), dev(H * W), dev(4 * H * W), dev(4 * H * W), dev(H * W)
+            image.d_y, image.d_mask, image.d_atoms_in, image.d_atoms, image.d_scratch = dev(8 * H * W), dev(H * W), dev(4 * H * W), dev(4 * H * W), dev(2 * H * W)
         self._to_device('y', y_model, image.d_y)
         return self.update_labels(image, y_mask, atoms, background_margin)
 

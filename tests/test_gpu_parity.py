@@ -261,7 +261,7 @@ def test_other_baseline_configs(eng, name, kw):
         assert np.array_equal(frag, ref['fg_fragment']) and np.array_equal(off, ref['fg_offset'])
 
 
-@pytest.mark.parametrize('name,margin', [('toy', 9), ('toy', 6.5), ('toy', np.inf), ('gowt1', 16), ('gowt1', 16.97), ('bbbc039', 20), ('bbbc039', 0)])
+@pytest.mark.parametrize('name,margin', [('toy', 9), ('toy', 6.5), ('toy', np.inf), ('toy', 300.5), ('toy', 1e9), ('gowt1', 16), ('gowt1', 16.97), ('bbbc039', 20), ('bbbc039', 0)])
 def test_device_image_preparation_bit_exact(eng, name, margin):
     """sdsm_prepare_image (windowed exact EDT on the device) against the numpy/scipy statement of objects.py:126-127:
     masked atoms map, per-atom pixel counts and bounding boxes -- bit-exact."""

@@ -106,10 +106,11 @@ def offset_image(g_raw, sigma1=math.sqrt(2), sigma2=40, offset_clip=3):
     return ndi.gaussian_filter(g_raw, sigma1) - offset
 
 
-def make_atoms(y, seeds, oversegment=1, rng=None, min_fg_pixels=30, max_irregularity=0.2):
+def make_atoms(y, seeds, oversegment=1, rng=None, min_fg_pixels=30, max_irregularity=0.2, fast=False):
     """Partitions the image into clusters (nearest foreground component) and atoms (nearest seed inside the cluster).
 
-    Returns (y_mask, atoms int32 HxW with labels 1..A, cluster label per atom, adjacency dict label -> set).
+    Returns (y_mask, atoms int32 HxW with labels 1..A, cluster label per atom, adjacency dict label -> set, clusters map,
+    seed point of every atom in label order).
     """
     rng = rng or np.random.default_rng(0)
     H, W = y.shape
@@ -128,7 +129,7 @@ def make_atoms(y, seeds, oversegment=1, rng=None, min_fg_pixels=30, max_irregula
         y_mask[lut[comp]] = False
     markers = np.where(y_mask, comp, 0)
     if markers.max() == 0:
-        return y_mask, np.zeros(y.shape, np.int32), np.zeros(0, int), {}
+        return y_mask, np.zeros(y.shape, np.int32), np.zeros(0, int), {}, np.zeros(y.shape, np.int32), []
     idx = ndi.distance_transform_edt(markers == 0, return_distances=False, return_indices=True)
     clusters = markers[idx[0], idx[1]]
     # seeds: given nuclei centres (those lying on foreground) plus, per cluster without any, its brightest pixel
@@ -141,17 +142,37 @@ def make_atoms(y, seeds, oversegment=1, rng=None, min_fg_pixels=30, max_irregula
             if 0 <= rr < H and 0 <= cc < W and markers[rr, cc] == markers[r, c]: extra.append((rr, cc))
     pts = pts + extra
     have = set(int(markers[r, c]) for r, c in pts)
-    for lab in np.unique(markers):
-        if lab == 0 or int(lab) in have: continue
-        pos = ndi.maximum_position(y, markers, lab)
-        pts.append((int(pos[0]), int(pos[1])))
+    if fast:
+        missing = [int(lab) for lab in np.unique(markers) if lab != 0 and int(lab) not in have]
+        if missing:
+            for pos in ndi.maximum_position(y, markers, index=missing): pts.append((int(pos[0]), int(pos[1])))
+    else:
+        for lab in np.unique(markers):
+            if lab == 0 or int(lab) in have: continue
+            pos = ndi.maximum_position(y, markers, lab)
+            pts.append((int(pos[0]), int(pos[1])))
     pts = sorted(set(pts))
     seed_map = np.zeros(y.shape, np.int32)
     for k, (r, c) in enumerate(pts, start=1): seed_map[r, c] = k
     # nearest seed of the same cluster: a Voronoi partition per cluster
     atoms = np.zeros(y.shape, np.int32)
     seed_cluster = np.array([clusters[r, c] for r, c in pts])
-    for lab in np.unique(clusters):
+    if fast:
+        # the same partition computed on the bounding box of every cluster (large images: the loop below works on full frames)
+        by_cluster = {}
+        for k, lab in enumerate(seed_cluster): by_cluster.setdefault(int(lab), []).append(k)
+        for lab, sl in enumerate(ndi.find_objects(clusters), start=1):
+            if sl is None or lab not in by_cluster: continue
+            sel = by_cluster[lab]
+            region = clusters[sl] == lab
+            if len(sel) == 1:
+                atoms[sl][region] = sel[0] + 1
+                continue
+            sub = np.ones(region.shape, bool)
+            for k in sel: sub[pts[k][0] - sl[0].start, pts[k][1] - sl[1].start] = False
+            idx2 = ndi.distance_transform_edt(sub, return_distances=False, return_indices=True)
+            atoms[sl][region] = seed_map[sl][idx2[0][region], idx2[1][region]]
+    for lab in (np.unique(clusters) if not fast else []):
         sel = np.nonzero(seed_cluster == lab)[0]
         region = clusters == lab
         if len(sel) == 1:
@@ -177,7 +198,7 @@ def make_atoms(y, seeds, oversegment=1, rng=None, min_fg_pixels=30, max_irregula
             if atom_cluster[u] == atom_cluster[v]:
                 adjacency[int(u)].add(int(v))
                 adjacency[int(v)].add(int(u))
-    return y_mask, atoms, atom_cluster[1:], adjacency
+    return y_mask, atoms, atom_cluster[1:], adjacency, clusters.astype(np.int32), [pts[int(k) - 1] for k in labels]
 
 
 def enumerate_candidates(atom_cluster, adjacency, max_set_size=3, max_candidates=None):
@@ -221,7 +242,7 @@ def make_workload(name, oversegment=2, max_set_size=3, max_candidates=None, seed
     scale = dsm_kwargs.pop('scale')
     dsm_cfg = dsm_config(scale, **dsm_kwargs)
     y = offset_image(g_raw, sigma2=(40 if scale is None else scale))
-    y_mask, atoms, atom_cluster, adjacency = make_atoms(y, seeds, oversegment, np.random.default_rng(spec['seed'] + 1))
+    y_mask, atoms, atom_cluster, adjacency, clusters, atom_seeds = make_atoms(y, seeds, oversegment, np.random.default_rng(spec['seed'] + 1))
     footprints = enumerate_candidates(atom_cluster, adjacency, max_set_size, max_candidates)
     return dict(name=name, g_raw=g_raw, y=y, y_mask=y_mask, atoms=atoms, footprints=footprints, dsm_cfg=dsm_cfg,
-                adjacency=adjacency, atom_cluster=atom_cluster)
+                adjacency=adjacency, atom_cluster=atom_cluster, clusters=clusters, atom_seeds=atom_seeds)
