@@ -31,26 +31,41 @@ if ROOT not in sys.path: sys.path.insert(0, ROOT)
 
 WORKLOAD = 'gowt1'
 WORKLOAD_DESC = 'GOWT1-shaped 1024x1024 synthetic nuclei image (BASELINE config 1): atoms + universes + adjacent-atom sets, AF_scale 42.43'
-# the other BASELINE configurations (parity-test cases; `--workload` times them, the default stays the config the metric is quoted on)
+# the other BASELINE configurations (`--workload` times them; the default stays the config the metric is quoted on)
 OTHER_WORKLOADS = {
     'bbbc039': ('BBBC039-shaped 520x696 image, default configuration (BASELINE config 0)', dict()),
     'nih3t3': ('NIH3T3-shaped 1344x1024 image, clustered nuclei, strong inhomogeneity (BASELINE config 2)', dict()),
     'tiled': ('1024x1024 crop of the 4096x4096 tiled field, 1250 nuclei, AF_scale 10 (BASELINE config 4)', dict(shape=(1024, 1024), n=1250)),
+    'batch': ('batch of GOWT1-shaped 1024x1024 images (BASELINE config 3, seeds 1000...): image-sharded over the ranks, K images per launch', dict()),
+    'tiled4k': ('4096x4096 tiled field, ~20k nuclei, AF_scale 10 (BASELINE config 4): ONE image, candidates sharded over the ranks (LPT), results gathered on the host', dict()),
 }
 
 
-def make_workload(rank, args):
+def make_workload(rank, args, seed=None):
     from workloads import synth
     global WORKLOAD_DESC
+    if args.workload == 'tiled4k':
+        WORKLOAD_DESC = OTHER_WORKLOADS['tiled4k'][0]
+        spec = dict(synth.WORKLOADS['tiled4k'])
+        if args.field: spec['shape'], spec['n'] = (args.field, args.field), int(20000 * (args.field / 4096.) ** 2)
+        g_raw, seeds, _ = synth.make_image(**spec)
+        cfg = synth.dsm_config(10, alpha=3.3e-4 * 100)
+        y = synth.offset_image(g_raw, sigma2=10)
+        y_mask, atoms, atom_cluster, adjacency, clusters, atom_seeds = synth.make_atoms(y, seeds, 2, np.random.default_rng(spec['seed'] + 1), fast=True)
+        fps = synth.enumerate_candidates(atom_cluster, adjacency, 3, args.max_candidates)
+        return dict(name='tiled4k', y=y, y_mask=y_mask, atoms=atoms, footprints=fps, dsm_cfg=cfg)
+    if args.workload == 'batch':
+        WORKLOAD_DESC = OTHER_WORKLOADS['batch'][0]
+        return synth.make_workload(WORKLOAD, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=seed, max_candidates=args.max_candidates)
     if args.workload != WORKLOAD:
         WORKLOAD_DESC, kw = OTHER_WORKLOADS[args.workload]
         name = 'tiled4k' if args.workload == 'tiled' else args.workload
         base = synth.WORKLOADS[name]['seed']
-        return synth.make_workload(name, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=base,
+        return synth.make_workload(name, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=base + rank,
                                    max_candidates=args.max_candidates, **kw)
-    # weak scaling: every rank generates, uploads and solves its own image of the SAME synthetic configuration and seed,
-    # so that the work per GPU is exactly fixed as N grows (different seeds differ by +-10 % in work)
-    return synth.make_workload(WORKLOAD, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=1,
+    # image-sharded: every rank generates, uploads and solves its OWN image of the synthetic configuration (seed 1 + rank:
+    # the images differ by about +-10 % in work, which the max-over-ranks timing shows)
+    return synth.make_workload(WORKLOAD, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=1 + rank,
                                max_candidates=args.max_candidates)
 
 
@@ -170,17 +185,21 @@ class CpuArm(object):
 
 def workload_config(w, world, args):
     """The keys that define the workload: identical in both arms."""
-    return {'workload': WORKLOAD_DESC, 'candidates_per_image': len(w['footprints']), 'images_per_step': world,
-            'candidate_list': f'atoms + universes + adjacent-atom sets up to {args.max_set_size} (oversegment {args.oversegment})',
-            'sharding': 'one image of the same synthetic configuration per rank, no collective',
-            'l2': 'GPU arm: flushed between timed iterations (256 MiB write)'}
+    mode = {'batch': 'batch', 'tiled4k': 'sharded'}.get(args.workload, 'single')
+    sharding = {'single': 'image-sharded: one image per rank (seed 1 + rank), one launch per image, no collective',
+                'batch': f'image-sharded: {args.images} images per rank and launch (seeds 1000 + rank * {args.images} ...), no collective',
+                'sharded': 'candidate-sharded: one image replicated on every rank, candidates split by cost (LPT), packed results gathered on the host (gloo), no collective on the data path'}[mode]
+    return {'workload': WORKLOAD_DESC, 'candidates_per_image': len(w['footprints']),
+            'images_per_step': {'single': world, 'batch': world * args.images, 'sharded': 1}[mode],
+            'candidate_list': f'atoms + universes + adjacent-atom sets up to {3 if mode == "sharded" else args.max_set_size} (oversegment {2 if mode == "sharded" else args.oversegment})',
+            'sharding': sharding, 'l2': 'GPU arm: flushed between timed iterations (256 MiB write)'}
 
 
 def run_reference(args):
     rank = int(os.environ.get('RANK', 0))
     if rank != 0: return
     cores = os.cpu_count() or 1
-    w = make_workload(0, args)
+    w = make_workload(0, args, seed=1000)
     arm = CpuArm(w, cores, sample=max(16, min(2 * cores, 64)))
     est, walls = [], []
     t_begin = time.perf_counter()
@@ -223,12 +242,33 @@ def run_gpu(args):
     from superdsm_b200 import _lib
     from tests.compat.refshim import Image, Object
     from superdsm_b200.objects import compute_objects, forget_images, get_engine
-    w = make_workload(rank, args)
-    fps = w['footprints']
     eng = get_engine(local_rank)
-    eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
-    eng.set_params(w['dsm_cfg'])
-    handle = eng.prepare(fps)
+    gloo = dist.new_group(backend='gloo') if world > 1 else None      # host-side result gather of the candidate-sharded mode
+    mode = {'batch': 'batch', 'tiled4k': 'sharded'}.get(args.workload, 'single')
+    if mode == 'batch':
+        # K images per rank and launch, distinct seeds over all ranks (BASELINE config 3: seeds 1000 ...)
+        ws = [make_workload(rank, args, seed=1000 + rank * args.images + i) for i in range(args.images)]
+        w = ws[0]
+        images = [eng.upload_image(wi['y'], wi['y_mask'], wi['atoms'], wi['dsm_cfg']['background_margin']) for wi in ws]
+        eng.bind_images(images)
+        eng.set_params(w['dsm_cfg'])
+        fps = [fp for wi in ws for fp in wi['footprints']]
+        handle = eng.prepare([wi['footprints'] for wi in ws], multi=True)
+        n_images = len(ws)
+    else:
+        w = make_workload(rank, args)
+        fps = w['footprints']
+        all_fps = fps
+        eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
+        eng.set_params(w['dsm_cfg'])
+        if mode == 'sharded':
+            # ONE image on every rank, the candidates split by cost (LPT): strong scaling
+            from superdsm_b200.engine import lpt_shards
+            from superdsm_b200.sharding import candidate_costs_from_counts
+            mine = lpt_shards(candidate_costs_from_counts(all_fps, eng.atom_count), world)[rank]
+            fps = [all_fps[i] for i in mine]
+        handle = eng.prepare(fps)
+        n_images = 1
     stream = torch.cuda.current_stream(device)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)        # > 126 MB L2
 
@@ -263,11 +303,12 @@ def run_gpu(args):
         raise SystemExit(f'persistent solver did not finish: {stats}')
     o = handle['out']
     n = handle['n']
+    pixels_local = int(handle['cands']['n'].sum())
     info = o['info'][:32 * n].cpu().numpy().view(np.int32).reshape(n, 8)
     status = o['status'][:4 * n].cpu().numpy().view(np.int32)
 
     class _R(object): pass
-    r = _R(); r.cands = handle['cands']; r.info = info
+    r = _R(); r.cands = handle['cands'].copy(); r.info = info
     alg_bytes, alg_flops = algorithmic_work(r)
     optimal = int((status == _lib.ST_OPTIMAL).sum())
     n_errors = int((status >= _lib.ST_ERROR).sum())
@@ -275,18 +316,37 @@ def run_gpu(args):
         # CvxprogError candidates (both elliptical passes failed, objects.py:351-353) are legitimate results of the reference
         # too, but its compute_objects raises on them: the headline workload has none, the others drop them from the e2e leg
         if args.workload == WORKLOAD: raise SystemExit(f'solver reported errors: {np.bincount(status)}')
+        if mode != 'single': raise SystemExit(f'solver reported errors in a {mode} workload: {np.bincount(status)}')
         fps = [fp for fp, st in zip(fps, status) if st < _lib.ST_ERROR]
 
     # ---- end to end through the public API (`e2e`): host arrays in, Objects out ----
-    y_img = Image(w['y'], w['y_mask'])
+    if mode == 'batch':
+        from superdsm_b200.objects import compute_objects_multi
 
-    def e2e_step():
-        objs = []
-        for fp in fps:
-            ob = Object(); ob.footprint = set(fp); objs.append(ob)
-        forget_images()                                                # every step uploads its image again
-        compute_objects(objs, y_img, w['atoms'], w['dsm_cfg'], None)
-        return objs
+        def e2e_step():
+            jobs = [([Object(fp) for fp in wi['footprints']], Image(wi['y'], wi['y_mask']), wi['atoms']) for wi in ws]
+            compute_objects_multi(jobs, w['dsm_cfg'])                  # uploads every image, one launch, Objects out
+            return [ob for objs, _, _ in jobs for ob in objs]
+    elif mode == 'sharded':
+        from superdsm_b200.sharding import compute_objects_sharded
+        del handle
+        torch.cuda.empty_cache()
+        y_img = Image(w['y'], w['y_mask'])
+        keep = [fp for fp in all_fps]
+
+        def e2e_step():
+            objs = [Object(fp) for fp in keep]
+            forget_images()
+            compute_objects_sharded(objs, y_img, w['atoms'], w['dsm_cfg'], None, group=gloo)     # every rank ends with all results
+            return objs
+    else:
+        y_img = Image(w['y'], w['y_mask'])
+
+        def e2e_step():
+            objs = [Object(fp) for fp in fps]
+            forget_images()                                                # every step uploads its image again
+            compute_objects(objs, y_img, w['atoms'], w['dsm_cfg'], None)
+            return objs
     e2e_step()
     h2d0, d2h0 = eng.h2d_bytes, eng.d2h_bytes
     barrier()
@@ -301,13 +361,14 @@ def run_gpu(args):
     assert all(np.isfinite(ob.energy) for ob in objs)
 
     # ---- max over ranks ----
-    t = torch.tensor([total_ms, e2e_s * 1e3, float(len(fps))], dtype=torch.float64, device=device)
+    t = torch.tensor([total_ms, e2e_s * 1e3, float(len(fps)), float(n_images)], dtype=torch.float64, device=device)
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        total_ms_max, e2e_ms_max, cand_total = float(tmax[0]), float(tmax[1]), float(tsum[2])
+        total_ms_max, e2e_ms_max, cand_total, img_total = float(tmax[0]), float(tmax[1]), float(tsum[2]), float(tsum[3])
     else:
-        total_ms_max, e2e_ms_max, cand_total = total_ms, e2e_s * 1e3, float(len(fps))
+        total_ms_max, e2e_ms_max, cand_total, img_total = total_ms, e2e_s * 1e3, float(len(fps)), float(n_images)
+    if mode == 'sharded': img_total = 1.0
 
     if rank == 0:
         peaks = {}
@@ -327,11 +388,12 @@ def run_gpu(args):
         value = cand_total * args.steps / (total_ms_max * 1e-3)
         line = {
             'metric': 'dsm_candidate_solves_per_s', 'value': value, 'unit': 'candidate-solves/s', 'n_gpus': world, 'steps': args.steps,
-            'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'strong' if mode == 'sharded' else 'weak', 'vs_baseline': None,
             'dtype': 'f64', 'data': 'synthetic',
             'config': workload_config(w, world, args),
-            'stats': {'pixels_per_step_per_gpu': int(handle['cands']['n'].sum()), 'optimal': optimal, 'errors': n_errors,
-                      'images_per_s': world * args.steps / (total_ms_max * 1e-3)},
+            'stats': {'pixels_per_step_per_gpu': pixels_local, 'optimal': optimal, 'errors': n_errors, 'candidates_per_step': int(cand_total),
+                      'images_per_step': int(img_total), 'images_per_s': img_total * args.steps / (total_ms_max * 1e-3),
+                      'e2e_images_per_s': img_total * e2e_steps / (e2e_ms_max * 1e-3)},
             'e2e': {'value': cand_total * e2e_steps / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
                     'd2h_bytes_per_step': int(d2h), 'includes': 'pinned H2D of y, mask, atoms; device EDT + atom statistics; descriptors; solve; D2H of results; Object materialisation'},
             'gpu_launches': int(gpu_launches),
@@ -371,6 +433,8 @@ def main():
     ap.add_argument('--max-set-size', type=int, default=4)
     ap.add_argument('--max-candidates', type=int, default=None)
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--images', type=int, default=8, help='--workload batch: images per rank and launch')
+    ap.add_argument('--field', type=int, default=0, help='--workload tiled4k: edge of the field in pixels (default 4096)')
     ap.add_argument('--workload', default=WORKLOAD, choices=[WORKLOAD] + sorted(OTHER_WORKLOADS))
     args = ap.parse_args()
     if args.impl == 'reference': run_reference(args)

@@ -21,6 +21,9 @@ if ROOT not in sys.path: sys.path.insert(0, ROOT)
 from oracle.make_full_golden import WORKLOAD_ARGS, mask_hash     # noqa: E402
 
 OUT = os.path.join(ROOT, 'tests', 'golden')
+#: workload -> arguments of workloads.synth.make_workload (only image and atoms matter: the stage enumerates the candidates itself)
+GEM_ARGS = {'toy': dict(name='toy', oversegment=2, max_set_size=1), 'gowt1': dict(WORKLOAD_ARGS['gowt1']),
+            'bbbc039': dict(name='bbbc039', oversegment=2, max_set_size=1, seed=39)}
 #: workload -> beta of the GEM stage (globalenergymin.py:144; AF_beta x scale^2 under automation)
 BETA = {'bbbc039': 0.0, 'gowt1': 1188.0, 'toy': 150.0}
 _job = None
@@ -54,8 +57,7 @@ def main():
     from workloads.synth import make_workload
     wname = sys.argv[1]
     procs = int(sys.argv[2]) if len(sys.argv) > 2 else (os.cpu_count() or 1)
-    args = dict(WORKLOAD_ARGS[wname]) if wname in WORKLOAD_ARGS else dict(name=wname, oversegment=2, max_set_size=1)
-    w = make_workload(**args)
+    w = make_workload(**GEM_ARGS[wname])
     ref = ref_gem_harness.load()
     _job = (w['y'], w['y_mask'], w['atoms'], w['dsm_cfg'])
     pool = mp.get_context('fork').Pool(procs)

@@ -52,13 +52,13 @@ def test_restated_set_cover_reproduces_the_reference_cover(name):
 @pytest.mark.parametrize('name', ['toy', 'bbbc039', 'gowt1'])
 def test_gem_stream_through_the_gpu_seam(name):
     if not os.path.isfile(os.path.join(GOLDEN, f'gem_{name}.npz')): pytest.skip('fixture not generated')
-    from oracle.make_full_golden import WORKLOAD_ARGS, mask_hash
-    from oracle.make_gem_golden import object_stats
+    from oracle.make_full_golden import mask_hash
+    from oracle.make_gem_golden import GEM_ARGS, object_stats
     from superdsm_b200.objects import compute_objects
     from tests.compat.refshim import Image, Object
     from workloads.synth import make_workload
     z, fps, cover = _load(name)
-    w = make_workload(**(WORKLOAD_ARGS[name] if name in WORKLOAD_ARGS else dict(name=name, oversegment=2, max_set_size=1)))
+    w = make_workload(**GEM_ARGS[name])
     assert float(w['y'].sum()) == float(z['image_checksum'])
     y = Image(w['y'], w['y_mask'])
     scale = float(w['dsm_cfg']['scale'])
