@@ -53,6 +53,7 @@ class NormalizedEnergyComputer(object):
         cfg['smooth_amount'] = np.inf
         self.cfg = cfg
         self.cache = {}
+        self.solved = {}                             # key -> (request, cvxopt status bits of the fit): diagnostics
         self.image = None
         self.uploads = 0                             # uploads of y (stays 1: the rounds only send label maps)
         self.launches = 0                            # solver batches
@@ -81,6 +82,7 @@ class NormalizedEnergyComputer(object):
             if st == _lib.ST_ERROR: out.append(CvxprogError('elliptical initialisation failed'))
             elif st == _lib.ST_BADREGION: raise SolverError('region mismatch between host and device')
             else: out.append(float(res.energy[k]) / float(res.cands['n'][k]))
+            self.solved[reqs[k][1].key()] = (reqs[k][1], int(res.info[k, 5]), res.info[k, 1:4].copy())
         return out
 
     def compute(self, requests):

@@ -83,6 +83,7 @@ struct CState {
     double bt, uz0, vt, gux, gux_res, gex;
     double sigma, eta, step, dt, dz, ds, dsdz, dz2, ds2;
     double val1, psi_last, energy;
+    double f_trial, psi_trial;             // scaled value / psi of the last line-search trial (= the next iterate when it is accepted)
     unsigned long long ns_ctrl;            // diagnostics: time spent in this candidate's control tasks so far (ns)
     int32_t pc, stage, iters, relaxed, pass, use_xi;
     int32_t req_vec, req_gvec, req_h;      // the pending evaluation: point, where the gradient goes, Hessian wanted
@@ -93,7 +94,8 @@ struct CState {
 struct EvalReq {
     const double* x;       // point to evaluate (6 + m values, or 6)
     double hfac;           // factor of the Hessian rows the T_HG tasks write: z * scale / n (objects.py:380), or 1 (diagnostics)
-    int32_t want_h, use_xi;
+    int32_t want_h, use_xi;  // want_h: 0 value + gradient, 1 value + gradient + Hessian, 2 Hessian only (value and gradient at this
+                             // point are already known: the accepted trial of the line search was evaluated at it)
     int32_t cpt, cpw;      // non-empty cells per CTA-wide evaluation task (chains that stay in one CTA, diagnostics) / per warp item
 };
 

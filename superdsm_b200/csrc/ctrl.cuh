@@ -179,6 +179,32 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
     return sc * psi;
 }
 
+// Hessian-only evaluations (EvalReq.want_h == 2): only the theta-theta block is left to gather (the other rows are assembled by
+// the T_HG tasks); value and gradient at this point are the accepted line-search trial's.
+template <int BLOCK>
+__device__ void gather_hessian_block(const Prob& P, Sm& sm, double hz, int N)
+{
+    const int tid = threadIdx.x;
+    double acc[21];
+#pragma unroll
+    for (int k = 0; k < 21; ++k) acc[k] = 0;
+    for (int i = tid; i < P.n_ne; i += BLOCK) {
+        const double* sh = P.scrH + (size_t)P.clist[i] * SCRH;
+#pragma unroll
+        for (int k = 0; k < 21; ++k) acc[k] += sh[k];
+    }
+    __syncthreads();
+    block_sum<BLOCK, 21>(acc, sm.red_part, sm.red_out);
+    if (tid < 21) {
+        int a = 0, t = tid;
+        while (t >= a + 1) { t -= a + 1; ++a; }
+        const double v = hz * P.scale_cp * sm.red_out[tid];
+        P.H[a * N + t] = v;
+        P.H[t * N + a] = v;
+    }
+    __syncthreads();
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // T_HG tasks: rows 6.. of the Hessian (the xi-theta and xi-xi blocks, dsm.py:369-374) of a candidate that asked for one.
 // One warp per grid point j: it visits the <= 25 cells that see j in a fixed order and adds their local
@@ -783,7 +809,13 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
     if (S.pc != PC_START && S.pc != PC_TRACESTART) {
         double psi = 0.0;
         double* gout = P.V + (size_t)S.req_gvec * ld;
-        if (!S.use_xi) f0 = S.req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
+        if (S.req_h == 2) {
+            // Hessian only: value and gradient are those of the accepted trial (same point, same bits: PC_ACCEPT)
+            gather_hessian_block<BLOCK>(P, sm, S.z, S.use_xi ? P.N : 6);
+            f0 = S.f_trial;
+            psi = S.psi_trial;
+        }
+        else if (!S.use_xi) f0 = S.req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
         else {
             const double* xe = P.V + (size_t)S.req_vec * ld;
             f0 = S.req_h ? gather_cells<BLOCK, true>(P, sm, xe, gout, S.z, &psi) : gather_cells<BLOCK, false>(P, sm, xe, gout, S.z, &psi);
@@ -969,6 +1001,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
         }
         case PC_TRIAL: {                     // F and Df at x + step dx are in (f0, ng)
             const double step = S.step;
+            S.f_trial = f0; S.psi_trial = S.psi_last;
             const double newt = S.t + step * S.dt, newz = S.z + step * S.dz2, news = S.s + step * S.ds2;
             const double newf = f0 - newt;
             double ngg;
@@ -1041,8 +1074,12 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             S.s = S.lm * S.d;
             S.z = S.lm / S.d;
             S.iters += 1;
+            // x is the accepted trial point (the same expression in the same arithmetic as PC_TRIALREQ), where value and gradient
+            // are known (S.f_trial, ng): the reference evaluates F there again -- with identical results, dsm.py:388-418 caches them
+            // -- so only the Hessian is asked for
+            for (int i = tid; i < Nc; i += BLOCK) g[i] = ng[i];
             __syncthreads();
-            REQUEST(V_X, V_G, 1, PC_TOP, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+            REQUEST(V_X, V_G, 2, PC_TOP, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
             break;
         }
         // ---- the driver around the solves: objects.py:321-358 (elliptical initialisation), 361-412 (cvxprog) ----

@@ -456,7 +456,8 @@ __device__ __noinline__ void cell_hessian(const double* __restrict__ py, const u
         }
 }
 
-template <bool HESS>
+// MODE 0: value + gradient; 1: value + gradient + local Hessian; 2: local Hessian only
+template <int MODE>
 __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, const uint32_t* __restrict__ prc, const float* __restrict__ gcell,
                                              int npix, uint32_t am, const double* __restrict__ xr, const double* __restrict__ xc,
                                              const double* x, double tol, double* Tt, int* slotj,
@@ -468,15 +469,17 @@ __device__ __forceinline__ void eval_cell_xi(const double* __restrict__ py, cons
     __syncwarp();
     XI[lane] = lane < na ? x[6 + slotj[lane]] : 0.0;  // the xi values this cell sees (zero-padded: rows are read in groups of four)
     __syncwarp();
-    const double2 tot = cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI, slotj + SLOTJ_INTS);
-    if (lane < 6) sg[lane] = tot.x;
-    if (lane == 6) sg[31] = tot.x;
-    // xi gradient: straight into the slot that grid point slotj[a] keeps for this cell (seen from the grid point's cell, this
-    // cell sits at the mirrored neighbour position), so that the control task sums 25 contiguous numbers per grid point
-    // instead of chasing cell -> mask -> scratch entry
-    if (lane < na) xig[(size_t)slotj[lane] * NSLOT + (NSLOT - 1 - slotj[32 + lane])] = tot.y;
-    __syncwarp();
-    if (HESS) cell_hessian(py, prc, gcell, npix, na, xr, xc, x, tol, Tt, XI, sh);
+    if (MODE != 2) {
+        const double2 tot = cell_value_grad(py, prc, gcell, npix, na, xr, xc, x, tol, reinterpret_cast<char*>(Tt), XI, slotj + SLOTJ_INTS);
+        if (lane < 6) sg[lane] = tot.x;
+        if (lane == 6) sg[31] = tot.x;
+        // xi gradient: straight into the slot that grid point slotj[a] keeps for this cell (seen from the grid point's cell, this
+        // cell sits at the mirrored neighbour position), so that the control task sums 25 contiguous numbers per grid point
+        // instead of chasing cell -> mask -> scratch entry
+        if (lane < na) xig[(size_t)slotj[lane] * NSLOT + (NSLOT - 1 - slotj[32 + lane])] = tot.y;
+        __syncwarp();
+    }
+    if (MODE != 0) cell_hessian(py, prc, gcell, npix, na, xr, xc, x, tol, Tt, XI, sh);
     __syncwarp();
 }
 
@@ -549,8 +552,9 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     __syncwarp();
     const float* gcell = ws.gval + (size_t)GROW * (pix_off + st);
     double* xig = ws.xig + (size_t)cell_off * NSLOT;
-    if (rq.want_h) eval_cell_xi<true>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
-    else eval_cell_xi<false>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
+    if (rq.want_h == 2) eval_cell_xi<2>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
+    else if (rq.want_h) eval_cell_xi<1>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
+    else eval_cell_xi<0>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
 }
 
 }  // namespace sdsm
