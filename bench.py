@@ -6,8 +6,10 @@
 
 A step = one pass of the hot path (region packing, smooth-matrix construction, elliptical + DSM solves, result
 rasterisation) over every candidate of one synthetic 1024 x 1024 image: atoms, cluster universes and the sets of
-adjacent atoms the GEM stage enumerates.  With N > 1 every rank works on its own image (image-sharded, no collective on
-the data path; weak scaling); `value` = candidates of all ranks / max-over-ranks device time.
+adjacent atoms the GEM stage enumerates.  The steps cycle through a pool of 4 images (seeds 1..4); with N > 1 rank r starts
+at image r, so that at any time the ranks work on different images while every rank does the same work over the timed
+region (image-sharded, no collective on the data path; weak scaling); `value` = candidates of all ranks / max-over-ranks
+device time.  `--workload batch`: K images per launch; `--workload tiled4k`: one 4096 x 4096 field, candidate-sharded (strong).
 """
 import os
 
@@ -63,9 +65,7 @@ def make_workload(rank, args, seed=None):
         base = synth.WORKLOADS[name]['seed']
         return synth.make_workload(name, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=base + rank,
                                    max_candidates=args.max_candidates, **kw)
-    # image-sharded: every rank generates, uploads and solves its OWN image of the synthetic configuration (seed 1 + rank:
-    # the images differ by about +-10 % in work, which the max-over-ranks timing shows)
-    return synth.make_workload(WORKLOAD, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=1 + rank,
+    return synth.make_workload(WORKLOAD, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=1 if seed is None else seed,
                                max_candidates=args.max_candidates)
 
 
@@ -149,26 +149,27 @@ class CpuArm(object):
     """The CPU implementation of the path (the oracle port) on all host cores: one worker process per core, one BLAS thread
     each.  A step times a stratified sample: the candidates are sorted by pixel count and cut into `sample` strata of equal
     size, step k takes member k (mod size) of every stratum, and every measured time stands for its whole stratum, so that
-    the figure is (time for ALL candidates of the image on `cores` cores, perfectly packed) -- candidates / that time."""
+    the figure is (time for ALL candidates of the workload's images on `cores` cores, perfectly packed) -- candidates / that time."""
 
-    def __init__(self, w, cores, sample):
+    def __init__(self, ws, cores, sample):
         import multiprocessing as mp
-        self.w, self.cores = w, cores
-        fps = w['footprints']
-        count = np.bincount(np.asarray(w['atoms']).reshape(-1))
-        npix = np.array([sum(int(count[a]) for a in fp) for fp in fps])
-        order = np.argsort(npix, kind='stable')
-        self.strata = [s for s in np.array_split(order, min(sample, len(fps))) if len(s)]
+        self.ws, self.cores = ws, cores
+        self.items, npix = [], []
+        for wi in ws:
+            count = np.bincount(np.asarray(wi['atoms']).reshape(-1))
+            for fp in wi['footprints']:
+                self.items.append((wi, fp)); npix.append(sum(int(count[a]) for a in fp))
+        order = np.argsort(np.array(npix), kind='stable')
+        self.strata = [s for s in np.array_split(order, min(sample, len(self.items))) if len(s)]
         self.pool = mp.get_context('fork').Pool(cores)
         self.blas_threads = self.pool.apply(_blas_threads)
-        self.n = len(fps)
+        self.n = len(self.items)
 
     def step(self, k):
         """Returns (estimated seconds for the whole candidate list on all cores, wall seconds of this step, core-seconds spent)."""
-        w = self.w
         picks = [int(s[k % len(s)]) for s in self.strata][::-1]              # largest first: better packing of the pool
         weights = [len(s) for s in self.strata][::-1]
-        jobs = [(w['y'], w['y_mask'], w['atoms'], w['footprints'][i], w['dsm_cfg']) for i in picks]
+        jobs = [(self.items[i][0]['y'], self.items[i][0]['y_mask'], self.items[i][0]['atoms'], self.items[i][1], self.items[i][0]['dsm_cfg']) for i in picks]
         t0 = time.perf_counter()
         out = self.pool.map(_cpu_worker, jobs, chunksize=1)
         wall = time.perf_counter() - t0
@@ -185,13 +186,28 @@ class CpuArm(object):
         self.pool.join()
 
 
-def workload_config(w, world, args):
+def pool_size(args):
+    """Images of the default workload's pool: step s of rank r takes image (r + s) mod pool, so that over the timed steps every
+    rank does the same work on different images at any one time."""
+    return max(1, args.pool) if args.workload == WORKLOAD else 1
+
+
+def make_pool(rank, args):
+    if args.workload == WORKLOAD:
+        from workloads import synth
+        return [synth.make_workload(WORKLOAD, oversegment=args.oversegment, max_set_size=args.max_set_size, seed=1 + i,
+                                    max_candidates=args.max_candidates) for i in range(pool_size(args))]
+    return [make_workload(rank, args, seed=1000)]
+
+
+def workload_config(ws, world, args):
     """The keys that define the workload: identical in both arms."""
     mode = {'batch': 'batch', 'tiled4k': 'sharded'}.get(args.workload, 'single')
-    sharding = {'single': 'image-sharded: one image per rank (seed 1 + rank), one launch per image, no collective',
+    P = pool_size(args)
+    sharding = {'single': f'image-sharded: one image per rank and step out of a pool of {P} (seeds 1..{P}; step s of rank r takes image (r + s) mod {P}), one launch per image, no collective',
                 'batch': f'image-sharded: {args.images} images per rank and launch (seeds 1000 + rank * {args.images} ...), no collective',
                 'sharded': 'candidate-sharded: one image replicated on every rank, candidates split by cost (LPT), packed results gathered on the host (gloo), no collective on the data path'}[mode]
-    return {'workload': WORKLOAD_DESC, 'candidates_per_image': len(w['footprints']),
+    return {'workload': WORKLOAD_DESC, 'candidates_per_image': [len(wi['footprints']) for wi in ws] if len(ws) > 1 else len(ws[0]['footprints']),
             'images_per_step': {'single': world, 'batch': world * args.images, 'sharded': 1}[mode],
             'candidate_list': f'atoms + universes + adjacent-atom sets up to {3 if mode == "sharded" else args.max_set_size} (oversegment {2 if mode == "sharded" else args.oversegment})',
             'sharding': sharding, 'l2': 'GPU arm: flushed between timed iterations (256 MiB write)'}
@@ -201,8 +217,8 @@ def run_reference(args):
     rank = int(os.environ.get('RANK', 0))
     if rank != 0: return
     cores = os.cpu_count() or 1
-    w = make_workload(0, args, seed=1000)
-    arm = CpuArm(w, cores, sample=max(16, min(2 * cores, 64)))
+    ws = make_pool(0, args)
+    arm = CpuArm(ws, cores, sample=max(16, min(2 * cores, 64)))
     est, walls = [], []
     t_begin = time.perf_counter()
     for step in range(args.warmup + args.steps):
@@ -213,13 +229,13 @@ def run_reference(args):
         est.append(e); walls.append(wall)
         if time.perf_counter() - t_begin > 200 and len(est) >= 3: break      # time box: a few minutes in all
     arm.close()
-    n = len(w['footprints'])
+    n = arm.n
     value = n * len(est) / float(np.sum(est))
     desc = arm.describe()
     line = {'impl': 'reference', 'metric': 'dsm_candidate_solves_per_s', 'value': value, 'unit': 'candidate-solves/s',
             'n_gpus': args.gpus, 'steps': len(est), 'warmup': args.warmup, 'ms_per_step': 1e3 * float(np.mean(walls)),
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': workload_config(w, max(1, args.gpus), args),
+            'config': workload_config(ws, max(1, args.gpus), args),
             'cpu_baseline': {'value': value, 'unit': 'candidate-solves/s', 'cores': cores, 'blas_threads_per_process': arm.blas_threads,
                              'kind': 'port', 'sample': desc,
                              'note': 'numpy/scipy port of dsm.Energy + restated cvxopt cp (oracle/); the reference needs cvxopt + MKL, unavailable on this box'},
@@ -243,34 +259,41 @@ def run_gpu(args):
 
     from superdsm_b200 import _lib
     from tests.compat.refshim import Image, Object
-    from superdsm_b200.objects import compute_objects, forget_images, get_engine
+    from superdsm_b200.objects import compute_objects, compute_objects_multi, forget_images, get_engine
     eng = get_engine(local_rank)
     gloo = dist.new_group(backend='gloo') if world > 1 else None      # host-side result gather of the candidate-sharded mode
     mode = {'batch': 'batch', 'tiled4k': 'sharded'}.get(args.workload, 'single')
+
+    # ---- the units of work of this rank: `units[i]` = (images bound for the launch, prepared handle, footprint lists) ----
+    units = []
     if mode == 'batch':
         # K images per rank and launch, distinct seeds over all ranks (BASELINE config 3: seeds 1000 ...)
         ws = [make_workload(rank, args, seed=1000 + rank * args.images + i) for i in range(args.images)]
-        w = ws[0]
         images = [eng.upload_image(wi['y'], wi['y_mask'], wi['atoms'], wi['dsm_cfg']['background_margin']) for wi in ws]
         eng.bind_images(images)
-        eng.set_params(w['dsm_cfg'])
-        fps = [fp for wi in ws for fp in wi['footprints']]
-        handle = eng.prepare([wi['footprints'] for wi in ws], multi=True)
-        n_images = len(ws)
+        eng.set_params(ws[0]['dsm_cfg'])
+        units.append(dict(images=images, ws=ws, handle=eng.prepare([wi['footprints'] for wi in ws], multi=True)))
+    elif mode == 'sharded':
+        # ONE image on every rank, the candidates split by cost (LPT): strong scaling
+        from superdsm_b200.engine import lpt_shards
+        from superdsm_b200.sharding import candidate_costs_from_counts
+        ws = [make_workload(rank, args)]
+        all_fps = ws[0]['footprints']
+        image = eng.upload_image(ws[0]['y'], ws[0]['y_mask'], ws[0]['atoms'], ws[0]['dsm_cfg']['background_margin'])
+        eng.bind_images([image])
+        eng.set_params(ws[0]['dsm_cfg'])
+        mine = lpt_shards(candidate_costs_from_counts(all_fps, image.atom_count), world)[rank]
+        shard = dict(ws[0]); shard['footprints'] = [all_fps[i] for i in mine]
+        units.append(dict(images=[image], ws=[shard], handle=eng.prepare(shard['footprints'])))
     else:
-        w = make_workload(rank, args)
-        fps = w['footprints']
-        all_fps = fps
-        eng.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
-        eng.set_params(w['dsm_cfg'])
-        if mode == 'sharded':
-            # ONE image on every rank, the candidates split by cost (LPT): strong scaling
-            from superdsm_b200.engine import lpt_shards
-            from superdsm_b200.sharding import candidate_costs_from_counts
-            mine = lpt_shards(candidate_costs_from_counts(all_fps, eng.atom_count), world)[rank]
-            fps = [all_fps[i] for i in mine]
-        handle = eng.prepare(fps)
-        n_images = 1
+        ws = make_pool(rank, args)
+        eng.set_params(ws[0]['dsm_cfg'])
+        for wi in ws:
+            image = eng.upload_image(wi['y'], wi['y_mask'], wi['atoms'], wi['dsm_cfg']['background_margin'])
+            eng.bind_images([image])
+            units.append(dict(images=[image], ws=[wi], handle=eng.prepare(wi['footprints'])))
+    P = len(units)
+    unit_of = lambda step: units[(rank + step) % P]
     stream = torch.cuda.current_stream(device)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)        # > 126 MB L2
 
@@ -278,19 +301,22 @@ def run_gpu(args):
         if world > 1: dist.barrier()
         torch.cuda.synchronize(device)
 
+    def launch(u):
+        eng.bind_images(u['images'])                                        # host-side: the image set travels as a kernel argument
+        eng.run_prepared(u['handle'], stream)
+
     # ---- device-resident throughput (`value`) ----
-    for _ in range(args.warmup):
-        eng.run_prepared(handle, stream)
+    for s_ in range(args.warmup): launch(unit_of(s_))
     barrier()
     launches0 = eng.launch_count
     sampler = ClockSampler(local_rank)
     events = []
     barrier()
-    for _ in range(args.steps):
+    for s_ in range(args.steps):
         flush.fill_(1)                                                      # L2 flush between timed iterations
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        eng.run_prepared(handle, stream)
+        launch(unit_of(args.warmup + s_))
         e1.record(stream)
         events.append((e0, e1))
     barrier()
@@ -298,90 +324,99 @@ def run_gpu(args):
     gpu_launches = eng.launch_count - launches0
     step_ms = [a.elapsed_time(b) for a, b in events]
     total_ms = float(np.sum(step_ms))
+    if args.warmup + args.steps < P:
+        for u in units: launch(u)                                           # every unit has results to read below
+        torch.cuda.synchronize(device)
 
-    # results of the last step (for the work model and a sanity check)
-    stats = eng.solver_stats(handle['ws'], handle['plan'])
-    if stats['abort'] or stats['done'] != handle['n']:
-        raise SystemExit(f'persistent solver did not finish: {stats}')
-    o = handle['out']
-    n = handle['n']
-    pixels_local = int(handle['cands']['n'].sum())
-    info = o['info'][:32 * n].cpu().numpy().view(np.int32).reshape(n, 8)
-    status = o['status'][:4 * n].cpu().numpy().view(np.int32)
+    # ---- results of every unit (work model, sanity check); CvxprogError candidates (both elliptical passes failed,
+    #      objects.py:351-353) are legitimate results of the reference too, but its compute_objects raises on them: they are
+    #      dropped from the end-to-end leg ----
+    optimal = n_errors = 0
+    stats = None
+    for u in units:
+        h = u['handle']
+        stats = eng.solver_stats(h['ws'], h['plan'])
+        if stats['abort'] or stats['done'] != h['n']: raise SystemExit(f'persistent solver did not finish: {stats}')
+        n = h['n']
+        info = h['out']['info'][:32 * n].cpu().numpy().view(np.int32).reshape(n, 8)
+        status = h['out']['status'][:4 * n].cpu().numpy().view(np.int32)
 
-    class _R(object): pass
-    r = _R(); r.cands = handle['cands'].copy(); r.info = info
-    alg_bytes, alg_flops = algorithmic_work(r)
-    optimal = int((status == _lib.ST_OPTIMAL).sum())
-    n_errors = int((status >= _lib.ST_ERROR).sum())
-    bad_local = set()
-    if n_errors:
-        # CvxprogError candidates (both elliptical passes failed, objects.py:351-353) are legitimate results of the reference
-        # too, but its compute_objects raises on them: they are dropped from the e2e leg (the headline image, seed 1, has none)
-        bad_local = set(fp for fp, st in zip(fps, status) if st >= _lib.ST_ERROR)
-        if mode == 'batch':
-            pos = 0
-            for wi in ws:
-                k = len(wi['footprints'])
-                wi['footprints'] = [fp for fp, st in zip(wi['footprints'], status[pos:pos + k]) if st < _lib.ST_ERROR]
-                pos += k
-        fps = [fp for fp, st in zip(fps, status) if st < _lib.ST_ERROR]
+        class _R(object): pass
+        r = _R(); r.cands = h['cands'].copy(); r.info = info
+        u['alg_bytes'], u['alg_flops'] = algorithmic_work(r)
+        u['n'], u['pixels'] = n, int(h['cands']['n'].sum())
+        optimal += int((status == _lib.ST_OPTIMAL).sum()); n_errors += int((status >= _lib.ST_ERROR).sum())
+        pos = 0
+        u['fps'] = []
+        for wi in u['ws']:
+            k = len(wi['footprints'])
+            u['fps'].append([fp for fp, st in zip(wi['footprints'], status[pos:pos + k]) if st < _lib.ST_ERROR])
+            pos += k
+    timed_units = [unit_of(args.warmup + s_) for s_ in range(args.steps)]
+    cand_local = float(sum(u['n'] for u in timed_units))
+    alg_bytes = float(sum(u['alg_bytes'] for u in timed_units)); alg_flops = float(sum(u['alg_flops'] for u in timed_units))
+    pixels_local = int(np.mean([u['pixels'] for u in timed_units]))
 
     # ---- end to end through the public API (`e2e`): host arrays in, Objects out ----
-    if mode == 'batch':
-        from superdsm_b200.objects import compute_objects_multi
-
-        def e2e_step():
-            jobs = [([Object(fp) for fp in wi['footprints']], Image(wi['y'], wi['y_mask']), wi['atoms']) for wi in ws]
-            compute_objects_multi(jobs, w['dsm_cfg'])                  # uploads every image, one launch, Objects out
-            return [ob for objs, _, _ in jobs for ob in objs]
-    elif mode == 'sharded':
+    if mode == 'sharded':
         from superdsm_b200.sharding import compute_objects_sharded
-        del handle
-        torch.cuda.empty_cache()
-        y_img = Image(w['y'], w['y_mask'])
-        bad_fp = bad_local
+        bad = set(fp for fp in units[0]['ws'][0]['footprints'] if fp not in set(units[0]['fps'][0]))
         if world > 1:
             parts = [None] * world
-            dist.all_gather_object(parts, bad_fp, group=gloo)
-            bad_fp = set().union(*parts)
-        keep = [fp for fp in all_fps if fp not in bad_fp]
+            dist.all_gather_object(parts, bad, group=gloo)
+            bad = set().union(*parts)
+        keep = [fp for fp in all_fps if fp not in bad]
+        w0 = ws[0]
+        for u in units: del u['handle']
+        torch.cuda.empty_cache()
+        y_img = Image(w0['y'], w0['y_mask'])
 
-        def e2e_step():
+        def e2e_step(s_):
             objs = [Object(fp) for fp in keep]
             forget_images()
-            compute_objects_sharded(objs, y_img, w['atoms'], w['dsm_cfg'], None, group=gloo)     # every rank ends with all results
-            return objs
+            compute_objects_sharded(objs, y_img, w0['atoms'], w0['dsm_cfg'], None, group=gloo)     # every rank ends with all results
+            return objs, len(keep) / world
+    elif mode == 'batch':
+        def e2e_step(s_):
+            u = units[0]
+            jobs = [([Object(fp) for fp in fps], Image(wi['y'], wi['y_mask']), wi['atoms']) for wi, fps in zip(u['ws'], u['fps'])]
+            compute_objects_multi(jobs, u['ws'][0]['dsm_cfg'])          # uploads every image, one launch, Objects out
+            return [ob for objs, _, _ in jobs for ob in objs], sum(len(fps) for fps in u['fps'])
     else:
-        y_img = Image(w['y'], w['y_mask'])
-
-        def e2e_step():
-            objs = [Object(fp) for fp in fps]
+        def e2e_step(s_):
+            u = unit_of(s_)
+            wi = u['ws'][0]
+            objs = [Object(fp) for fp in u['fps'][0]]
             forget_images()                                                # every step uploads its image again
-            compute_objects(objs, y_img, w['atoms'], w['dsm_cfg'], None)
-            return objs
-    e2e_step()
+            compute_objects(objs, Image(wi['y'], wi['y_mask']), wi['atoms'], wi['dsm_cfg'], None)
+            return objs, len(objs)
+    e2e_step(0)
     h2d0, d2h0 = eng.h2d_bytes, eng.d2h_bytes
     barrier()
     t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 5))
-    for _ in range(e2e_steps):
-        objs = e2e_step()
+    e2e_steps = max(1, min(args.steps, 2 * P if mode == 'single' else 3))
+    e2e_cands = 0.0
+    for s_ in range(e2e_steps):
+        objs, cnt = e2e_step(s_)
+        e2e_cands += cnt
     torch.cuda.synchronize(device)
     e2e_s = time.perf_counter() - t0
     h2d = (eng.h2d_bytes - h2d0) // e2e_steps
     d2h = (eng.d2h_bytes - d2h0) // e2e_steps
     assert all(np.isfinite(ob.energy) for ob in objs)
 
-    # ---- max over ranks ----
-    t = torch.tensor([total_ms, e2e_s * 1e3, float(len(fps)), float(n_images)], dtype=torch.float64, device=device)
+    # ---- max over ranks (times), sum over ranks (units) ----
+    n_images = {'single': 1, 'batch': args.images, 'sharded': 1.0 / world}[mode]
+    t = torch.tensor([total_ms, e2e_s * 1e3, cand_local, e2e_cands, float(n_images)], dtype=torch.float64, device=device)
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        total_ms_max, e2e_ms_max, cand_total, img_total = float(tmax[0]), float(tmax[1]), float(tsum[2]), float(tsum[3])
+        tmin = t.clone(); dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        total_ms_max, e2e_ms_max, cand_total, e2e_cand_total, img_per_step = float(tmax[0]), float(tmax[1]), float(tsum[2]), float(tsum[3]), float(tsum[4])
+        total_ms_min = float(tmin[0])
     else:
-        total_ms_max, e2e_ms_max, cand_total, img_total = total_ms, e2e_s * 1e3, float(len(fps)), float(n_images)
-    if mode == 'sharded': img_total = 1.0
+        total_ms_max, e2e_ms_max, cand_total, e2e_cand_total, img_per_step = total_ms, e2e_s * 1e3, cand_local, e2e_cands, float(n_images)
+        total_ms_min = total_ms
 
     if rank == 0:
         peaks = {}
@@ -396,26 +431,26 @@ def run_gpu(args):
             traffic, traffic_src = float(tj['dram_bytes_per_launch']), tj['source']
         except Exception: pass
         ms_per_step = total_ms_max / args.steps
-        solver_ms = float(np.mean(step_ms))          # the solver kernel is >99% of a step (profiles/), both on this stream
-        achieved = alg_bytes / (solver_ms * 1e-3) / 1e9
-        value = cand_total * args.steps / (total_ms_max * 1e-3)
+        achieved = alg_bytes / (total_ms * 1e-3) / 1e9   # rank 0's launches: the solver kernel is > 97 % of a step (profiles/), both on this stream
+        value = cand_total / (total_ms_max * 1e-3)
         line = {
             'metric': 'dsm_candidate_solves_per_s', 'value': value, 'unit': 'candidate-solves/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True, 'scaling': 'strong' if mode == 'sharded' else 'weak', 'vs_baseline': None,
             'dtype': 'f64', 'data': 'synthetic',
-            'config': workload_config(w, world, args),
-            'stats': {'pixels_per_step_per_gpu': pixels_local, 'optimal': optimal, 'errors': n_errors, 'candidates_per_step': int(cand_total),
-                      'images_per_step': int(img_total), 'images_per_s': img_total * args.steps / (total_ms_max * 1e-3),
-                      'e2e_images_per_s': img_total * e2e_steps / (e2e_ms_max * 1e-3)},
-            'e2e': {'value': cand_total * e2e_steps / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
-                    'd2h_bytes_per_step': int(d2h), 'includes': 'pinned H2D of y, mask, atoms; device EDT + atom statistics; descriptors; solve; D2H of results; Object materialisation'},
+            'config': workload_config(ws, world, args),
+            'stats': {'pixels_per_step_per_gpu': pixels_local, 'optimal': optimal, 'errors': n_errors, 'candidates_per_step': cand_total / args.steps,
+                      'images_per_step': img_per_step, 'images_per_s': img_per_step * args.steps / (total_ms_max * 1e-3),
+                      'e2e_images_per_s': img_per_step * e2e_steps / (e2e_ms_max * 1e-3),
+                      'rank0_step_ms': [round(v, 2) for v in step_ms], 'slowest_over_fastest_rank': total_ms_max / max(total_ms_min, 1e-9)},
+            'e2e': {'value': e2e_cand_total / (e2e_ms_max * 1e-3), 'unit': 'candidate-solves/s', 'h2d_bytes_per_step': int(h2d),
+                    'd2h_bytes_per_step': int(d2h), 'includes': 'pinned H2D of y, mask, atoms; device EDT + atom statistics; descriptors; solve; D2H of results; Object materialisation' + ('; result gather over the ranks' if mode == 'sharded' else '')},
             'gpu_launches': int(gpu_launches),
             'roofline': {'kernel': 'k_solve (persistent solver: control CTAs + evaluation warps fed by device-side priority queues)', 'bound': 'hbm', 'achieved': achieved, 'peak': hbm_peak,
                          'unit': 'GB/s', 'frac': achieved / hbm_peak, 'traffic': traffic, 'traffic_source': traffic_src, 'peak_source': peak_src,
-                         'algorithmic_bytes_per_launch': alg_bytes,
-                         'fp64': {'achieved_gflops': alg_flops / (solver_ms * 1e-3) / 1e9, 'peak_gflops': dfma,
-                                  'frac': alg_flops / (solver_ms * 1e-3) / 1e9 / dfma, 'peak_source': 'register-resident DFMA loop measured in this run',
-                                  'note': 'the kernel is bound by dependent FP64 issue latency at 16 warps per SM, not by HBM: the G~ rows stream from DRAM at about 0.7 TB/s, 11 % of peak (DESIGN.md section 4)'}},
+                         'algorithmic_bytes_per_launch': alg_bytes / args.steps,
+                         'fp64': {'achieved_gflops': alg_flops / (total_ms * 1e-3) / 1e9, 'peak_gflops': dfma,
+                                  'frac': alg_flops / (total_ms * 1e-3) / 1e9 / dfma, 'peak_source': 'register-resident DFMA loop measured in this run',
+                                  'note': 'the kernel is bound by FP64 / conversion issue and dependent-issue latency at 16 warps per SM, not by HBM (DESIGN.md section 4)'}},
             'clocks': clocks,
             'solver': {k: stats[k] for k in ('n_eval', 'n_hrows', 'n_ctrl', 'n_promoted')} | {
                 'control_cta_time_share': {k[4:]: round(stats[k] / max(stats['cyc_total'], 1), 4) for k in ('cyc_ctrl', 'cyc_idle')},
@@ -423,10 +458,10 @@ def run_gpu(args):
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            arm = CpuArm(w, cores, sample=max(16, min(2 * cores, 64)))
+            arm = CpuArm(ws, cores, sample=max(16, min(2 * cores, 64)))
             est_all, wall, cpu_s = arm.step(0)
             arm.close()
-            line['cpu_baseline'] = {'value': len(w['footprints']) / est_all, 'unit': 'candidate-solves/s', 'cores': cores,
+            line['cpu_baseline'] = {'value': arm.n / est_all, 'unit': 'candidate-solves/s', 'cores': cores,
                                     'blas_threads_per_process': arm.blas_threads, 'kind': 'port',
                                     'sample': arm.describe() + f' ({wall:.1f} s wall, {cpu_s:.1f} core-s)',
                                     'note': 'numpy/scipy port of dsm.Energy + restated cvxopt cp (oracle/); cvxopt and MKL are unavailable on this box'}
@@ -447,6 +482,7 @@ def main():
     ap.add_argument('--max-candidates', type=int, default=None)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--images', type=int, default=8, help='--workload batch: images per rank and launch')
+    ap.add_argument('--pool', type=int, default=4, help='default workload: images in the pool the steps cycle through')
     ap.add_argument('--field', type=int, default=0, help='--workload tiled4k: edge of the field in pixels (default 4096)')
     ap.add_argument('--workload', default=WORKLOAD, choices=[WORKLOAD] + sorted(OTHER_WORKLOADS))
     args = ap.parse_args()

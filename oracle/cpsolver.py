@@ -39,7 +39,10 @@ RANK_ERROR = 'Rank(A) < p or Rank([H(x); A; Df(x); G]) < n'
 # last bits of a numerically singular z * Hess f far away from the optimum (LAPACK, CHOLMOD, numpy and the CUDA solver
 # disagree there), and when it happens to succeed cp restores the saved state one step later anyway (newphi >= phi0).
 # With 'saved' (the policy the CUDA solver implements) the saved state is restored in both cases, so
-# that the outcome no longer depends on those bits; 'cvxopt' is the strict restatement.
+# that the outcome no longer depends on those bits; 'cvxopt' is the strict restatement.  Second difference: after a restore
+# cvxopt refines the Newton system of the restored point against the gradient and Hessian of the ABANDONED point (its residual
+# closures are not updated) -- garbage by construction, and when the excursion overflowed a NaN that turns the whole solve
+# into an exception; 'saved' uses the derivatives of the restored point there.
 RESTORE_POLICY = 'saved'
 
 
@@ -185,6 +188,10 @@ def cp(F, FH, x0, trace=None, maxiters=MAXITERS, restore_policy=None, events=Non
                     _, g_r, H_r = FH(x, z)
                     L = _chol_lower(H_r)
                     gk = np.asarray(g_r, dtype=float).reshape(-1)
+                    if restore_policy == 'saved':
+                        # ... which may be garbage or non-finite: the 'saved' policy refines the Newton system against the
+                        # derivatives of the point it restored (g and Hk feed the residual closure below)
+                        g, Hk = gk, H_r
                 except ArithmeticError:
                     singular_kkt_matrix = True
             else:

@@ -30,7 +30,7 @@ WORKLOAD_ARGS = {
     'gowt1':   dict(name='gowt1', oversegment=3, max_set_size=4, seed=1),
     'bbbc039': dict(name='bbbc039', oversegment=3, max_set_size=4, seed=39),
     'nih3t3':  dict(name='nih3t3', oversegment=3, max_set_size=4, seed=3),
-    'tiled':   dict(name='tiled4k', oversegment=3, max_set_size=4, seed=5, shape=(1024, 1024), n=1250),
+    'tiled':   dict(name='tiled4k', oversegment=3, max_set_size=4, seed=5, shape=(1024, 1024), n=1250, max_candidates=8000),
 }
 
 

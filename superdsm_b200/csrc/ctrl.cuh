@@ -759,15 +759,17 @@ __device__ __forceinline__ void ipm_begin(CState& S)
 }
 
 // Prepares the evaluation of F at vector `vec`: records the request in S (it is published by publish_request when the control
-// task ends).  Returns false, recording nothing, if the point is not finite (the reference's Energy would raise on NaN).
+// task ends).  Returns false, recording nothing, if the point holds a NaN (the reference's Energy raises on NaN).
 template <int BLOCK>
 __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int want_h, bool budgeted)
 {
     const int tid = threadIdx.x;
     const int N = S.use_xi ? P.N : 6;
     const double* x = P.V + (size_t)vec * P.ld;
+    // NaN only: an infinite parameter (a relaxed excursion that overflowed) passes the reference's check (dsm.py:72 asserts on
+    // NaN), F evaluates to NaN / inf there, the factorisation of the non-finite KKT matrix fails and cp restores the saved state
     int bad = 0;
-    for (int i = tid; i < N; i += BLOCK) bad |= !isfinite(x[i]);
+    for (int i = tid; i < N; i += BLOCK) bad |= isnan(x[i]);
     if (__syncthreads_or(bad)) return false;
     // A solve whose line search never terminates (NaN merit values) runs into the reference's SIGALRM time-out
     // (dsm.py:483-489, cp_timeout = 300 s) and raises; here the evaluation budget plays that role.
@@ -906,13 +908,11 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             // succeed cp restores the saved state one step later anyway; so the saved state is restored in both cases
             // (oracle/cpsolver.py RESTORE_POLICY = 'saved').
             if (0 < S.relaxed && S.relaxed <= MAX_RELAXED) {
-                // Restart a standard line search from the last saved state.  cvxopt re-evaluates F at the restored
-                // point inside the KKT solver only: cpl's residual closures keep the Df and H of the abandoned point.
+                // Restart a standard line search from the last saved state: F is re-evaluated at the restored point.
                 S.phi = S.phi0s; S.gap = S.gap0s;
                 S.d = S.sv_d; S.lm = S.sv_lm; S.t = S.sv_t; S.s = S.sv_s; S.z = S.sv_z; S.lmsq = S.lm * S.lm;
                 __syncthreads();
-                for (int i = tid; i < Nc; i += BLOCK) { x[i] = sx[i]; sdx[i] = g[i]; }
-                for (size_t i = tid; i < (size_t)Nc * Nc; i += BLOCK) P.H2[i] = P.H[i];
+                for (int i = tid; i < Nc; i += BLOCK) x[i] = sx[i];
                 S.rxt = S.sv_rxt; S.resx = S.sv_resx; S.rznl = S.sv_rznl; S.resznl = fabs(S.rznl);
                 S.relaxed = -1;
                 __syncthreads();
@@ -925,7 +925,9 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
         case PC_RESTORED: {
             const bool ok = BIG ? cholesky_big<BLOCK>(P.H, Nc, P.Lg, sm) : cholesky<BLOCK>(P.H, Nc, Lf, sm);
             if (!ok) { S.r_ipm = 1; S.pc = PC_IPMDONE; break; }
-            hres_alt = true;
+            // cvxopt would refine the Newton system below against the gradient and Hessian of the abandoned point (cpl's residual
+            // closures keep them): garbage, possibly non-finite.  The 'saved' policy refines against the restored point's.
+            hres_alt = false;
             S.pc = PC_KKT;
             break;
         }
