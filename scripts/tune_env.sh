@@ -1,0 +1,6 @@
+#!/bin/bash
+# A/B of the scheduler knobs (environment, read at sdsm_create) on one box: ms per step of the default bench
+for cfg in "" "SDSM_CTRL_CTAS=64" "SDSM_CTRL_CTAS=80" "SDSM_CTRL_CTAS=36" "SDSM_HI_EVALS=150" "SDSM_HI_EVALS=600" "SDSM_HI_FRAC=0.06" "SDSM_HI_FRAC=0.0" "SDSM_TASK_SMALL_CELLS=64" "SDSM_SOLO_CELLS=16" "SDSM_SOLO_CELLS=64"; do
+  ms=$(env $cfg timeout 300 python bench.py --steps 4 --warmup 4 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads([l for l in sys.stdin.read().splitlines() if l.startswith('{')][-1]); print(round(d['ms_per_step'],2), d['stats']['rank0_step_ms'], d['solver']['control_cta_time_share'], d['solver']['evaluation_warp_time_share'])")
+  echo "[$cfg] $ms"
+done

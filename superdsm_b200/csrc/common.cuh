@@ -40,8 +40,11 @@ constexpr int TILE_DOUBLES = WARP_AREA_DOUBLES + 64;
 __host__ __device__ __forceinline__ int grow_stride(int na) { return na <= 4 ? 4 : (na <= 12 ? 12 : (na <= 20 ? 20 : GROW)); }
 constexpr int CTRL_BLOCK = SOLVE_BLOCK;   // control task: one CTA advances one candidate's state machine
 constexpr int CTRL_WARPS = CTRL_BLOCK / 32;
-constexpr int SMEM_L_CAP = 5504;  // doubles of shared memory for the packed Cholesky factor (N <= 104)
-constexpr int SMALL_N_MAX = 104;  // systems up to this size are factorised in shared memory, larger ones blocked in global memory / L2
+#ifndef SDSM_SMALL_N_MAX
+#define SDSM_SMALL_N_MAX 104      // (148 would fill the 100 KB of dynamic shared memory a CTA of k_solve has anyway; measured: no gain,
+#endif                            //  172.6 vs 173.3 ms per step -- the factorisations of mid-size systems are not what bounds the step)
+constexpr int SMALL_N_MAX = SDSM_SMALL_N_MAX;
+constexpr int SMEM_L_CAP = SMALL_N_MAX * (SMALL_N_MAX + 1) / 2;  // doubles of shared memory for the packed Cholesky factor  // systems up to this size are factorised in shared memory, larger ones blocked in global memory / L2
 constexpr int BIG_BLOCK  = SOLVE_BLOCK;
 constexpr int N_COUNTERS = 32;
 constexpr int NVEC       = 12;    // N-vectors of the interior-point solver

@@ -41,9 +41,10 @@ struct Sm {
     double *D, *Xj, *yv;   // large systems only: diagonal block, panel block, solved block (see cholesky_big)
     double *Wt;            // large systems only: one CB x CB_LD tile per warp (coalesced staging of global rows)
 };
-constexpr int CTRL_BPAD = 128;
+constexpr int CTRL_BPAD = 160;     // >= SMALL_N_MAX: the right-hand side of the triangular solves sits behind the factor
 __host__ __device__ inline size_t ctrl_smem_bytes(int lcap) { return sizeof(double) * (size_t)(lcap + CTRL_BPAD + CTRL_WARPS * 32 + 32) + sizeof(int) * 8 + CTRL_WARPS * sizeof(CState); }
 // factor capacity (doubles) a batch whose largest system has n_max unknowns asks for: the whole packed factor if n_max <= 104
+static_assert(CTRL_BPAD >= SMALL_N_MAX, "the solves' right-hand side must fit behind the factor");
 __host__ __device__ inline int ctrl_lcap(int n_max) { const int need = n_max * (n_max + 1) / 2; return need <= SMEM_L_CAP ? (need < 64 ? 64 : need) : SMEM_L_CAP; }
 
 __device__ __forceinline__ void carve_smem(Sm& sm, char* base, int lcap)
@@ -782,9 +783,11 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
 // Advances candidate c by one control task: consumes the evaluation it asked for, runs up to the next evaluation request.
 // Returns true if an evaluation was requested (ws.req[c] describes it; the caller schedules it), false if the candidate is
 // finished.  first = false: there is an evaluation to consume (always true except for the task that starts the candidate).
-template <int BLOCK, bool BIG>
+// BIG (runtime, uniform over the CTA): the system is larger than the shared-memory factor (blocked Cholesky in L2).  One
+// instantiation serves both: the state machine is inlined once (the kernel's code size is an instruction-cache matter).
+template <int BLOCK>
 __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
-                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells)
+                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells, const bool BIG)
 {
     const int tid = threadIdx.x;
     // The candidate's state lives in shared memory while the task runs, one copy per warp: all threads compute the same

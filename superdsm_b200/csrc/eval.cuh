@@ -491,25 +491,24 @@ constexpr size_t EVAL_SMEM = sizeof(double) * EVAL_WARPS * TILE_DOUBLES;
 // -- a warp takes the next cell when it is done with its last one (cells differ in their pixel counts) -- and leave the
 // per-cell value / gradient / Hessian in scrG / scrH.  smem_eval: EVAL_SMEM bytes; *s_next == 0 on entry (all threads
 // synchronised after it was set), and the caller synchronises the CTA after the call.
-__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, const CInfo& ci, int idx,
+__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int idx,
                                           double* Tt, int* slotj);
 
 __device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first,
                                           double* smem_eval, int* s_slotj, int* s_next)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const CInfo ci = ws.cinfo[c];
-    const int count = min(ws.req[c].cpt, ci.n_ne - first);
+    const int count = min(ws.req[c].cpt, ws.cinfo[c].n_ne - first);
     for (;;) {
         int i = 0;
         if (lane == 0) i = atomicAdd(s_next, 1);
         i = __shfl_sync(0xffffffffu, i, 0);
         if (i >= count) break;
-        eval_cell(par, cands, ws, c, ci, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * WARP_INTS);
+        eval_cell(par, cands, ws, c, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * WARP_INTS);
     }
 }
 
-__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, const CInfo& ci, int idx,
+__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int idx,
                                           double* Tt, int* slotj)
 {
     const int lane = threadIdx.x & 31;
@@ -526,7 +525,7 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     const double* xc = xr + h;
     double* sg = ws.scrG + (size_t)(cell_off + cell) * SCRG;
     double* sh = ws.scrH + (size_t)(cell_off + cell) * SCRH;
-    const int cw = ci.cw;
+    const int cw = ws.cinfo[c].cw;
     const int ca = cell / cw, cb = cell - ca * cw;
     if (!rq.use_xi) {
         if (rq.want_h) eval_cell_poly_h(py, prc, npix, xr, xc, rq.x, par.sparsity_tol, sg, sh);

@@ -23,6 +23,8 @@
 namespace sdsm {
 
 constexpr size_t SOLVE_SMEM_MIN = EVAL_SMEM > BIG_SMEM ? EVAL_SMEM : BIG_SMEM;
+static_assert(sizeof(double) * (size_t)(SMEM_L_CAP + CTRL_BPAD + CTRL_WARPS * 32 + 32) + sizeof(int) * 8 + CTRL_WARPS * sizeof(CState) <= EVAL_SMEM,
+              "the shared-memory Cholesky must not enlarge the CTA's shared memory beyond what the evaluation warps need (2 CTAs per SM)");
 __host__ __device__ inline size_t solve_smem_bytes(int lcap)
 {
     const size_t a = ctrl_smem_bytes(lcap);
@@ -85,13 +87,10 @@ __global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, in
 }
 
 // one warp: the evaluation item (c, first) = cells cell_list[first .. first + cpw) of candidate c's pending request
-__device__ __forceinline__ int eval_item(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* Tt, int* slotj)
+__device__ __forceinline__ void eval_item(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* Tt, int* slotj)
 {
-    const CInfo ci = ws.cinfo[c];
-    const EvalReq rq = ws.req[c];
-    const int count = min(rq.cpw, ci.n_ne - first);
-    for (int i = 0; i < count; ++i) eval_cell(par, cands, ws, c, ci, first + i, Tt, slotj);
-    return (rq.use_xi ? 2 : 0) + (rq.want_h ? 1 : 0);       // kind of the evaluation (statistics)
+    const int count = min(ws.req[c].cpw, ws.cinfo[c].n_ne - first);
+    for (int i = 0; i < count; ++i) eval_cell(par, cands, ws, c, first + i, Tt, slotj);
 }
 
 // the warp that finished an item of candidate c's current stage: the last one to finish starts the next stage
@@ -140,8 +139,9 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
         // ---- evaluation warps: independent consumers of ws.qe ----
         double* Tt = (double*)smem_solve + warp * TILE_DOUBLES;      // TILE_DOUBLES >= HG_ACC
         int* slotj = s_slotj + warp * WARP_INTS;
-        unsigned long long cyc_idle = 0, kcyc[4] = {0, 0, 0, 0}, kcnt[4] = {0, 0, 0, 0}, cyc_hg = 0, n_hg = 0, cyc_fin = 0;
-        unsigned n_popped = 0;
+        // statistics: four counters in registers (anything indexed dynamically would live in local memory)
+        unsigned long long cyc_idle = 0, cyc_eval = 0, cyc_hg = 0;
+        unsigned n_popped = 0, n_eval = 0, n_hg = 0;
         for (;;) {
             uint2 task = make_uint2(0u, 0u);
             int ok = 0;
@@ -159,23 +159,20 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
             const uint32_t type = task.x >> T_SHIFT;
             const int c = (int)(task.x & T_CMASK);
             if (type == T_EVAL) {
-                const int kind = eval_item(par, cands, ws, c, (int)task.y, Tt, slotj);
-                kcyc[kind] += (unsigned long long)(clock64() - c1); kcnt[kind] += 1;
+                eval_item(par, cands, ws, c, (int)task.y, Tt, slotj);
+                finish_item(ws, type, c);
+                cyc_eval += (unsigned long long)(clock64() - c1); n_eval += 1;
             } else {
                 const int m = ws.cinfo[c].m;
                 for (int j = (int)task.y; j < (int)task.y + HG_ITEM_ROWS && j < m; ++j) { hg_row(par, cands, ws, c, j, Tt); __syncwarp(); }
+                finish_item(ws, type, c);
                 cyc_hg += (unsigned long long)(clock64() - c1); n_hg += 1;
             }
-            const long long c2 = clock64();
-            finish_item(ws, type, c);
-            cyc_fin += (unsigned long long)(clock64() - c2);
         }
         if (lane == 0) {
-            unsigned long long ce = 0, ne = 0;
-            for (int k = 0; k < 4; ++k) { atomicAdd(ws.counters + Q_CYC_KIND + k, kcyc[k]); atomicAdd(ws.counters + Q_N_KIND + k, kcnt[k]); ce += kcyc[k]; ne += kcnt[k]; }
-            atomicAdd(ws.counters + Q_CYC_EVAL, ce); atomicAdd(ws.counters + Q_N_EVAL, ne);
-            atomicAdd(ws.counters + Q_CYC_HG, cyc_hg); atomicAdd(ws.counters + Q_N_HG, n_hg);
-            atomicAdd(ws.counters + Q_CYC_WIDLE, cyc_idle); atomicAdd(ws.counters + Q_CYC_WFIN, cyc_fin);
+            atomicAdd(ws.counters + Q_CYC_EVAL, cyc_eval); atomicAdd(ws.counters + Q_N_EVAL, (unsigned long long)n_eval);
+            atomicAdd(ws.counters + Q_CYC_HG, cyc_hg); atomicAdd(ws.counters + Q_N_HG, (unsigned long long)n_hg);
+            atomicAdd(ws.counters + Q_CYC_WIDLE, cyc_idle);
             atomicAdd(ws.counters + Q_CYC_WTOTAL, (unsigned long long)(clock64() - c_begin));
         }
         return;
@@ -218,8 +215,8 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
                 const bool big = (ws.cstate[c].use_xi ? 6 + ci.m : 6) > SMALL_N_MAX;
                 Sm sm;
                 bool requested;
-                if (big) { carve_smem_big(sm, smem_solve); requested = ctrl_step<BLOCK, true>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
-                else { carve_smem(sm, smem_solve, args.lcap); requested = ctrl_step<BLOCK, false>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells); }
+                if (big) carve_smem_big(sm, smem_solve); else carve_smem(sm, smem_solve, args.lcap);
+                requested = ctrl_step<BLOCK>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells, big);
                 if (tid == 0) { ws.cstate[c].ns_ctrl += globaltimer_ns() - t_link; q_progress(ws); }
                 if (!requested) {
                     if (tid == 0) {
