@@ -22,6 +22,7 @@
  * Environment (read by sdsm_create), all optional tuning knobs of the persistent solver kernel:
  *   SDSM_CTRL_CTAS (48 + a share of the grid that grows with the batch's share of small candidates)   CTAs that run control
  *                         tasks; the warps of all other CTAs run evaluation / Hessian-row items
+ *   SDSM_CTRL_SHARE (0.95)  share of the rest of the grid that becomes control CTAs per unit of the batch's solo share
  *   SDSM_SOLO_CELLS (512 / smooth_subsample)  candidates with at most this many pixel cells run their whole chain inside
  *                         one control CTA
  *   SDSM_TASK_SMALL_CELLS (512)  candidates with at most this many cells get evaluation items of one cell (else 4)
@@ -74,6 +75,8 @@ typedef struct sdsm_params {
                                 _compute_object (objects.py:184-191); 0: it is fitted like any other, as cvxprog itself does
                                 (objects.py:361-412, the c2f seam) */
     double abstol, reltol, feastol;   /* cvxopt defaults 1e-7, 1e-6, 1e-7 */
+    double hessian_sparsity_tol;      /* dsm/hessian_sparsity_tol (dsm.py:376-382): off-diagonal entries of the Hessian of psi below this
+                                         are dropped (deformable model only); 0: none */
 } sdsm_params;
 
 /* one candidate region.  The caller fills r0 .. n and img; sdsm_plan_batch() fills the offsets. */
@@ -147,6 +150,14 @@ int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* params);
 int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_t* d_ymask, const int32_t* d_atoms, int32_t H, int32_t W,
                        double background_margin, int32_t n_labels, int32_t* d_atoms_out, uint64_t* d_count, int32_t* d_box,
                        uint8_t* d_scratch, void* stream);
+
+/* The Preprocessing stage on the device (preprocess.py:39-68): d_y = gaussian_filter(g, sigma1) - offset, bit for bit as
+ * scipy computes it.  h_w1 / h_w2: HOST arrays with the 2 r + 1 weights of scipy's 1-D Gaussian kernels for sigma1 / sigma2
+ * (radius r = int(4 sigma + 0.5)).  offset_clip_abs = offset_clip * g.std() (the caller's numpy reduction; +inf: no clipping,
+ * preprocess.py:50-51); lower_clip = g.mean() for preprocess/lower_clip_mean, -inf otherwise.  d_scratch: 5 H W doubles +
+ * 2 H W + 32 bytes.  d_graw, d_y: float64 H x W on the device. */
+int sdsm_preprocess(sdsm_ctx* ctx, const double* d_graw, int32_t H, int32_t W, const double* h_w1, int32_t r1, const double* h_w2,
+                    int32_t r2, double sigma2, double offset_clip_abs, double lower_clip, double* d_y, double* d_scratch, void* stream);
 
 /* fills the offset fields of h_cands[0..n_cand) and the plan; host-only, no CUDA call */
 int sdsm_plan_batch(sdsm_ctx* ctx, sdsm_cand* h_cands, int32_t n_cand, sdsm_plan* plan);

@@ -251,6 +251,10 @@ class Energy(object):
         gd[gd < 0] = 0
         H = np.block([[Hqq, Hxq.T], [Hxq, Hxx]])
         H[np.arange(6, 6 + self.m), np.arange(6, 6 + self.m)] += gd
+        if self.hessian_sparsity_tol > 0:                                    # dsm.py:376-382: the diagonal is kept
+            small = np.abs(H) < self.hessian_sparsity_tol
+            small[np.diag_indices_from(small)] = False
+            H[small] = 0
         return H
 
 

@@ -5,7 +5,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, 'libsuperdsm_b200.so')
-SOURCES = [os.path.join(HERE, 'csrc', name) for name in ('sdsm.cu', 'common.cuh', 'pack.cuh', 'grid.cuh', 'eval.cuh', 'ctrl.cuh', 'sched.cuh', 'image.cuh', 'logistic.cuh')]
+SOURCES = [os.path.join(HERE, 'csrc', name) for name in ('sdsm.cu', 'common.cuh', 'pack.cuh', 'grid.cuh', 'eval.cuh', 'ctrl.cuh', 'sched.cuh', 'image.cuh', 'logistic.cuh', 'preprocess.cuh')]
 HEADER = os.path.join(os.path.dirname(HERE), 'include', 'superdsm_b200.h')
 
 

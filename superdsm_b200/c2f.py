@@ -49,7 +49,6 @@ class NormalizedEnergyComputer(object):
         cfg = dict(dsm_cfg)
         cfg.pop('smooth_mat_max_allocations', None)
         cfg.pop('background_margin', None)           # already applied by the caller (get_cvxprog_region on the cluster crop)
-        if cfg.get('hessian_sparsity_tol', 0) != 0: raise SolverError('hessian_sparsity_tol != 0 is not implemented')
         cfg['smooth_amount'] = np.inf
         self.cfg = cfg
         self.cache = {}

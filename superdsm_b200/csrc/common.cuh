@@ -62,7 +62,7 @@ struct Img { const double* y; const int32_t* atoms; int32_t H, W; };
 struct ImgSet { Img v[SDSM_MAX_IMAGES]; };      // passed to the kernels by value (constant bank): no device-side table to maintain
 
 struct Par {
-    double alpha, epsilon, scale, sparsity_tol, abstol, reltol, feastol;
+    double alpha, epsilon, scale, sparsity_tol, abstol, reltol, feastol, hess_tol;
     int32_t sub, R, has_smooth, init_elliptical, maxiters, skip_single_fg;
     const float* psf;   // device, (R+1)^2
 };

@@ -24,7 +24,7 @@ struct Prob {
     const int32_t* cstart; const uint32_t* amask; const int32_t* cellmap; const uint32_t* grid; const int32_t* clist;
     int n_ne;
     const double* xr; const double* xc;
-    double scale_cp, alpha, eps, tol;
+    double scale_cp, alpha, eps, tol, hess_tol;
     double *V, *H, *H2, *Lg;
     const double *scrG, *scrH, *xig;
     int sub;
@@ -67,7 +67,7 @@ __device__ __forceinline__ void setup_problem(Prob& P, const Par& par, const sds
     P.grid = ws.grid_rc + cd.cell_off; P.clist = ws.cell_list + cd.cell_off; P.n_ne = ci.n_ne;
     P.xr = ws.xtab + cd.tab_off; P.xc = P.xr + cd.h;
     P.scale_cp = par.scale / (double)cd.n;                                   // objects.py:380
-    P.alpha = par.alpha; P.eps = par.epsilon; P.tol = par.sparsity_tol; P.sub = par.sub;
+    P.alpha = par.alpha; P.eps = par.epsilon; P.tol = par.sparsity_tol; P.hess_tol = par.hess_tol; P.sub = par.sub;
     P.V = ws.vecs + cd.vec_off;
     const size_t nn = (size_t)P.ld * P.ld;
     P.H = ws.mats + cd.mat_off; P.H2 = P.H + nn; P.Lg = P.H2 + nn;
@@ -156,7 +156,9 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
     if (HESS && tid < 21) {
         int a = 0, t = tid;
         while (t >= a + 1) { t -= a + 1; ++a; }
-        const double v = hz * sc * sm.red_out[8 + tid];
+        double u = sm.red_out[8 + tid];
+        if (a != t && fabs(u) < P.hess_tol) u = 0.0;                           // dsm.py:376-382 (the diagonal is kept)
+        const double v = hz * sc * u;
         P.H[a * N + t] = v;
         P.H[t * N + a] = v;
     }
@@ -183,7 +185,7 @@ __device__ double gather_cells(const Prob& P, Sm& sm, const double* x, double* g
 // Hessian-only evaluations (EvalReq.want_h == 2): only the theta-theta block is left to gather (the other rows are assembled by
 // the T_HG tasks); value and gradient at this point are the accepted line-search trial's.
 template <int BLOCK>
-__device__ void gather_hessian_block(const Prob& P, Sm& sm, double hz, int N)
+__device__ void gather_hessian_block(const Prob& P, Sm& sm, double hz, int N, double prune)
 {
     const int tid = threadIdx.x;
     double acc[21];
@@ -199,7 +201,9 @@ __device__ void gather_hessian_block(const Prob& P, Sm& sm, double hz, int N)
     if (tid < 21) {
         int a = 0, t = tid;
         while (t >= a + 1) { t -= a + 1; ++a; }
-        const double v = hz * P.scale_cp * sm.red_out[tid];
+        double u = sm.red_out[tid];
+        if (a != t && fabs(u) < prune) u = 0.0;
+        const double v = hz * P.scale_cp * u;
         P.H[a * N + t] = v;
         P.H[t * N + a] = v;
     }
@@ -279,10 +283,13 @@ __device__ __forceinline__ void hg_row(const Par& par, const sdsm_cand* __restri
             if (gd < 0) gd = 0;
             s += gd;
         }
+        else if (fabs(s) < par.hess_tol) s = 0.0;                            // dsm.py:376-382: small off-diagonal entries dropped
         H[(size_t)(6 + j) * N + 6 + k] = s * fac;
     }
     if (lane < 6) {
-        const double s = acc[SP * SP + lane] * fac;
+        double s = acc[SP * SP + lane];
+        if (fabs(s) < par.hess_tol) s = 0.0;
+        s *= fac;
         H[(size_t)(6 + j) * N + lane] = s;
         H[(size_t)lane * N + 6 + j] = s;
     }
@@ -816,7 +823,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
         double* gout = P.V + (size_t)S.req_gvec * ld;
         if (S.req_h == 2) {
             // Hessian only: value and gradient are those of the accepted trial (same point, same bits: PC_ACCEPT)
-            gather_hessian_block<BLOCK>(P, sm, S.z, S.use_xi ? P.N : 6);
+            gather_hessian_block<BLOCK>(P, sm, S.z, S.use_xi ? P.N : 6, S.use_xi ? P.hess_tol : 0.0);
             f0 = S.f_trial;
             psi = S.psi_trial;
         }

@@ -15,16 +15,17 @@ namespace sdsm {
 
 constexpr int EDT_MAX_MARGIN = 65534;     // vertical distances are kept in 16 bits (65535: no foreground within the window)
 
-__global__ void k_edt_cols(const double* __restrict__ y, int H, int W, int Mi, uint16_t* __restrict__ g)
+// feature pixels: y > thr (thr = 0 for the region mask of objects.py:126-127)
+__global__ void k_edt_cols(const double* __restrict__ y, int H, int W, int Mi, uint16_t* __restrict__ g, double thr)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
     if (c >= W) return;
     int best = 65535;
-    if (!(y[(size_t)r * W + c] <= 0)) best = 0;              // scipy: the zero elements of (y <= 0)
+    if (!(y[(size_t)r * W + c] <= thr)) best = 0;            // scipy: the zero elements of (y <= thr)
     else {
         for (int d = 1; d <= Mi; ++d) {
-            const bool up = r - d >= 0 && !(y[(size_t)(r - d) * W + c] <= 0);
-            const bool dn = r + d < H && !(y[(size_t)(r + d) * W + c] <= 0);
+            const bool up = r - d >= 0 && !(y[(size_t)(r - d) * W + c] <= thr);
+            const bool dn = r + d < H && !(y[(size_t)(r + d) * W + c] <= thr);
             if (up || dn) { best = d; break; }
         }
     }

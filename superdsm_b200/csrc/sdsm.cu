@@ -8,6 +8,7 @@
 
 #include "common.cuh"
 #include "image.cuh"
+#include "preprocess.cuh"
 #include "pack.cuh"
 #include "grid.cuh"
 #include "eval.cuh"
@@ -25,6 +26,8 @@ struct sdsm_ctx {
     bool have_par = false;
     float* d_psf = nullptr;
     size_t psf_cap = 0;
+    double* d_w = nullptr;                   // Gaussian weights of sdsm_preprocess
+    size_t w_cap = 0;
     int64_t launches = 0;
     int solve_ctas_per_sm = 1;               // resident CTAs of k_solve per SM (occupancy query)
     int solo_cells = 0;                      // SDSM_SOLO_CELLS: chains of candidates up to this many cells stay in one CTA
@@ -34,6 +37,7 @@ struct sdsm_ctx {
     bool ctrl_ctas_fixed = false;            // SDSM_CTRL_CTAS given: no adaptation to the batch
     int ctrl_ctas = 48;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
     int hi_evals = 300;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
+    double ctrl_share = 0.95;                // SDSM_CTRL_SHARE: share of the remaining grid the control CTAs get per unit of solo work
     std::string err;
 };
 
@@ -81,6 +85,7 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     if (const char* e = getenv("SDSM_TIMEOUT_S")) ctx->timeout_s = atof(e);
     if (const char* e = getenv("SDSM_HI_FRAC")) ctx->hi_frac = atof(e);
     if (const char* e = getenv("SDSM_HI_EVALS")) ctx->hi_evals = atoi(e);
+    if (const char* e = getenv("SDSM_CTRL_SHARE")) ctx->ctrl_share = atof(e);
     if (const char* e = getenv("SDSM_CTRL_CTAS")) { ctx->ctrl_ctas = atoi(e); ctx->ctrl_ctas_fixed = true; }
     return SDSM_OK;
 }
@@ -90,6 +95,7 @@ extern "C" void sdsm_destroy(sdsm_ctx* ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->d_psf) cudaFree(ctx->d_psf);
+    if (ctx->d_w) cudaFree(ctx->d_w);
     delete ctx;
 }
 
@@ -131,10 +137,54 @@ extern "C" int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const dim3 block(128), grid((W + 127) / 128, H);
     k_edt_init<<<(n_labels + 256) / 256, 256, 0, stream>>>(n_labels, H, W, (unsigned long long*)d_count, d_box);
-    if (!unbounded) { k_edt_cols<<<grid, block, 0, stream>>>(d_y, H, W, Mi, (uint16_t*)d_scratch); ctx->launches++; }
+    if (!unbounded) { k_edt_cols<<<grid, block, 0, stream>>>(d_y, H, W, Mi, (uint16_t*)d_scratch, 0.0); ctx->launches++; }
     k_edt_rows<<<grid, block, 0, stream>>>((const uint16_t*)d_scratch, d_ymask, d_atoms, H, W, Mi, unbounded ? -1.0 : background_margin, n_labels, d_atoms_out,
                                            (unsigned long long*)d_count, d_box);
     ctx->launches += 2;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_preprocess(sdsm_ctx* ctx, const double* d_graw, int32_t H, int32_t W, const double* h_w1, int32_t r1, const double* h_w2,
+                               int32_t r2, double sigma2, double offset_clip_abs, double lower_clip, double* d_y, double* d_scratch, void* stream_)
+{
+    if (!ctx || !d_graw || !h_w1 || !h_w2 || !d_y || !d_scratch || H < 1 || W < 1 || r1 < 0 || r2 < 0 || !(sigma2 > 0)) return SDSM_E_ARG;
+    const bool have_clip = offset_clip_abs < 1e300;
+    const int Mi = (int)sigma2 + 1;                                      // only distances < sigma2 contribute (preprocess.py:58)
+    if (have_clip && Mi > EDT_MAX_MARGIN) { ctx->err = "preprocess/sigma2 > 65533 is not implemented"; return SDSM_E_UNSUPPORTED; }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const size_t n = (size_t)H * W, wbytes = sizeof(double) * (size_t)(2 * r1 + 1 + 2 * r2 + 1);
+    if (wbytes > ctx->w_cap) {
+        if (ctx->d_w) CUDA_TRY(ctx, cudaFree(ctx->d_w));
+        ctx->d_w = nullptr; ctx->w_cap = 0;
+        CUDA_TRY(ctx, cudaMalloc(&ctx->d_w, wbytes + 64));
+        ctx->w_cap = wbytes;
+    }
+    double* w1 = ctx->d_w; double* w2 = w1 + 2 * r1 + 1;
+    CUDA_TRY(ctx, cudaMemcpyAsync(w1, h_w1, sizeof(double) * (2 * r1 + 1), cudaMemcpyHostToDevice, stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(w2, h_w2, sizeof(double) * (2 * r2 + 1), cudaMemcpyHostToDevice, stream));
+    // scratch: [0] pass buffer, [1] smooth1, [2] original offset, [3] clipped offset, [4] t0 (+ 16-bit distances and the max behind it)
+    double* tmp = d_scratch; double* s1 = tmp + n; double* orig = s1 + n; double* clipped = orig + n; double* t0 = clipped + n;
+    uint16_t* gv = reinterpret_cast<uint16_t*>(t0 + n);
+    unsigned long long* tmax = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(gv) + ((2 * n + 15) / 16) * 16);
+    const dim3 block(128), grid((W + 127) / 128, H);
+    const double inf = 1e308 * 10;
+    k_gauss_pass<<<grid, block, 0, stream>>>(d_graw, tmp, H, W, w1, r1, 0, inf);
+    k_gauss_pass<<<grid, block, 0, stream>>>(tmp, s1, H, W, w1, r1, 1, inf);
+    k_gauss_pass<<<grid, block, 0, stream>>>(d_graw, tmp, H, W, w2, r2, 0, inf);
+    k_gauss_pass<<<grid, block, 0, stream>>>(tmp, orig, H, W, w2, r2, 1, inf);
+    ctx->launches += 4;
+    if (have_clip) {
+        k_gauss_pass<<<grid, block, 0, stream>>>(d_graw, tmp, H, W, w2, r2, 0, offset_clip_abs);
+        k_gauss_pass<<<grid, block, 0, stream>>>(tmp, clipped, H, W, w2, r2, 1, inf);
+        CUDA_TRY(ctx, cudaMemsetAsync(tmax, 0, sizeof(unsigned long long), stream));
+        k_edt_cols<<<grid, block, 0, stream>>>(d_graw, H, W, Mi, gv, offset_clip_abs);
+        k_blend_weight<<<grid, block, 0, stream>>>(gv, H, W, Mi, sigma2, t0, tmax);
+        ctx->launches += 4;
+    }
+    k_offset_image<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(s1, orig, clipped, t0, tmax, have_clip ? 1 : 0, lower_clip, n, d_y);
+    ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
 }
@@ -149,6 +199,7 @@ extern "C" int sdsm_set_params(sdsm_ctx* ctx, const sdsm_params* p)
     Par par{};
     par.alpha = p->alpha; par.epsilon = p->epsilon; par.scale = p->scale; par.sparsity_tol = p->sparsity_tol;
     par.abstol = p->abstol; par.reltol = p->reltol; par.feastol = p->feastol;
+    par.hess_tol = p->hessian_sparsity_tol > 0 ? p->hessian_sparsity_tol : 0.0;
     par.sub = p->subsample; par.R = p->radius; par.has_smooth = p->has_smooth; par.init_elliptical = p->init_elliptical;
     par.maxiters = p->maxiters;
     par.skip_single_fg = p->skip_single_fg ? 1 : 0;
@@ -264,7 +315,7 @@ static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_can
     args.trace = trace;
     const int grid = ctx->sm_count * ctx->solve_ctas_per_sm;
     // batches of small candidates keep their chains inside control CTAs: give those the share of the grid their work has
-    if (!ctx->ctrl_ctas_fixed && d_order) args.n_ctrl_ctas += (int)(0.65 * (grid - 8 - args.n_ctrl_ctas) * solo_share);
+    if (!ctx->ctrl_ctas_fixed && d_order) args.n_ctrl_ctas += (int)(ctx->ctrl_share * (grid - 8 - args.n_ctrl_ctas) * solo_share);
     if (args.n_ctrl_ctas < 1) args.n_ctrl_ctas = 1;
     if (args.n_ctrl_ctas > grid - 1) args.n_ctrl_ctas = grid - 1;
     k_solve<<<grid, SOLVE_BLOCK, solve_smem_bytes(lcap), stream>>>(ctx->imgs, ctx->par, d_cands, ws, out, args);

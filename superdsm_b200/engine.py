@@ -310,12 +310,13 @@ class Engine(object):
         if callable(cfg.get('init')):
             raise SolverError('callable dsm/init is not implemented on the device')
         key = tuple(sorted((k, str(v)) for k, v in cfg.items() if k in
-                           ('alpha', 'epsilon', 'scale', 'sparsity_tol', 'smooth_amount', 'smooth_subsample',
+                           ('alpha', 'epsilon', 'scale', 'sparsity_tol', 'hessian_sparsity_tol', 'smooth_amount', 'smooth_subsample',
                             'gaussian_shape_multiplier', 'init'))) + (bool(skip_single_fg),)
         if key == self._params_key: return
         p = _lib.Params()
         p.alpha, p.epsilon, p.scale = float(cfg['alpha']), float(cfg['epsilon']), float(cfg['scale'])
         p.sparsity_tol = float(cfg.get('sparsity_tol', 0))
+        p.hessian_sparsity_tol = float(cfg.get('hessian_sparsity_tol', 0))
         p.subsample = int(cfg['smooth_subsample']) if np.isfinite(cfg['smooth_subsample']) else 16
         p.init_elliptical = 1 if cfg.get('init', 'elliptical') == 'elliptical' else 0
         p.maxiters, p.abstol, p.reltol, p.feastol = 100, 1e-7, 1e-6, 1e-7      # cvxopt defaults (never changed by the reference)

@@ -96,7 +96,7 @@ def _state(res, k, footprint, dt):
 
 
 def _check_cfg(cfg):
-    if cfg.get('hessian_sparsity_tol', 0) != 0: raise SolverError('hessian_sparsity_tol != 0 is not implemented')
+    if not (cfg.get('hessian_sparsity_tol', 0) >= 0): raise SolverError('hessian_sparsity_tol must be >= 0')
 
 
 def _compute_objects(objects, y, atoms, x_map, lock, dsm_cfg, log_root_dir):
@@ -190,7 +190,6 @@ def cvxprog(region, scale, epsilon, alpha, smooth_amount, smooth_subsample, gaus
     A region with a single foreground pixel is fitted like any other: the skip of such regions is a rule of
     ``_compute_object`` (``objects.py:184-191``), not of ``cvxprog``.
     """
-    if hessian_sparsity_tol != 0: raise SolverError('hessian_sparsity_tol != 0 is not implemented')
     engine = get_engine()
     mask = np.asarray(region.mask, dtype=bool)
     # a one-atom image whose usable pixels are exactly the region (margin = inf keeps every masked pixel)
@@ -198,7 +197,7 @@ def cvxprog(region, scale, epsilon, alpha, smooth_amount, smooth_subsample, gaus
     _bound.pop(id(engine), None)
     engine.set_params(dict(scale=scale, epsilon=epsilon, alpha=alpha, smooth_amount=smooth_amount, smooth_subsample=smooth_subsample,
                            gaussian_shape_multiplier=gaussian_shape_multiplier, smooth_mat_dtype=smooth_mat_dtype,
-                           sparsity_tol=sparsity_tol, init=init), skip_single_fg=False)
+                           sparsity_tol=sparsity_tol, hessian_sparsity_tol=hessian_sparsity_tol, init=init), skip_single_fg=False)
     res = engine.solve([{1}])
     st = int(res.status[0])
     if st == _lib.ST_ERROR: raise CvxprogError('elliptical initialisation failed')

@@ -144,3 +144,54 @@ def test_c2f_level_synchronous_scheduler(eng):
         irregular += 1
     assert compared >= 50 and irregular <= 0.05 * compared, (irregular, compared)
     print('clusters', len(keep), 'requests', n_requests, 'rounds', run_level_synchronous.last_rounds, 'regions', compared, 'irregular mismatches', irregular, 'worst relative error', worst)
+
+
+@pytest.mark.parametrize('name,kw', [('toy', dict()), ('bbbc039', dict()), ('gowt1', dict(sigma2=42.43)), ('nih3t3', dict(lower_clip_mean=True)),
+                                     ('toy', dict(offset_clip=np.inf, sigma2=7.5)), ('tiled4k', dict(sigma2=10, shape=(777, 1031)))])
+def test_preprocessing_on_the_device_is_bit_exact(eng, name, kw):
+    """preprocess.py:39-68 (three Gaussian filters, sigma up to 42: 341 taps with 'reflect' boundaries, the EDT blend) against the scipy
+    statement of the same lines: identical bits on the five synthetic shapes."""
+    import scipy.ndimage as ndi
+    from superdsm_b200.preprocess import offset_image
+    from workloads import synth
+    kw = dict(kw)
+    spec = dict(synth.WORKLOADS[name])
+    if 'shape' in kw: spec['shape'] = kw.pop('shape'); spec['n'] = 300
+    g_raw, _, _ = synth.make_image(**spec)
+    sigma1, sigma2 = kw.get('sigma1', np.sqrt(2)), kw.get('sigma2', 40)
+    offset_clip, lower = kw.get('offset_clip', 3), kw.get('lower_clip_mean', False)
+    # the reference's lines, verbatim in meaning (scipy on the host)
+    offset = ndi.gaussian_filter(g_raw, sigma2)
+    if not np.isinf(offset_clip):
+        clip_abs = offset_clip * g_raw.std()
+        clipped = ndi.gaussian_filter(g_raw.clip(0, clip_abs), sigma2)
+        t = ndi.distance_transform_edt(~(g_raw > clip_abs))
+        t = (sigma2 - t).clip(0, np.inf)
+        t = (t / t.max()) ** 2
+        offset = (1 - t) * clipped + t * offset
+    if lower: offset = np.max([offset, np.full(g_raw.shape, g_raw.mean())], axis=0)
+    ref = ndi.gaussian_filter(g_raw, sigma1) - offset
+    y = offset_image(g_raw, sigma1, sigma2, offset_clip, lower, engine=eng)
+    assert y.shape == ref.shape and np.array_equal(y, ref), (np.abs(y - ref).max(), int((y != ref).sum()))
+
+
+def test_hessian_sparsity_tol_against_the_reference(eng):
+    """dsm/hessian_sparsity_tol (dsm.py:376-382): off-diagonal entries of the Hessian of psi below the tolerance are dropped, the
+    diagonal is kept.  Golden: the reference's own Energy.hessian (tests/golden/hesstol.npz, oracle/make_hesstol_golden.py)."""
+    import os
+    from tests.golden_util import GOLDEN_DIR, GoldenCase
+    z = np.load(os.path.join(GOLDEN_DIR, 'hesstol.npz'))
+    for name, ks in (('hand', (0, 2)), ('toy', (0, 3))):
+        case = GoldenCase(name)
+        eng.set_image(case.y, case.y_mask, case.atoms, case.dsm_cfg['background_margin'])
+        for k in ks:
+            tol, p, ref = float(z[f'{name}_{k}_tol']), z[f'{name}_{k}_p'], z[f'{name}_{k}_hess_lower']
+            eng.set_params(dict(case.dsm_cfg, hessian_sparsity_tol=tol))
+            eng.solve(case.footprints)
+            _, _, H = eng.eval_candidate(k, p)
+            L = np.tril(H)
+            assert np.array_equal(L != 0, ref != 0), (name, k, int((L != 0).sum()), int((ref != 0).sum()))     # the same entries survive
+            assert np.allclose(L, ref, rtol=1e-9, atol=1e-12 * np.abs(ref).max())
+            eng.set_params(case.dsm_cfg)
+            eng.solve(case.footprints)
+            assert (np.tril(eng.eval_candidate(k, p)[2]) != 0).sum() > (ref != 0).sum()                         # without it: denser
