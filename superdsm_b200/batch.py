@@ -11,8 +11,7 @@ all jobs (``sdsm_set_images`` / ``sdsm_cand.img``), and the jobs continue with t
 the results are bit-identical to running each job alone (every candidate's fit is independent of its batch).
 
 Result formats: :func:`object_rows` / :func:`write_label_csv` produce the (size, centroid) table the reference's regression
-suite compares label maps with (``tests/regression/validate.py:26-45``), :func:`rasterize_labels` a label map of disjoint
-objects.
+suite compares label maps with (``tests/regression/validate.py:26-45``), :func:`rasterize_labels` a label map.
 """
 import csv
 import threading
@@ -148,13 +147,26 @@ def write_label_csv(path, rows):
 
 
 def rasterize_labels(shape, objects, background_label=0):
-    """uint16 label map of disjoint objects (the objects of a set cover are: their regions do not overlap); labels 1.. in order."""
-    out = np.full(shape, background_label, np.uint16)
+    """uint16 label map of the objects, labels 1.. in order.  The sets of a cover may share atoms, so foregrounds can overlap:
+    a pixel claimed by several objects gets the label of the nearest pixel claimed by exactly one (the reference resolves such
+    pixels by a watershed of the same distance map, ``render.py:427-433``)."""
+    import scipy.ndimage as ndi
+    out = np.zeros(shape, np.uint16)
+    claims = np.zeros(shape, np.uint8)
     label = 0
     for o in objects:
         if o.fg_fragment is None or not np.asarray(o.fg_fragment).any(): continue
         label += 1
         r, c = (int(v) for v in o.fg_offset)
         h, w = o.fg_fragment.shape
-        out[r:r + h, c:c + w][np.asarray(o.fg_fragment, bool)] = label
+        frag = np.asarray(o.fg_fragment, bool)
+        out[r:r + h, c:c + w][frag] = label
+        claims[r:r + h, c:c + w][frag] += 1
+    contested = claims > 1
+    if contested.any():
+        sure = (claims == 1)
+        if sure.any():
+            idx = ndi.distance_transform_edt(~sure, return_distances=False, return_indices=True)
+            out[contested] = out[idx[0][contested], idx[1][contested]]
+    if background_label != 0: out[claims == 0] = background_label
     return out

@@ -76,6 +76,9 @@ def test_result_formats(tmp_path):
     assert open(tmp_path / 'x.csv').read().splitlines() == ['"Object size","Center X","Center Y"', '"1","0.0","0.0"', '"3","3.7","2.3"']
     lab = rasterize_labels((5, 6), [a, b])
     assert lab.dtype == np.uint16 and lab[2, 3] == 1 and lab[3, 3] == 0 and lab[3, 4] == 1 and lab[0, 0] == 2 and (lab > 0).sum() == 4
+    c = Object({3}); c.fg_offset, c.fg_fragment = np.array([2, 4]), np.array([[1, 1]], bool)          # overlaps a at (2, 4)
+    lab = rasterize_labels((5, 6), [a, b, c])
+    assert lab[2, 5] == 3 and lab[2, 4] in (1, 3) and (lab > 0).sum() == 5
 
 
 @pytest.mark.skipif(not os.path.isdir('/root/reference/superdsm'), reason='the reference is only present in the build container')
@@ -107,30 +110,56 @@ def test_reference_gem_stage_as_a_lockstep_job():
     assert np.allclose([o.energy for o in sink['toy']], z['energy'], rtol=1e-12, atol=1e-12)
 
 
+def _mask_of(o, shape):
+    m = np.zeros(shape, bool)
+    r, c = (int(v) for v in o.fg_offset)
+    h, w = o.fg_fragment.shape
+    m[r:r + h, c:c + w] = o.fg_fragment
+    return m
+
+
+def _split_job(seed, parts, sink):
+    """A job on another GOWT1-shaped image (same hyper-parameters): its candidate list in `parts` consecutive calls."""
+    from workloads.synth import make_workload
+    w = make_workload('gowt1', oversegment=2, max_set_size=2, seed=seed)
+    y = Image(w['y'], w['y_mask'])
+    chunks = np.array_split(np.arange(len(w['footprints'])), parts)
+
+    def job(compute_objects):
+        objs = []
+        for idx in chunks:
+            batch = [Object(w['footprints'][i]) for i in idx]
+            compute_objects(batch, y, w['atoms'], w['dsm_cfg'], None)
+            objs += batch
+        sink[seed] = objs
+        return len(objs)
+    return job
+
+
 @pytest.mark.gpu
-def test_three_gem_streams_in_lockstep_on_the_device():
-    """Three images' GEM streams (5 + 4 + 12 calls) as lock-step jobs: 12 launches instead of 21, every result bit-identical to the
-    job run alone, and the covers' (size, centroid) tables equal to the fixtures (the label-map format of tests/regression)."""
+def test_gem_stream_and_other_images_in_lockstep_on_the_device():
+    """The recorded GEM stream of the GOWT1-shaped image (11 non-empty calls) and two other images of the batch (3 calls each) as
+    lock-step jobs: 11 launches instead of 17, every result bit-identical to the job run alone, and the cover's (size, centroid)
+    table equal to the fixture (the label-map format of tests/regression)."""
     from superdsm_b200.objects import compute_objects
-    names = ('toy', 'bbbc039', 'gowt1')
     sink, alone = {}, {}
-    jobs, meta = [], {}
-    for name in names:
-        job, z, fps, cover, w = _stream_job(name, sink)
-        jobs.append(job); meta[name] = (z, fps, cover, w)
+    job, z, fps, cover, w = _stream_job('gowt1', sink)
     lb = LockstepBatch()
-    counts = lb.run(jobs)
-    assert counts == [len(meta[n][1]) for n in names]
-    ncalls = [int((meta[n][0]['call_len'] > 0).sum()) for n in names]
-    assert lb.launches == max(ncalls) and lb.calls == sum(ncalls)
-    for name in names:
-        job, z, fps, cover, w = _stream_job(name, alone)
-        job(compute_objects)                                               # the same job through the single-image seam
-        for a, b in zip(sink[name], alone[name]):
+    counts = lb.run([job, _split_job(2, 3, sink), _split_job(3, 3, sink)])
+    nonempty = int((z['call_len'] > 0).sum())
+    assert counts[0] == len(fps) and lb.launches == nonempty and lb.calls == nonempty + 6
+    _stream_job('gowt1', alone)[0](compute_objects)                        # the same jobs through the single-image seam
+    _split_job(2, 3, alone)(compute_objects)
+    _split_job(3, 3, alone)(compute_objects)
+    for key in ('gowt1', 2, 3):
+        assert len(sink[key]) == len(alone[key])
+        for a, b in zip(sink[key], alone[key]):
             assert a.energy == b.energy and a.is_optimal == b.is_optimal and a.on_boundary == b.on_boundary
             assert np.array_equal(a.fg_offset, b.fg_offset) and np.array_equal(a.fg_fragment, b.fg_fragment)
-        by_fp = {tuple(sorted(o.footprint)): o for o in sink[name]}
-        rows = object_rows([by_fp[fp] for fp in cover])
-        assert sorted(rows) == sorted(tuple(r) for r in z['stats'].tolist())
-        lab = rasterize_labels(w['y'].shape, [by_fp[fp] for fp in cover])
-        assert len(np.unique(lab)) - 1 == len(rows) and sorted(np.bincount(lab.reshape(-1))[1:].tolist()) == sorted(r[0] for r in rows)
+    by_fp = {tuple(sorted(o.footprint)): o for o in sink['gowt1']}
+    rows = object_rows([by_fp[fp] for fp in cover])
+    assert sorted(rows) == sorted(tuple(r) for r in z['stats'].tolist())
+    lab = rasterize_labels(w['y'].shape, [by_fp[fp] for fp in cover])
+    union = np.zeros(w['y'].shape, bool)
+    for fp in cover: union |= _mask_of(by_fp[fp], union.shape)
+    assert len(np.unique(lab)) - 1 == len(rows) and np.array_equal(lab > 0, union)       # every claimed pixel labelled, covers may overlap
