@@ -151,6 +151,19 @@ int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_t* d_ymask,
                        double background_margin, int32_t n_labels, int32_t* d_atoms_out, uint64_t* d_count, int32_t* d_box,
                        uint8_t* d_scratch, void* stream);
 
+/* sdsm_prepare_image for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments, results
+ * and errors as sdsm_prepare_image, minus d_scratch: the scratch is a file-scope device array inside the library, of
+ * 2 * SDSM_NOALLOC_MAX_PIXELS bytes (8 MiB), held by every GPU that loads the library until the process exits.  Images with
+ * H * W > SDSM_NOALLOC_MAX_PIXELS are refused with SDSM_E_UNSUPPORTED (sdsm_last_error() says why).  The call allocates and
+ * frees nothing (no cudaMalloc / cudaFree, no allocating library routine); inputs and outputs are the caller's.  All calls on
+ * a device share the one array: it keeps the previous call's contents (every call overwrites what it reads, nothing needs
+ * clearing), and two calls that OVERLAP on the GPU (different streams, no ordering between them) race on it -- order them. */
+#define SDSM_NOALLOC_MAX_PIXELS (4 * 1024 * 1024)
+int sdsm_prepare_image_noalloc(sdsm_ctx* ctx, const double* d_y, const uint8_t* d_ymask, const int32_t* d_atoms, int32_t H, int32_t W,
+                               double background_margin, int32_t n_labels, int32_t* d_atoms_out, uint64_t* d_count, int32_t* d_box,
+                               void* stream);
+
 /* The Preprocessing stage on the device (preprocess.py:39-68): d_y = gaussian_filter(g, sigma1) - offset, bit for bit as
  * scipy computes it.  h_w1 / h_w2: HOST arrays with the 2 r + 1 weights of scipy's 1-D Gaussian kernels for sigma1 / sigma2
  * (radius r = int(4 sigma + 0.5)).  offset_clip_abs = offset_clip * g.std() (the caller's numpy reduction; +inf: no clipping,

@@ -47,7 +47,7 @@ class Out(ctypes.Structure):
 EXPORTS = ('sdsm_abi_version', 'sdsm_create', 'sdsm_destroy', 'sdsm_last_error', 'sdsm_set_image', 'sdsm_set_images', 'sdsm_set_params',
            'sdsm_plan_batch', 'sdsm_solve_batch', 'sdsm_eval_candidate', 'sdsm_export_smooth', 'sdsm_trace_solve',
            'sdsm_dfma_peak', 'sdsm_launch_count', 'sdsm_solver_stats', 'sdsm_sweep_eval', 'sdsm_finish_times', 'sdsm_prepare_image',
-           'sdsm_preprocess')
+           'sdsm_preprocess', 'sdsm_prepare_image_noalloc')
 
 _lib = None
 
@@ -71,6 +71,7 @@ def load():
     lib.sdsm_set_images.argtypes = [vp, ctypes.POINTER(ImageDesc), i32]
     lib.sdsm_set_params.argtypes = [vp, ctypes.POINTER(Params)]
     lib.sdsm_prepare_image.argtypes = [vp, vp, vp, vp, i32, i32, ctypes.c_double, i32, vp, vp, vp, vp, vp]
+    lib.sdsm_prepare_image_noalloc.argtypes = [vp, vp, vp, vp, i32, i32, ctypes.c_double, i32, vp, vp, vp, vp]
     lib.sdsm_preprocess.argtypes = [vp, vp, i32, i32, vp, i32, vp, i32, ctypes.c_double, ctypes.c_double, ctypes.c_double, vp, vp, vp]
     lib.sdsm_plan_batch.argtypes = [vp, vp, i32, ctypes.POINTER(Plan)]
     lib.sdsm_solve_batch.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, vp, vp, vp, ctypes.c_size_t, ctypes.POINTER(Out), vp]

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 
@@ -143,6 +144,53 @@ extern "C" int sdsm_prepare_image(sdsm_ctx* ctx, const double* d_y, const uint8_
     ctx->launches += 2;
     CUDA_TRY(ctx, cudaGetLastError());
     return SDSM_OK;
+}
+
+// ---- sdsm_prepare_image without caller scratch and without any allocation -------------------------------------------------
+// The 16-bit vertical distances of the distance transform live in a file-scope device array: every GPU that loads the library
+// holds SDSM_NOALLOC_MAX_PIXELS * 2 bytes until the process exits.  `g_prepare_scratch` below is, in HOST code, only a stand-in
+// for the symbol: its device address is asked for once per device (with that device current) and handed to the kernels.
+static __device__ __align__(256) unsigned char g_prepare_scratch[(size_t)SDSM_NOALLOC_MAX_PIXELS * 2];
+
+static cudaError_t prepare_scratch_address(int device, uint8_t** out)
+{
+    constexpr int MAX_DEVICES = 64;
+    static uint8_t* addr[MAX_DEVICES] = {};              // resolved addresses, one per device
+    static std::mutex lock;
+    if (device < 0 || device >= MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> hold(lock);
+    if (!addr[device]) {
+        int current = -1;
+        cudaError_t e = cudaGetDevice(&current);
+        if (e != cudaSuccess) return e;
+        if (current != device) return cudaErrorInvalidDevice;       // the caller made `device` current; never resolve on another one
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_prepare_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        addr[device] = static_cast<uint8_t*>(p);
+    }
+    *out = addr[device];
+    return cudaSuccess;
+}
+
+extern "C" int sdsm_prepare_image_noalloc(sdsm_ctx* ctx, const double* d_y, const uint8_t* d_ymask, const int32_t* d_atoms, int32_t H, int32_t W,
+                                          double background_margin, int32_t n_labels, int32_t* d_atoms_out, uint64_t* d_count, int32_t* d_box,
+                                          void* stream_)
+{
+    if (!ctx) return SDSM_E_ARG;
+    if (H < 2 || W < 2) return SDSM_E_ARG;
+    if ((long long)H * (long long)W > (long long)SDSM_NOALLOC_MAX_PIXELS) {
+        ctx->err = "sdsm_prepare_image_noalloc: image of " + std::to_string(H) + " x " + std::to_string(W) + " pixels exceeds the built-in scratch of " +
+                   std::to_string((long long)SDSM_NOALLOC_MAX_PIXELS) + " pixels (SDSM_NOALLOC_MAX_PIXELS); use sdsm_prepare_image with caller scratch";
+        return SDSM_E_UNSUPPORTED;
+    }
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    uint8_t* scratch = nullptr;
+    CUDA_TRY(ctx, prepare_scratch_address(ctx->device, &scratch));
+    // Nothing in the scratch has to start at zero: k_edt_cols writes every one of the H * W distances before k_edt_rows reads
+    // them (same stream), and a call with an infinite margin does not touch it.  The contents of the previous call are overwritten.
+    return sdsm_prepare_image(ctx, d_y, d_ymask, d_atoms, H, W, background_margin, n_labels, d_atoms_out, d_count, d_box, scratch, stream_);
 }
 
 extern "C" int sdsm_preprocess(sdsm_ctx* ctx, const double* d_graw, int32_t H, int32_t W, const double* h_w1, int32_t r1, const double* h_w2,
