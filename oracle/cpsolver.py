@@ -45,6 +45,9 @@ RANK_ERROR = 'Rank(A) < p or Rank([H(x); A; Df(x); G]) < n'
 # into an exception; 'saved' uses the derivatives of the restored point there.
 RESTORE_POLICY = 'saved'
 
+#: diagnostics: a list here collects (iteration, pass, first step, trials, accepted step) of every line search
+LS_LOG = None
+
 
 class _State(object):
     __slots__ = ('x', 't', 's', 'z', 'd', 'lmbda', 'rx_x', 'rx_t', 'rznl', 'dx', 'dt', 'dz', 'ds')
@@ -254,6 +257,7 @@ def cp(F, FH, x0, trace=None, maxiters=MAXITERS, restore_policy=None, events=Non
             dz = dz / lmbda
             tmax = max(0.0, -ds, -dz)
             step = 1.0 if tmax == 0 else min(1.0, STEP / tmax)
+            ls_first, ls_trials = step, 0
 
             # "Backtrack until newx is in domain of f": F never leaves its domain here, but the call is
             # made (and cached by the reference, dsm.py:388-418).
@@ -272,6 +276,7 @@ def cp(F, FH, x0, trace=None, maxiters=MAXITERS, restore_policy=None, events=Non
                 newz = z + step * dz2
                 news = s + step * ds2
                 nf0, ng = F(newx)
+                ls_trials += 1
                 ng = np.asarray(ng, dtype=float).reshape(-1)
                 newf = nf0 - newt
                 newrx_x = newz * ng
@@ -350,6 +355,7 @@ def cp(F, FH, x0, trace=None, maxiters=MAXITERS, restore_policy=None, events=Non
                             # reference's SIGALRM time-out (dsm.py:483-489) is what ends it.  Treat as the
                             # time-out would: an exception.
                             raise TimeoutError('cpl line search stalled')
+            if LS_LOG is not None: LS_LOG.append((iters, i, ls_first, ls_trials, step))
 
         x = x + step * dx
         t = t + step * dt

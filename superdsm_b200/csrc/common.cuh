@@ -47,7 +47,8 @@ constexpr int SMALL_N_MAX = SDSM_SMALL_N_MAX;
 constexpr int SMEM_L_CAP = SMALL_N_MAX * (SMALL_N_MAX + 1) / 2;  // doubles of shared memory for the packed Cholesky factor  // systems up to this size are factorised in shared memory, larger ones blocked in global memory / L2
 constexpr int BIG_BLOCK  = SOLVE_BLOCK;
 constexpr int N_COUNTERS = 32;
-constexpr int NVEC       = 12;    // N-vectors of the interior-point solver
+constexpr int SPEC_MAX   = 8;     // line-search trial points one request can evaluate (speculative backtracking, ctrl.cuh)
+constexpr int NVEC       = 12 + 2 * SPEC_MAX;    // N-vectors of the interior-point solver: 12 + the trial points and their gradients
 
 // one task queue: two rings (0: normal, 1: urgent) of `mask + 1` slots each, one ring of 2 (mask + 1) arrival events
 struct Queue {
@@ -91,6 +92,9 @@ struct CState {
     int32_t pc, stage, iters, relaxed, pass, use_xi;
     int32_t req_vec, req_gvec, req_h;      // the pending evaluation: point, where the gradient goes, Hessian wanted
     int32_t status, bits, it1, it2, it3, nf, nh, have1, r_ipm;
+    // speculative backtracking: the pending / last trial request holds spec_n points (x + step beta^k dx, k < spec_n), spec_k is
+    // the one being examined; ls_cnt = trials examined in the current line search, ls_prev = in the previous one (the predictor)
+    int32_t spec_n, spec_k, ls_cnt, ls_prev;
 };
 
 // what the evaluation tasks need to know about a candidate (written by the control task that files the request)
@@ -100,6 +104,7 @@ struct EvalReq {
     int32_t want_h, use_xi;  // want_h: 0 value + gradient, 1 value + gradient + Hessian, 2 Hessian only (value and gradient at this
                              // point are already known: the accepted trial of the line search was evaluated at it)
     int32_t cpt, cpw;      // non-empty cells per CTA-wide evaluation task (chains that stay in one CTA, diagnostics) / per warp item
+    int32_t npts, ld;      // points to evaluate: x + k * ld for k < npts, results in the k-th copy of scrG / xig (npts > 1: no Hessian)
 };
 
 // Workspace carved out of the caller's buffer.  Per-pixel / per-cell / per-table arrays are indexed with the
@@ -122,6 +127,7 @@ struct WS {
     CInfo*    cinfo;       // [n_cand]
     CState*   cstate;      // [n_cand]
     EvalReq*  req;         // [n_cand]
+    size_t    sg_stride, xig_stride;   // doubles between the SPEC_MAX copies of scrG / xig (one per trial point of a request)
     double*   scrG;        // [C * 32]   per-cell value ([31]) + theta gradient ([0..5]) of the last evaluation
     double*   xig;         // [C * 25]   xi gradient of the last evaluation: entry [j * 25 + s] = contribution to grid point j of the
                            //            cell at neighbour position s of j's cell (zero where there is none; zeroed per batch)
@@ -173,8 +179,8 @@ inline Layout make_layout(int64_t P, int64_t C, int64_t T, int64_t V, int64_t M,
     L.o_cinfo = take(sizeof(CInfo) * (size_t)n_cand);
     L.o_cstate = take(sizeof(CState) * (size_t)n_cand);
     L.o_req = take(sizeof(EvalReq) * (size_t)n_cand);
-    L.o_scrG = take(sizeof(double) * SCRG * C);
-    L.o_xig = take(sizeof(double) * NSLOT * C);
+    L.o_scrG = take(sizeof(double) * SCRG * C * SPEC_MAX);
+    L.o_xig = take(sizeof(double) * NSLOT * C * SPEC_MAX);
     L.o_scrH = take(sizeof(double) * SCRH * C);
     L.o_vecs = take(sizeof(double) * V);
     L.o_mats = take(sizeof(double) * M);
@@ -222,6 +228,7 @@ inline WS make_ws(void* base, const Layout& L)
     w.cinfo = (CInfo*)(b + L.o_cinfo);
     w.cstate = (CState*)(b + L.o_cstate);
     w.req = (EvalReq*)(b + L.o_req);
+    w.sg_stride = (size_t)SCRG * (size_t)L.C; w.xig_stride = (size_t)NSLOT * (size_t)L.C;
     w.scrG = (double*)(b + L.o_scrG);
     w.xig = (double*)(b + L.o_xig);
     w.scrH = (double*)(b + L.o_scrH);
@@ -402,10 +409,12 @@ __device__ __forceinline__ void q_put(const WS& ws, const Queue& q, int ring, un
     st_release_u32(q.ev + es, (uint32_t)e + 1u);
 }
 
-// whole CTA: publishes `count` tasks (type, c, first = k * stride for k < count).  Everything the CTA wrote before the call
+constexpr uint32_t PT_SHIFT = 24;          // evaluation items: task.y = trial point << PT_SHIFT | first cell
+// whole CTA: publishes `count` tasks (type, c, first = k * stride for k < count; with per_pt: point k / per_pt, first (k % per_pt) * stride).  Everything the CTA wrote before the call
 // is visible to the consumers of the tasks.  s_base: two unsigned long longs of shared memory.
 template <int BLOCK>
-__device__ __forceinline__ void q_push_range(const WS& ws, const Queue& q, int ring, uint32_t type, uint32_t c, int count, int stride, unsigned long long* s_base)
+__device__ __forceinline__ void q_push_range(const WS& ws, const Queue& q, int ring, uint32_t type, uint32_t c, int count, int stride, unsigned long long* s_base,
+                                             int per_pt = 0x7fffffff)
 {
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -415,7 +424,7 @@ __device__ __forceinline__ void q_push_range(const WS& ws, const Queue& q, int r
     }
     __syncthreads();
     const unsigned long long base = s_base[0], ebase = s_base[1];
-    for (int k = threadIdx.x; k < count; k += BLOCK) q_put(ws, q, ring, base + k, ebase + k, type, c, (uint32_t)(k * stride));
+    for (int k = threadIdx.x; k < count; k += BLOCK) q_put(ws, q, ring, base + k, ebase + k, type, c, ((uint32_t)(k / per_pt) << PT_SHIFT) | (uint32_t)((k % per_pt) * stride));
 }
 
 // whole warp: the same for a warp (everything the WARP wrote before the call is visible to the consumers)

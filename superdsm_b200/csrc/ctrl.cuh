@@ -14,7 +14,9 @@ constexpr int MAX_RELAXED = 8;
 constexpr int EVAL_BUDGET = 50000;   // evaluations of F per candidate (a regular solve needs < 4000: 100 iterations, few trials each)
 constexpr double CP_STEP = 0.99, CP_BETA = 0.5, CP_ALPHA = 0.01;
 
-enum { V_X = 0, V_G, V_DX, V_T, V_NX, V_NG, V_SX, V_SDX, V_RD, V_X0, V_E, V_W };
+enum { V_X = 0, V_G, V_DX, V_T, V_NX, V_NG, V_SX, V_SDX, V_RD, V_X0, V_E, V_W,
+       V_SPX /* SPEC_MAX line-search trial points */, V_SPG = V_SPX + SPEC_MAX /* and their gradients */ };
+static_assert(V_SPG + SPEC_MAX == NVEC, "vector count");
 enum { PC_START = 0, PC_TOP, PC_RESTORED, PC_TRIAL, PC_VAL1, PC_VALINIT, PC_JX, PC_J0, PC_FINAL, PC_DONE, PC_TRACESTART };
 enum { STG_ELL1 = 0, STG_ELL2, STG_DSM, STG_TRACE };
 
@@ -761,6 +763,7 @@ __device__ __forceinline__ void ipm_begin(CState& S)
 {
     S.t = 0.0; S.s = 1.0; S.z = 1.0; S.d = 1.0; S.lm = 1.0;
     S.relaxed = 0; S.iters = 0;
+    S.spec_n = 1; S.spec_k = 0; S.ls_cnt = 0; S.ls_prev = 1;
     S.th1 = S.th2 = S.th3 = 0.0; S.pres0 = S.dres0 = 1.0;
     S.phi0s = S.dphi0s = S.gap0s = S.step0s = S.dsdz0s = S.sigma0s = S.eta0s = 0.0;
     S.sv_t = S.sv_s = S.sv_z = S.sv_d = S.sv_lm = S.sv_dt = S.sv_dz = S.sv_ds = S.sv_resx = S.sv_rznl = S.sv_rxt = 0.0;
@@ -783,6 +786,7 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
     // (dsm.py:483-489, cp_timeout = 300 s) and raises; here the evaluation budget plays that role.
     if (budgeted && S.nf + S.nh >= EVAL_BUDGET) return false;
     S.req_vec = vec; S.req_gvec = gvec; S.req_h = want_h;
+    S.spec_n = 1; S.spec_k = 0;                                 // one point (PC_TRIALREQ may add speculative ones)
     if (want_h) S.nh += 1; else S.nf += 1;                      // evaluation counters (reported in out.info)
     return true;
 }
@@ -794,7 +798,7 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
 // instantiation serves both: the state machine is inlined once (the kernel's code size is an instruction-cache matter).
 template <int BLOCK>
 __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
-                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells, const bool BIG)
+                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells, int spec_max, int spec_retry, const bool BIG)
 {
     const int tid = threadIdx.x;
     // The candidate's state lives in shared memory while the task runs, one copy per warp: all threads compute the same
@@ -813,27 +817,14 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
     setup_problem(P, par, cd, ci, ws);
     const int ld = P.ld;
     double* x = P.V + V_X * ld;  double* g = P.V + V_G * ld;   double* dx = P.V + V_DX * ld; double* tv = P.V + V_T * ld;
-    double* nx = P.V + V_NX * ld; double* ng = P.V + V_NG * ld; double* sx = P.V + V_SX * ld; double* sdx = P.V + V_SDX * ld;
+    double* sx = P.V + V_SX * ld; double* sdx = P.V + V_SDX * ld;
     double* x0 = P.V + V_X0 * ld; double* ev = P.V + V_E * ld; double* w6 = P.V + V_W * ld;
     int32_t* info = out.d_info + (size_t)c * 8;
 
     double f0 = 0.0;
-    if (S.pc != PC_START && S.pc != PC_TRACESTART) {
-        double psi = 0.0;
-        double* gout = P.V + (size_t)S.req_gvec * ld;
-        if (S.req_h == 2) {
-            // Hessian only: value and gradient are those of the accepted trial (same point, same bits: PC_ACCEPT)
-            gather_hessian_block<BLOCK>(P, sm, S.z, S.use_xi ? P.N : 6, S.use_xi ? P.hess_tol : 0.0);
-            f0 = S.f_trial;
-            psi = S.psi_trial;
-        }
-        else if (!S.use_xi) f0 = S.req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
-        else {
-            const double* xe = P.V + (size_t)S.req_vec * ld;
-            f0 = S.req_h ? gather_cells<BLOCK, true>(P, sm, xe, gout, S.z, &psi) : gather_cells<BLOCK, false>(P, sm, xe, gout, S.z, &psi);
-        }
-        S.psi_last = psi;
-    }
+    // there is an evaluation to consume (always, except for the task that starts the candidate); PC_TRIAL sets it again to look
+    // at the next point of a speculative request
+    bool need_gather = S.pc != PC_START && S.pc != PC_TRACESTART;
     bool hres_alt = false;
     bool yield = false;
     bool requested = false;
@@ -845,6 +836,26 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
     } while (0)
 
     while (!yield) {
+        if (need_gather) {
+            need_gather = false;
+            double psi = 0.0;
+            const int pt = S.pc == PC_TRIAL ? S.spec_k : 0;          // the point of the request whose results are wanted
+            double* gout = P.V + (size_t)(S.req_gvec + pt) * ld;
+            P.scrG = ws.scrG + (size_t)pt * ws.sg_stride + (size_t)cd.cell_off * SCRG;
+            P.xig = ws.xig + (size_t)pt * ws.xig_stride + (size_t)cd.cell_off * NSLOT;
+            if (S.req_h == 2) {
+                // Hessian only: value and gradient are those of the accepted trial (same point, same bits: PC_ACCEPT)
+                gather_hessian_block<BLOCK>(P, sm, S.z, S.use_xi ? P.N : 6, S.use_xi ? P.hess_tol : 0.0);
+                f0 = S.f_trial;
+                psi = S.psi_trial;
+            }
+            else if (!S.use_xi) f0 = S.req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
+            else {
+                const double* xe = P.V + (size_t)(S.req_vec + pt) * ld;
+                f0 = S.req_h ? gather_cells<BLOCK, true>(P, sm, xe, gout, S.z, &psi) : gather_cells<BLOCK, false>(P, sm, xe, gout, S.z, &psi);
+            }
+            S.psi_last = psi;
+        }
         const int Nc = S.use_xi ? P.N : 6;
         const int tri_n = Nc * (Nc + 1) / 2;
         const bool l_sm = !BIG && tri_n <= sm.lcap && Nc <= CTRL_BPAD;
@@ -1001,18 +1012,51 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             S.step = (tmax == 0.0) ? 1.0 : fmin(1.0, CP_STEP / tmax);
             S.phi = S.th1 * S.gap + S.th2 * S.resx + S.th3 * S.resznl;
             S.dphi = (S.pass == 0) ? -S.phi : (-S.th1 * (1 - S.sigma) * S.gap - S.th2 * (1 - S.eta) * S.resx - S.th3 * (1 - S.eta) * S.resznl);
+            if (S.ls_cnt > 0) S.ls_prev = S.ls_cnt;          // a new line search starts: the last one examined that many trials
+            S.ls_cnt = 0;
             S.pc = PC_TRIALREQ;
             break;
         }
         case PC_TRIALREQ: {
+            // Speculative backtracking.  The line search examines x + step dx, x + beta step dx, ... one after the other, and every
+            // trial costs a round trip through the evaluation warps.  One request therefore evaluates the next K points of that
+            // sequence (the same expressions in the same arithmetic as K sequential requests would use); PC_TRIAL then examines
+            // them in order and stops at the first one the line search accepts, so decisions and results are those of the
+            // sequential search, bit for bit.  K is predicted: line searches that follow each other (the two passes of an
+            // iteration in particular) tend to need the same number of trials.
+            int K = 1;
+            if (spec_max > 1) K = S.ls_cnt == 0 ? S.ls_prev : (S.ls_cnt < spec_retry ? spec_retry : S.ls_cnt);
+            K = K < 1 ? 1 : (K > spec_max ? spec_max : K);
             __syncthreads();
-            for (int i = tid; i < Nc; i += BLOCK) nx[i] = x[i] + S.step * dx[i];
+            {
+                double st = S.step;
+                for (int k = 0; k < K; ++k) {
+                    double* px = P.V + (size_t)(V_SPX + k) * ld;
+                    for (int i = tid; i < Nc; i += BLOCK) px[i] = x[i] + st * dx[i];
+                    st *= CP_BETA;
+                }
+            }
             __syncthreads();
-            REQUEST(V_NX, V_NG, 0, PC_TRIAL, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+            REQUEST(V_SPX, V_SPG, 0, PC_TRIAL, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+            if (requested && K > 1) {
+                // a later point that holds a NaN ends the request before it (the sequential search would have stopped there)
+                int Ke = 1;
+                for (int k = 1; k < K; ++k) {
+                    const double* px = P.V + (size_t)(V_SPX + k) * ld;
+                    int bad = 0;
+                    for (int i = tid; i < Nc; i += BLOCK) bad |= isnan(px[i]);
+                    if (__syncthreads_or(bad)) break;
+                    Ke = k + 1;
+                }
+                S.spec_n = Ke;
+            }
             break;
         }
         case PC_TRIAL: {                     // F and Df at x + step dx are in (f0, ng)
             const double step = S.step;
+            const double* ng = P.V + (size_t)(V_SPG + S.spec_k) * ld;
+            bool resumed = false;
+            S.ls_cnt += 1;
             S.f_trial = f0; S.psi_trial = S.psi_last;
             const double newt = S.t + step * S.dt, newz = S.z + step * S.dz2, news = S.s + step * S.ds2;
             const double newf = f0 - newt;
@@ -1065,11 +1109,20 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
                         S.dz2 = S.dz * S.lm / S.d; S.ds2 = S.ds * S.lm * S.d;
                         S.dsdz = S.dsdz0s; S.sigma = S.sigma0s; S.eta = S.eta0s;
                         S.relaxed = -1;
+                        resumed = true;
                     } else if (newphi <= S.phi + CP_ALPHA * step * S.dphi) { backtrack = false; S.relaxed = -1; }
                     else { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }   // cvxopt would repeat this trial until the reference's SIGALRM time-out fires
                 }
             }
-            if (backtrack) S.pc = PC_TRIALREQ;
+            if (backtrack) {
+                if (resumed) { S.ls_cnt = 0; S.pc = PC_TRIALREQ; }                     // another point, another direction
+                else if (S.spec_k + 1 < S.spec_n) {
+                    // the next trial is already evaluated: what a request for it would have checked, then look at it
+                    if (S.nf + S.nh >= EVAL_BUDGET) { S.r_ipm = 2; S.pc = PC_IPMDONE; }
+                    else { S.spec_k += 1; S.nf += 1; need_gather = true; }
+                }
+                else S.pc = PC_TRIALREQ;
+            }
             else if (S.pass == 0) { S.pass = 1; S.pc = PC_PASS; }
             else S.pc = PC_ACCEPT;
             break;
@@ -1089,7 +1142,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             // x is the accepted trial point (the same expression in the same arithmetic as PC_TRIALREQ), where value and gradient
             // are known (S.f_trial, ng): the reference evaluates F there again -- with identical results, dsm.py:388-418 caches them
             // -- so only the Hessian is asked for
-            for (int i = tid; i < Nc; i += BLOCK) g[i] = ng[i];
+            { const double* ng = P.V + (size_t)(V_SPG + S.spec_k) * ld; for (int i = tid; i < Nc; i += BLOCK) g[i] = ng[i]; }
             __syncthreads();
             REQUEST(V_X, V_G, 2, PC_TOP, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
             break;
@@ -1213,6 +1266,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = S.z * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;
             rq.cpt = P.n_ne <= task_small_cells ? EVAL_WARPS : EVAL_CELLS;
             rq.cpw = P.n_ne <= task_small_cells ? 1 : (P.n_ne <= 4 * task_small_cells ? 2 : WARP_ITEM_CELLS);
+            rq.npts = S.spec_n; rq.ld = P.ld;
             ws.req[c] = rq;
         }
     }

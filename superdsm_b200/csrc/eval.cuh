@@ -491,11 +491,11 @@ constexpr size_t EVAL_SMEM = sizeof(double) * EVAL_WARPS * TILE_DOUBLES;
 // -- a warp takes the next cell when it is done with its last one (cells differ in their pixel counts) -- and leave the
 // per-cell value / gradient / Hessian in scrG / scrH.  smem_eval: EVAL_SMEM bytes; *s_next == 0 on entry (all threads
 // synchronised after it was set), and the caller synchronises the CTA after the call.
-__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int idx,
+__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int idx, int pt,
                                           double* Tt, int* slotj);
 
 __device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first,
-                                          double* smem_eval, int* s_slotj, int* s_next)
+                                          double* smem_eval, int* s_slotj, int* s_next, int npts = 1)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int count = min(ws.req[c].cpt, ws.cinfo[c].n_ne - first);
@@ -503,12 +503,12 @@ __device__ __forceinline__ void eval_task(const Par& par, const sdsm_cand* __res
         int i = 0;
         if (lane == 0) i = atomicAdd(s_next, 1);
         i = __shfl_sync(0xffffffffu, i, 0);
-        if (i >= count) break;
-        eval_cell(par, cands, ws, c, first + i, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * WARP_INTS);
+        if (i >= count * npts) break;                // the cells of all npts trial points of the request share the warps
+        eval_cell(par, cands, ws, c, first + i % count, i / count, smem_eval + warp * TILE_DOUBLES, s_slotj + warp * WARP_INTS);
     }
 }
 
-__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int idx,
+__device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int idx, int pt,
                                           double* Tt, int* slotj)
 {
     const int lane = threadIdx.x & 31;
@@ -516,14 +516,15 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     const int64_t pix_off = cd->pix_off, cell_off = cd->cell_off, tab_off = cd->tab_off;
     const int cell = ws.cell_list[cell_off + idx];
     const int h = cd->h;
-    const EvalReq rq = ws.req[c];
+    EvalReq rq = ws.req[c];
+    rq.x += (size_t)pt * rq.ld;                      // the pt-th trial point of the request (pt = 0 unless it is a speculative one)
     const int32_t* cstart = ws.cell_start + cell_off;
     const int st = cstart[cell], npix = cstart[cell + 1] - st;
     const double* py = ws.pix_y + pix_off + st;
     const uint32_t* prc = ws.pix_rc + pix_off + st;
     const double* xr = ws.xtab + tab_off;
     const double* xc = xr + h;
-    double* sg = ws.scrG + (size_t)(cell_off + cell) * SCRG;
+    double* sg = ws.scrG + (size_t)pt * ws.sg_stride + (size_t)(cell_off + cell) * SCRG;
     double* sh = ws.scrH + (size_t)(cell_off + cell) * SCRH;
     const int cw = ws.cinfo[c].cw;
     const int ca = cell / cw, cb = cell - ca * cw;
@@ -550,7 +551,7 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     }
     __syncwarp();
     const float* gcell = ws.gval + (size_t)GROW * (pix_off + st);
-    double* xig = ws.xig + (size_t)cell_off * NSLOT;
+    double* xig = ws.xig + (size_t)pt * ws.xig_stride + (size_t)cell_off * NSLOT;
     if (rq.want_h == 2) eval_cell_xi<2>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
     else if (rq.want_h) eval_cell_xi<1>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);
     else eval_cell_xi<0>(py, prc, gcell, npix, am, xr, xc, rq.x, par.sparsity_tol, Tt, slotj, sg, xig, sh);

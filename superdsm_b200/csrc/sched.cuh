@@ -37,6 +37,10 @@ struct SolveArgs {
     int solo_cells;          // candidates with at most this many non-empty cells run their chain inside one CTA
     int task_small_cells;    // candidates with at most this many non-empty cells get one cell per evaluation item
     int hi_evals;            // a candidate that has needed more evaluations of F than this becomes urgent (ring 1)
+    int spec_max;            // trial points per line-search request (1: none speculative)
+    int spec_retry;          // points of the second request of a line search whose first request had one point
+    int spec_solo;           // chains inside one control CTA speculate too
+    int spec_prio;           // of the chains that go through the queue, only urgent ones (ring 1) speculate
     int n_ctrl_ctas;         // CTAs [0, n_ctrl_ctas) run control tasks, the warps of the others evaluation / Hessian-row items
     unsigned long long timeout_ns;   // watchdog: the kernel is aborted when no control task has finished for this long
     double* trace;           // diagnostics (STG_TRACE) or nullptr
@@ -87,10 +91,10 @@ __global__ void k_seed(WS ws, const int32_t* __restrict__ order, int n_first, in
 }
 
 // one warp: the evaluation item (c, first) = cells cell_list[first .. first + cpw) of candidate c's pending request
-__device__ __forceinline__ void eval_item(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, double* Tt, int* slotj)
+__device__ __forceinline__ void eval_item(const Par& par, const sdsm_cand* __restrict__ cands, const WS& ws, int c, int first, int pt, double* Tt, int* slotj)
 {
     const int count = min(ws.req[c].cpw, ws.cinfo[c].n_ne - first);
-    for (int i = 0; i < count; ++i) eval_cell(par, cands, ws, c, first + i, Tt, slotj);
+    for (int i = 0; i < count; ++i) eval_cell(par, cands, ws, c, first + i, pt, Tt, slotj);
 }
 
 // the warp that finished an item of candidate c's current stage: the last one to finish starts the next stage
@@ -159,7 +163,7 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
             const uint32_t type = task.x >> T_SHIFT;
             const int c = (int)(task.x & T_CMASK);
             if (type == T_EVAL) {
-                eval_item(par, cands, ws, c, (int)task.y, Tt, slotj);
+                eval_item(par, cands, ws, c, (int)(task.y & ((1u << PT_SHIFT) - 1u)), (int)(task.y >> PT_SHIFT), Tt, slotj);
                 finish_item(ws, type, c);
                 cyc_eval += (unsigned long long)(clock64() - c1); n_eval += 1;
             } else {
@@ -216,7 +220,12 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
                 Sm sm;
                 bool requested;
                 if (big) carve_smem_big(sm, smem_solve); else carve_smem(sm, smem_solve, args.lcap);
-                requested = ctrl_step<BLOCK>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells, big);
+                // (the same criterion as `solo` below, before the step: only a heuristic, the results do not depend on it)
+                const bool solo_before = ci.n_ne <= EVAL_WARPS || (ci.n_ne <= args.solo_cells && ws.cstate[c].nf + ws.cstate[c].nh <= args.hi_evals);
+                // chains inside this CTA: the extra points run on warps of this CTA that a single point leaves idle; chains that go through
+                // the queue: extra points compete with everybody's evaluations, so (spec_prio) only the urgent ones get them
+                const int spec_max = (solo_before ? !args.spec_solo : (args.spec_prio && !ws.prio[c])) ? 1 : args.spec_max;
+                requested = ctrl_step<BLOCK>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells, spec_max, args.spec_retry, big);
                 if (tid == 0) { ws.cstate[c].ns_ctrl += globaltimer_ns() - t_link; q_progress(ws); }
                 if (!requested) {
                     if (tid == 0) {
@@ -235,14 +244,15 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
                     // publishing is the LAST thing a control task does: the candidate's next control task may start on another
                     // SM as soon as the evaluations have finished
                     const int cpw = ws.req[c].cpw;
-                    const int n_items = (ci.n_ne + cpw - 1) / cpw;
+                    const int per_pt = (ci.n_ne + cpw - 1) / cpw;
+                    const int n_items = per_pt * ws.req[c].npts;            // the cells of every trial point of the request
                     if (tid == 0) {
                         ws.pending[c] = n_items;
                         // a chain that turns out long becomes urgent: it would otherwise finish long after the bulk of the batch
                         if (!ws.prio[c]) { const CState* S = ws.cstate + c; if (S->nf + S->nh > args.hi_evals) { ws.prio[c] = 1; ++n_promoted; } }
                     }
                     __syncthreads();
-                    q_push_range<BLOCK>(ws, ws.qe, ws.prio[c], T_EVAL, (uint32_t)c, n_items, cpw, s_base);
+                    q_push_range<BLOCK>(ws, ws.qe, ws.prio[c], T_EVAL, (uint32_t)c, n_items, cpw, s_base, per_pt);
                     break;
                 }
                 // the whole chain in this CTA: evaluate here and go on
@@ -252,7 +262,7 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
                 for (int k = 0; k < n_tasks; ++k) {
                     if (tid == 0) s_next = 0;
                     __syncthreads();
-                    eval_task(par, cands, ws, c, k * cpt, (double*)smem_solve, s_slotj, &s_next);
+                    eval_task(par, cands, ws, c, k * cpt, (double*)smem_solve, s_slotj, &s_next, rq.npts);
                     __syncthreads();
                 }
                 if (rq.want_h && rq.use_xi)
@@ -292,7 +302,7 @@ k_diag_eval_begin(Par par, const sdsm_cand* __restrict__ cands, int c, WS ws, co
     for (size_t i = tid; i < (size_t)N * N; i += SOLVE_BLOCK) P.H[i] = 0.0;
     bad = __syncthreads_or(bad);
     if (tid == 0) {
-        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = P.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.cpw = 1;
+        EvalReq rq; rq.x = nx; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = P.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.cpw = 1; rq.npts = 1; rq.ld = 0;
         ws.req[c] = rq;
         ws.cstate[c].pc = bad ? -1 : PC_DONE;
     }
@@ -401,7 +411,7 @@ k_sweep_prep(Par par, const sdsm_cand* __restrict__ cands, int n_cand, WS ws, in
         __syncthreads();
         if (threadIdx.x == 0) {
             const int ld = 6 + (par.has_smooth ? cd.cell_cap : 0);
-            EvalReq rq; rq.x = ws.vecs + cd.vec_off + (size_t)V_X * ld; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = ci.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.cpw = 1;
+            EvalReq rq; rq.x = ws.vecs + cd.vec_off + (size_t)V_X * ld; rq.hfac = 1.0; rq.want_h = want_h; rq.use_xi = ci.m > 0 ? 1 : 0; rq.cpt = EVAL_CELLS; rq.cpw = 1; rq.npts = 1; rq.ld = 0;
             ws.req[c] = rq;
             s_base = atomicAdd(ws.counters + Q_TAIL, (unsigned long long)count);
         }

@@ -38,6 +38,10 @@ struct sdsm_ctx {
     bool ctrl_ctas_fixed = false;            // SDSM_CTRL_CTAS given: no adaptation to the batch
     int ctrl_ctas = 48;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
     int hi_evals = 300;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
+    int spec_max = SPEC_MAX;                 // SDSM_SPEC_MAX: trial points per line-search request (1: no speculative backtracking)
+    int spec_retry = 4;                      // SDSM_SPEC_RETRY: points of the request after a first request of one point was rejected
+    int spec_prio = 1;                       // SDSM_SPEC_PRIO: 1 = of the chains that go through the queue only the urgent ones speculate
+    int spec_solo = 1;                       // SDSM_SPEC_SOLO: 1 = chains inside one control CTA speculate too (their points are evaluated in that CTA)
     double ctrl_share = 0.95;                // SDSM_CTRL_SHARE: share of the remaining grid the control CTAs get per unit of solo work
     std::string err;
 };
@@ -86,6 +90,10 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     if (const char* e = getenv("SDSM_TIMEOUT_S")) ctx->timeout_s = atof(e);
     if (const char* e = getenv("SDSM_HI_FRAC")) ctx->hi_frac = atof(e);
     if (const char* e = getenv("SDSM_HI_EVALS")) ctx->hi_evals = atoi(e);
+    if (const char* e = getenv("SDSM_SPEC_MAX")) { ctx->spec_max = atoi(e); if (ctx->spec_max < 1) ctx->spec_max = 1; if (ctx->spec_max > SPEC_MAX) ctx->spec_max = SPEC_MAX; }
+    if (const char* e = getenv("SDSM_SPEC_RETRY")) { ctx->spec_retry = atoi(e); if (ctx->spec_retry < 1) ctx->spec_retry = 1; }
+    if (const char* e = getenv("SDSM_SPEC_SOLO")) ctx->spec_solo = atoi(e) != 0;
+    if (const char* e = getenv("SDSM_SPEC_PRIO")) ctx->spec_prio = atoi(e) != 0;
     if (const char* e = getenv("SDSM_CTRL_SHARE")) ctx->ctrl_share = atof(e);
     if (const char* e = getenv("SDSM_CTRL_CTAS")) { ctx->ctrl_ctas = atoi(e); ctx->ctrl_ctas_fixed = true; }
     return SDSM_OK;
@@ -358,6 +366,10 @@ static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_can
     args.solo_cells = solo_cells_of(ctx);
     args.task_small_cells = ctx->task_small_cells;
     args.hi_evals = ctx->hi_evals;
+    args.spec_max = ctx->spec_max;
+    args.spec_retry = ctx->spec_retry;
+    args.spec_solo = ctx->spec_solo;
+    args.spec_prio = ctx->spec_prio;
     args.n_ctrl_ctas = ctx->ctrl_ctas;
     args.timeout_ns = (unsigned long long)(ctx->timeout_s * 1e9);
     args.trace = trace;
@@ -385,7 +397,7 @@ extern "C" int sdsm_solve_batch(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     WS ws = make_ws(d_workspace, L);
     CUDA_TRY(ctx, cudaMemsetAsync(ws.cstate, 0, sizeof(CState) * (size_t)n_cand, stream));
-    CUDA_TRY(ctx, cudaMemsetAsync(ws.xig, 0, sizeof(double) * NSLOT * (size_t)L.C, stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.xig, 0, sizeof(double) * NSLOT * (size_t)L.C * SPEC_MAX, stream));
     CUDA_TRY(ctx, cudaMemsetAsync(out->d_fgmask, 0, (size_t)plan->fgmask_len, stream));
 
     const int pack_grid = n_cand < 8 * ctx->sm_count ? n_cand : 8 * ctx->sm_count;
