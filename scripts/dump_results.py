@@ -27,7 +27,10 @@ def dump(path, names):
         out[f'{name}_fgbox'] = res.fgbox.copy()
         out[f'{name}_fgsum'] = np.array([int(res.foreground(k)[1].sum()) if res.status[k] < 2 else -1 for k in range(K)])
         out[f'{name}_ms'] = np.array(ts) * 1e3
-        print(name, K, 'candidates', 'ms', [round(t * 1e3, 1) for t in ts], 'nf', int(res.info[:, 6].sum()), 'nh', int(res.info[:, 7].sum()), flush=True)
+        st = eng.solver_stats(); tot = max(st['cyc_total'], 1); wtot = max(st['cyc_wtotal'], 1)
+        print(name, K, 'candidates', 'ms', [round(t * 1e3, 1) for t in ts], 'nf', int(res.info[:, 6].sum()), 'nh', int(res.info[:, 7].sum()),
+              'ctrl busy %.3f eval %.3f hrows %.3f widle %.3f' % (st['cyc_ctrl'] / tot, st['cyc_eval'] / wtot, st['cyc_hrows'] / wtot, st['cyc_widle'] / wtot),
+              {k: st[k] for k in ('n_eval', 'n_hrows', 'n_ctrl')}, flush=True)
     np.savez_compressed(path, **out)
 
 

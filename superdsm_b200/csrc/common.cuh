@@ -87,6 +87,7 @@ struct CState {
     double bt, uz0, vt, gux, gux_res, gex;
     double sigma, eta, step, dt, dz, ds, dsdz, dz2, ds2;
     double val1, psi_last, energy;
+    double z_spec;                         // the z a speculative Hessian was scaled with (spec_h)
     double f_trial, psi_trial;             // scaled value / psi of the last line-search trial (= the next iterate when it is accepted)
     unsigned long long ns_ctrl;            // diagnostics: time spent in this candidate's control tasks so far (ns)
     int32_t pc, stage, iters, relaxed, pass, use_xi;
@@ -95,6 +96,7 @@ struct CState {
     // speculative backtracking: the pending / last trial request holds spec_n points (x + step beta^k dx, k < spec_n), spec_k is
     // the one being examined; ls_cnt = trials examined in the current line search, ls_prev = in the previous one (the predictor)
     int32_t spec_n, spec_k, ls_cnt, ls_prev;
+    int32_t spec_h, spec_pad;              // spec_h: the pending / last trial was evaluated with its Hessian (PC_TRIALREQ)
 };
 
 // what the evaluation tasks need to know about a candidate (written by the control task that files the request)

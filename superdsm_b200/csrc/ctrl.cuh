@@ -763,7 +763,7 @@ __device__ __forceinline__ void ipm_begin(CState& S)
 {
     S.t = 0.0; S.s = 1.0; S.z = 1.0; S.d = 1.0; S.lm = 1.0;
     S.relaxed = 0; S.iters = 0;
-    S.spec_n = 1; S.spec_k = 0; S.ls_cnt = 0; S.ls_prev = 1;
+    S.spec_n = 1; S.spec_k = 0; S.ls_cnt = 0; S.ls_prev = 1; S.spec_h = 0; S.spec_pad = 0; S.z_spec = 0.0;
     S.th1 = S.th2 = S.th3 = 0.0; S.pres0 = S.dres0 = 1.0;
     S.phi0s = S.dphi0s = S.gap0s = S.step0s = S.dsdz0s = S.sigma0s = S.eta0s = 0.0;
     S.sv_t = S.sv_s = S.sv_z = S.sv_d = S.sv_lm = S.sv_dt = S.sv_dz = S.sv_ds = S.sv_resx = S.sv_rznl = S.sv_rxt = 0.0;
@@ -786,7 +786,7 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
     // (dsm.py:483-489, cp_timeout = 300 s) and raises; here the evaluation budget plays that role.
     if (budgeted && S.nf + S.nh >= EVAL_BUDGET) return false;
     S.req_vec = vec; S.req_gvec = gvec; S.req_h = want_h;
-    S.spec_n = 1; S.spec_k = 0;                                 // one point (PC_TRIALREQ may add speculative ones)
+    S.spec_n = 1; S.spec_k = 0; S.spec_h = 0;                   // one point, as asked (PC_TRIALREQ may add speculative work)
     if (want_h) S.nh += 1; else S.nf += 1;                      // evaluation counters (reported in out.info)
     return true;
 }
@@ -798,7 +798,7 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
 // instantiation serves both: the state machine is inlined once (the kernel's code size is an instruction-cache matter).
 template <int BLOCK>
 __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
-                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells, int spec_max, int spec_retry, const bool BIG)
+                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells, int spec_max, int spec_retry, int spec_hess, const bool BIG)
 {
     const int tid = threadIdx.x;
     // The candidate's state lives in shared memory while the task runs, one copy per warp: all threads compute the same
@@ -840,19 +840,20 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             need_gather = false;
             double psi = 0.0;
             const int pt = S.pc == PC_TRIAL ? S.spec_k : 0;          // the point of the request whose results are wanted
+            const int req_h = S.pc == PC_TRIAL ? 0 : S.req_h;        // (a trial evaluated with its Hessian: that is gathered when it is accepted)
             double* gout = P.V + (size_t)(S.req_gvec + pt) * ld;
             P.scrG = ws.scrG + (size_t)pt * ws.sg_stride + (size_t)cd.cell_off * SCRG;
             P.xig = ws.xig + (size_t)pt * ws.xig_stride + (size_t)cd.cell_off * NSLOT;
-            if (S.req_h == 2) {
+            if (req_h == 2) {
                 // Hessian only: value and gradient are those of the accepted trial (same point, same bits: PC_ACCEPT)
                 gather_hessian_block<BLOCK>(P, sm, S.z, S.use_xi ? P.N : 6, S.use_xi ? P.hess_tol : 0.0);
                 f0 = S.f_trial;
                 psi = S.psi_trial;
             }
-            else if (!S.use_xi) f0 = S.req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
+            else if (!S.use_xi) f0 = req_h ? gather_poly<BLOCK, true>(P, sm, gout, S.z, &psi) : gather_poly<BLOCK, false>(P, sm, gout, S.z, &psi);
             else {
                 const double* xe = P.V + (size_t)(S.req_vec + pt) * ld;
-                f0 = S.req_h ? gather_cells<BLOCK, true>(P, sm, xe, gout, S.z, &psi) : gather_cells<BLOCK, false>(P, sm, xe, gout, S.z, &psi);
+                f0 = req_h ? gather_cells<BLOCK, true>(P, sm, xe, gout, S.z, &psi) : gather_cells<BLOCK, false>(P, sm, xe, gout, S.z, &psi);
             }
             S.psi_last = psi;
         }
@@ -1038,6 +1039,21 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             }
             __syncthreads();
             REQUEST(V_SPX, V_SPG, 0, PC_TRIAL, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
+            if (requested && K == 1 && spec_hess && S.pass == 1 && S.ls_cnt == 0 && S.ls_prev == 1) {
+                // Speculative Hessian.  The first pass of this iteration accepted its first trial, so this pass almost certainly
+                // will too (the two passes of an iteration need the same number of trials nearly always), and the accepted point
+                // is the next iterate, whose Hessian is the next thing asked for: evaluate it with the trial (one pass over the
+                // pixels instead of two, one round trip less).  The rows the T_HG tasks write are scaled with the z of the next
+                // iterate, which only depends on the step: PC_ACCEPT's expressions.  H of the current iterate is not needed any
+                // more (it is factored, and the Newton system is solved).
+                const double ds = (1.0 + S.step * S.ds) * S.lm;
+                const double dz = (1.0 + S.step * S.dz) * S.lm;
+                const double sq_s = sqrt(ds), sq_z = sqrt(dz);
+                const double d_new = S.d * sq_s / sq_z;
+                const double lm_new = sq_s * sq_z;
+                S.z_spec = lm_new / d_new;
+                S.req_h = 1; S.spec_h = 1;
+            }
             if (requested && K > 1) {
                 // a later point that holds a NaN ends the request before it (the sequential search would have stopped there)
                 int Ke = 1;
@@ -1114,6 +1130,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
                     else { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }   // cvxopt would repeat this trial until the reference's SIGALRM time-out fires
                 }
             }
+            if (backtrack) S.spec_h = 0;                 // (a Hessian evaluated with this trial is of no use)
             if (backtrack) {
                 if (resumed) { S.ls_cnt = 0; S.pc = PC_TRIALREQ; }                     // another point, another direction
                 else if (S.spec_k + 1 < S.spec_n) {
@@ -1144,6 +1161,17 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             // -- so only the Hessian is asked for
             { const double* ng = P.V + (size_t)(V_SPG + S.spec_k) * ld; for (int i = tid; i < Nc; i += BLOCK) g[i] = ng[i]; }
             __syncthreads();
+            if (S.spec_h && S.z_spec == S.z) {
+                // the Hessian at x came with the trial: what the request for it would have checked and counted, then on to PC_TOP
+                S.spec_h = 0;
+                if (S.nf + S.nh >= EVAL_BUDGET) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }
+                S.nh += 1;
+                gather_hessian_block<BLOCK>(P, sm, S.z, Nc, S.use_xi ? P.hess_tol : 0.0);
+                f0 = S.f_trial; S.psi_last = S.psi_trial;
+                S.pc = PC_TOP;
+                break;
+            }
+            S.spec_h = 0;
             REQUEST(V_X, V_G, 2, PC_TOP, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
             break;
         }
@@ -1263,7 +1291,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
     if (tid == 0) {
         if (requested) {
             EvalReq rq;
-            rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = S.z * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;
+            rq.x = P.V + (size_t)S.req_vec * P.ld; rq.hfac = (S.spec_h ? S.z_spec : S.z) * P.scale_cp; rq.want_h = S.req_h; rq.use_xi = S.use_xi;
             rq.cpt = P.n_ne <= task_small_cells ? EVAL_WARPS : EVAL_CELLS;
             rq.cpw = P.n_ne <= task_small_cells ? 1 : (P.n_ne <= 4 * task_small_cells ? 2 : WARP_ITEM_CELLS);
             rq.npts = S.spec_n; rq.ld = P.ld;
