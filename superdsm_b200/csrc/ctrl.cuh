@@ -798,7 +798,7 @@ __device__ bool prepare_request(const Prob& P, CState& S, int vec, int gvec, int
 // instantiation serves both: the state machine is inlined once (the kernel's code size is an instruction-cache matter).
 template <int BLOCK>
 __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const sdsm_cand& cd, const CInfo& ci, const WS& ws, int c,
-                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells, int spec_max, int spec_retry, int spec_hess, const bool BIG)
+                          Sm& sm, const sdsm_out& out, double* trace, int task_small_cells, int spec_max, int spec_eager, int spec_retry, int spec_hess, int spec_skip, const bool BIG)
 {
     const int tid = threadIdx.x;
     // The candidate's state lives in shared memory while the task runs, one copy per warp: all threads compute the same
@@ -1019,14 +1019,42 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             break;
         }
         case PC_TRIALREQ: {
+            if (spec_skip && S.pass == 0 && 0 <= S.relaxed && S.relaxed < MAX_RELAXED) {
+                // First pass while relaxed steps are allowed: cp accepts or rejects the trial on newgap alone, which is a function
+                // of the step (PC_TRIAL: the merit function is only consulted when relaxed is -1 or MAX_RELAXED).  cp evaluates F
+                // at every trial point all the same, but nothing of what F returns there is ever used (the second pass overwrites
+                // it), so the whole first-pass search runs here, without evaluations.  What an evaluation can do besides returning
+                // values is kept: a NaN in the point raises (prepare_request), the budget stands in for the time-out, and the
+                // trials are counted as the evaluations the reference makes.
+                for (;;) {
+                    const double step = S.step;
+                    int bad = 0;
+                    for (int i = tid; i < Nc; i += BLOCK) bad |= isnan(x[i] + step * dx[i]);
+                    if (__syncthreads_or(bad) || S.nf + S.nh >= EVAL_BUDGET) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }
+                    S.nf += 1; S.ls_cnt += 1;
+                    const double newgap = (1.0 - (1.0 - S.sigma) * step) * S.gap + step * step * S.dsdz;
+                    if (newgap <= (1.0 - CP_ALPHA * step) * S.gap) {
+                        const double r = newgap / S.gap;
+                        S.sigma = fmin(r, r * r * r);
+                        S.eta = 0.0;
+                        S.pass = 1; S.pc = PC_PASS;
+                        break;
+                    }
+                    S.step *= CP_BETA;
+                }
+                break;
+            }
             // Speculative backtracking.  The line search examines x + step dx, x + beta step dx, ... one after the other, and every
             // trial costs a round trip through the evaluation warps.  One request therefore evaluates the next K points of that
             // sequence (the same expressions in the same arithmetic as K sequential requests would use); PC_TRIAL then examines
             // them in order and stops at the first one the line search accepts, so decisions and results are those of the
             // sequential search, bit for bit.  K is predicted: line searches that follow each other (the two passes of an
             // iteration in particular) tend to need the same number of trials.
+            // The first request of the second pass is a confident one (its predictor is the first pass of the same iteration);
+            // the others are made only for candidates allowed to waste evaluations (spec_eager).
             int K = 1;
-            if (spec_max > 1) K = S.ls_cnt == 0 ? S.ls_prev : (S.ls_cnt < spec_retry ? spec_retry : S.ls_cnt);
+            if (S.ls_cnt == 0) { if (spec_eager || S.pass == 1) K = S.ls_prev; }
+            else if (spec_eager) K = S.ls_cnt < spec_retry ? spec_retry : S.ls_cnt;
             K = K < 1 ? 1 : (K > spec_max ? spec_max : K);
             __syncthreads();
             {

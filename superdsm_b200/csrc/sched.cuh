@@ -40,8 +40,9 @@ struct SolveArgs {
     int spec_max;            // trial points per line-search request (1: none speculative)
     int spec_retry;          // points of the second request of a line search whose first request had one point
     int spec_solo;           // chains inside one control CTA speculate too
+    int spec_skip;           // first-pass line searches that do not depend on F run without evaluations
     int spec_hess;           // a trial that will probably be accepted is evaluated with its Hessian
-    int spec_prio;           // of the chains that go through the queue, only urgent ones (ring 1) speculate
+    int spec_prio;           // of the chains that go through the queue, only urgent ones (ring 1) make requests on an unconfident prediction
     int n_ctrl_ctas;         // CTAs [0, n_ctrl_ctas) run control tasks, the warps of the others evaluation / Hessian-row items
     unsigned long long timeout_ns;   // watchdog: the kernel is aborted when no control task has finished for this long
     double* trace;           // diagnostics (STG_TRACE) or nullptr
@@ -225,8 +226,9 @@ k_solve(const __grid_constant__ ImgSet imgs, Par par, const sdsm_cand* __restric
                 const bool solo_before = ci.n_ne <= EVAL_WARPS || (ci.n_ne <= args.solo_cells && ws.cstate[c].nf + ws.cstate[c].nh <= args.hi_evals);
                 // chains inside this CTA: the extra points run on warps of this CTA that a single point leaves idle; chains that go through
                 // the queue: extra points compete with everybody's evaluations, so (spec_prio) only the urgent ones get them
-                const int spec_max = (solo_before ? !args.spec_solo : (args.spec_prio && !ws.prio[c])) ? 1 : args.spec_max;
-                requested = ctrl_step<BLOCK>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells, spec_max, args.spec_retry, args.spec_hess, big);
+                const int spec_max = (solo_before && !args.spec_solo) ? 1 : args.spec_max;
+                const int spec_eager = solo_before || !args.spec_prio || ws.prio[c];
+                requested = ctrl_step<BLOCK>(par, img, cd, ci, ws, c, sm, out, args.trace, args.task_small_cells, spec_max, spec_eager, args.spec_retry, args.spec_hess, args.spec_skip, big);
                 if (tid == 0) { ws.cstate[c].ns_ctrl += globaltimer_ns() - t_link; q_progress(ws); }
                 if (!requested) {
                     if (tid == 0) {

@@ -40,6 +40,7 @@ struct sdsm_ctx {
     int hi_evals = 300;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     int spec_max = SPEC_MAX;                 // SDSM_SPEC_MAX: trial points per line-search request (1: no speculative backtracking)
     int spec_retry = 4;                      // SDSM_SPEC_RETRY: points of the request after a first request of one point was rejected
+    int spec_skip = 1;                       // SDSM_SPEC_SKIP: 1 = first-pass line searches whose decisions do not depend on F make no evaluations
     int spec_hess = 1;                       // SDSM_SPEC_HESS: 1 = a trial that will probably be accepted is evaluated with its Hessian
     int spec_prio = 1;                       // SDSM_SPEC_PRIO: 1 = of the chains that go through the queue only the urgent ones speculate
     int spec_solo = 1;                       // SDSM_SPEC_SOLO: 1 = chains inside one control CTA speculate too (their points are evaluated in that CTA)
@@ -94,6 +95,7 @@ extern "C" int sdsm_create(sdsm_ctx** out, int device)
     if (const char* e = getenv("SDSM_SPEC_MAX")) { ctx->spec_max = atoi(e); if (ctx->spec_max < 1) ctx->spec_max = 1; if (ctx->spec_max > SPEC_MAX) ctx->spec_max = SPEC_MAX; }
     if (const char* e = getenv("SDSM_SPEC_RETRY")) { ctx->spec_retry = atoi(e); if (ctx->spec_retry < 1) ctx->spec_retry = 1; }
     if (const char* e = getenv("SDSM_SPEC_SOLO")) ctx->spec_solo = atoi(e) != 0;
+    if (const char* e = getenv("SDSM_SPEC_SKIP")) ctx->spec_skip = atoi(e) != 0;
     if (const char* e = getenv("SDSM_SPEC_HESS")) ctx->spec_hess = atoi(e) != 0;
     if (const char* e = getenv("SDSM_SPEC_PRIO")) ctx->spec_prio = atoi(e) != 0;
     if (const char* e = getenv("SDSM_CTRL_SHARE")) ctx->ctrl_share = atof(e);
@@ -372,6 +374,7 @@ static int run_solver(sdsm_ctx* ctx, cudaStream_t stream, const sdsm_cand* d_can
     args.spec_retry = ctx->spec_retry;
     args.spec_solo = ctx->spec_solo;
     args.spec_hess = ctx->spec_hess;
+    args.spec_skip = ctx->spec_skip;
     args.spec_prio = ctx->spec_prio;
     args.n_ctrl_ctas = ctx->ctrl_ctas;
     args.timeout_ns = (unsigned long long)(ctx->timeout_s * 1e9);
