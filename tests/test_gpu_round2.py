@@ -195,3 +195,36 @@ def test_hessian_sparsity_tol_against_the_reference(eng):
             eng.set_params(case.dsm_cfg)
             eng.solve(case.footprints)
             assert (np.tril(eng.eval_candidate(k, p)[2]) != 0).sum() > (ref != 0).sum()                         # without it: denser
+
+
+def test_speculative_evaluation_changes_no_bit(monkeypatch):
+    """The solver evaluates line-search trials ahead of cp's decisions (several backtracking points per request, the Hessian
+    with a trial that will be accepted, no evaluations at all in first-pass searches that do not look at F): decisions and
+    results must be those of the sequential search, bit for bit -- energies, parameters, status, iteration and evaluation
+    counters, foreground masks.  Context A is created with every speculation off, context B with the defaults."""
+    from superdsm_b200.engine import Engine
+    from workloads import synth
+    for var in ('SDSM_SPEC_MAX', 'SDSM_SPEC_HESS', 'SDSM_SPEC_SKIP', 'SDSM_SPEC_SOLO', 'SDSM_SPEC_PRIO'): monkeypatch.delenv(var, raising=False)
+    monkeypatch.setenv('SDSM_SPEC_MAX', '1'); monkeypatch.setenv('SDSM_SPEC_HESS', '0'); monkeypatch.setenv('SDSM_SPEC_SKIP', '0')
+    plain = Engine(0)
+    for var in ('SDSM_SPEC_MAX', 'SDSM_SPEC_HESS', 'SDSM_SPEC_SKIP'): monkeypatch.delenv(var)
+    spec = Engine(0)
+    monkeypatch.setenv('SDSM_SPEC_PRIO', '0'); monkeypatch.setenv('SDSM_SPEC_RETRY', '8')
+    eager = Engine(0)                                                    # every candidate speculates, as far as it goes
+    w = synth.make_workload('gowt1', oversegment=3, max_set_size=4, seed=1)
+    fps = w['footprints'][::3]                                           # every size class, incl. the long irregular chains
+    out = []
+    for e in (plain, spec, eager):
+        e.set_image(w['y'], w['y_mask'], w['atoms'], w['dsm_cfg']['background_margin'])
+        e.set_params(w['dsm_cfg'])
+        res = e.solve(fps)
+        out.append((res.energy.copy(), res.status.copy(), res.info.copy(), [res.params(k) for k in range(len(fps)) if res.status[k] < 2],
+                    res.fgbox.copy(), res.fgmask.copy(), e.solver_stats()))
+    a = out[0]
+    assert (a[2][:, 6] > 40).any() and (a[1] == 0).mean() > 0.9
+    for b in out[1:]:
+        assert np.array_equal(a[0].view(np.uint64), b[0].view(np.uint64))
+        assert np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2]) and np.array_equal(a[4], b[4]) and np.array_equal(a[5], b[5])
+        for p, q in zip(a[3], b[3]): assert np.array_equal(p.view(np.uint64), q.view(np.uint64))
+    # and it does what it is for: fewer control tasks (round trips) and fewer evaluation items
+    assert out[1][6]['n_ctrl'] < 0.7 * a[6]['n_ctrl'] and out[1][6]['n_eval'] < 0.9 * a[6]['n_eval']
