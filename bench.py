@@ -69,13 +69,16 @@ def make_workload(rank, args, seed=None):
                                max_candidates=args.max_candidates)
 
 
-def algorithmic_work(res, cfg_subsample=None):
+def algorithmic_work(res, counts=None):
     """Algorithmic bytes and flops of one solver launch, from SURVEY.md section 8(d) and the evaluation counters the
     kernel reports: per value+gradient evaluation 12 n + 16 (6 + m) + 8 bytes, per Hessian evaluation
     12 n + 8 (6 + m) + 4 (6 + m)(7 + m) bytes, plus the result pass (8 n); flops likewise with k = nnz(G~) / n <= 25."""
     n = res.cands['n'].astype(np.float64)
     m = res.info[:, 0].astype(np.float64)
     nf = res.info[:, 6].astype(np.float64)
+    # info[6] counts the evaluations the reference makes.  Not charged: trials the solver decides without evaluating F (their
+    # outcome does not depend on F) and accepted trials evaluated in one pass with their Hessian (sdsm_eval_counts).
+    if counts is not None: nf = nf - counts[:, 0] - counts[:, 2]
     nh = res.info[:, 7].astype(np.float64)
     N = 6 + m
     kbar = np.where(m > 0, 12.2, 0.0)            # SURVEY.md section 8(a3): k = 11-14
@@ -343,7 +346,9 @@ def run_gpu(args):
 
         class _R(object): pass
         r = _R(); r.cands = h['cands'].copy(); r.info = info
-        u['alg_bytes'], u['alg_flops'] = algorithmic_work(r)
+        counts = eng.eval_counts(h['ws'], n, h['plan'])
+        u['alg_bytes'], u['alg_flops'] = algorithmic_work(r, counts)
+        u['evals'] = np.array([int(info[:, 6].sum()), int(info[:, 7].sum())] + counts.sum(axis=0).tolist(), dtype=np.int64)
         u['n'], u['pixels'] = n, int(h['cands']['n'].sum())
         optimal += int((status == _lib.ST_OPTIMAL).sum()); n_errors += int((status >= _lib.ST_ERROR).sum())
         pos = 0
@@ -453,6 +458,8 @@ def run_gpu(args):
                                   'note': 'the kernel is bound by FP64 / conversion issue and dependent-issue latency at 16 warps per SM, not by HBM (DESIGN.md section 4)'}},
             'clocks': clocks,
             'solver': {k: stats[k] for k in ('n_eval', 'n_hrows', 'n_ctrl', 'n_promoted')} | {
+                'evaluations_all_units': dict(zip(('reference_value_gradient', 'reference_hessian', 'decided_without_evaluation', 'evaluated_ahead_unused',
+                                                   'merged_with_hessian', 'hessians_in_vain'), sum(u['evals'] for u in units).tolist())),
                 'control_cta_time_share': {k[4:]: round(stats[k] / max(stats['cyc_total'], 1), 4) for k in ('cyc_ctrl', 'cyc_idle')},
                 'evaluation_warp_time_share': {k[4:]: round(stats[k] / max(stats['cyc_wtotal'], 1), 4) for k in ('cyc_eval', 'cyc_hrows', 'cyc_widle')}},
         }

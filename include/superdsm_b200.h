@@ -207,6 +207,15 @@ int sdsm_dfma_peak(sdsm_ctx* ctx, double* d_scratch, int32_t iters, int64_t* flo
  * tasks (microseconds); SYNCHRONISES the stream. */
 int sdsm_finish_times(sdsm_ctx* ctx, const sdsm_plan* plan, const void* d_workspace, int32_t* h_us, void* stream);
 
+/* Diagnostics: h_counts[4 * n_cand] receives, for every candidate of the last sdsm_solve_batch() on this workspace, what the
+ * solver did ahead of cvxopt's cp (oracle/cpsolver.py; results are bit-identical to the sequential search): [0] line-search
+ * trials cp evaluates F at whose outcome does not depend on F (first pass, relaxed steps allowed: cpsolver.py:286-287) and that
+ * were decided without an evaluation, [1] trial points evaluated ahead and never examined, [2] accepted trials whose Hessian
+ * was evaluated with them (one pass over the pixels instead of two), [3] such Hessians evaluated in vain.  info[6] / info[7]
+ * of sdsm_out keep counting the evaluations the REFERENCE makes; executed value+gradient passes = info[6] - [0] + [1] - [2].
+ * SYNCHRONISES the stream. */
+int sdsm_eval_counts(sdsm_ctx* ctx, const sdsm_plan* plan, const void* d_workspace, int32_t* h_counts, void* stream);
+
 /* Measurement aid: `repeats` sweeps of the evaluation tasks (rows = 0; value + gradient, plus the per-cell Hessians if
  * want_h) or of the Hessian-row tasks (rows = 1) over EVERY candidate of the last solved batch at its solution, outside
  * the solver: the streaming pass the HBM / FP64 roofline of the energy kernels is quoted on.  Time it with CUDA events. */

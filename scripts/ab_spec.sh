@@ -4,6 +4,7 @@ B=$PWD/superdsm_b200/libsuperdsm_b200_base.so
 SDSM_LIB=$B python scripts/dump_results.py gpurun_out/ab_base.npz gowt1 tiled bbbc039 nih3t3 2>&1 | grep -v Warn
 python scripts/dump_results.py gpurun_out/ab_new.npz gowt1 tiled bbbc039 nih3t3 2>&1 | grep -v Warn
 python scripts/dump_results.py --compare gpurun_out/ab_base.npz gpurun_out/ab_new.npz | grep -v identical
-for cfg in "SDSM_SPEC_MAX=1 SDSM_SPEC_HESS=0 SDSM_SPEC_SKIP=0" "SDSM_SPEC_SKIP=0" "" "SDSM_SPEC_PRIO=0"; do
-  env $cfg timeout 300 python bench.py --steps 4 --warmup 4 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads([l for l in sys.stdin.read().splitlines() if l.startswith('{')][-1]); print('[$cfg]', round(d['ms_per_step'],2), d['stats']['rank0_step_ms'], d['value'], d['e2e']['value'], d['solver']['control_cta_time_share'], d['solver']['evaluation_warp_time_share'])"
+for cfg in "SDSM_SPEC_MAX=1 SDSM_SPEC_HESS=0 SDSM_SPEC_SKIP=0" "" "SDSM_CTRL_CTAS=64"; do
+  env $cfg timeout 300 python bench.py --steps 4 --warmup 4 --no-cpu-baseline 2>/dev/null | python -c "import sys,json; d=json.loads([l for l in sys.stdin.read().splitlines() if l.startswith('{')][-1]); print('[$cfg]', round(d['ms_per_step'],2), d['stats']['rank0_step_ms'], d['value'], d['e2e']['value'], d['solver'], d['roofline']['frac'], d['roofline']['fp64']['frac'])"
 done
+python -m pytest tests/test_gpu_round2.py -q -m gpu -k speculative 2>&1 | tail -3

@@ -30,7 +30,8 @@ def dump(path, names):
         st = eng.solver_stats(); tot = max(st['cyc_total'], 1); wtot = max(st['cyc_wtotal'], 1)
         print(name, K, 'candidates', 'ms', [round(t * 1e3, 1) for t in ts], 'nf', int(res.info[:, 6].sum()), 'nh', int(res.info[:, 7].sum()),
               'ctrl busy %.3f eval %.3f hrows %.3f widle %.3f' % (st['cyc_ctrl'] / tot, st['cyc_eval'] / wtot, st['cyc_hrows'] / wtot, st['cyc_widle'] / wtot),
-              {k: st[k] for k in ('n_eval', 'n_hrows', 'n_ctrl')}, flush=True)
+              {k: st[k] for k in ('n_eval', 'n_hrows', 'n_ctrl')},
+              'skipped/unused/merged/hwasted', eng.eval_counts().sum(axis=0).tolist() if hasattr(eng.lib, 'sdsm_eval_counts') else None, 'it', res.info[:, 1:4].clip(0).sum(axis=0).tolist(), flush=True)
     np.savez_compressed(path, **out)
 
 

@@ -47,7 +47,7 @@ class Out(ctypes.Structure):
 EXPORTS = ('sdsm_abi_version', 'sdsm_create', 'sdsm_destroy', 'sdsm_last_error', 'sdsm_set_image', 'sdsm_set_images', 'sdsm_set_params',
            'sdsm_plan_batch', 'sdsm_solve_batch', 'sdsm_eval_candidate', 'sdsm_export_smooth', 'sdsm_trace_solve',
            'sdsm_dfma_peak', 'sdsm_launch_count', 'sdsm_solver_stats', 'sdsm_sweep_eval', 'sdsm_finish_times', 'sdsm_prepare_image',
-           'sdsm_preprocess', 'sdsm_prepare_image_noalloc')
+           'sdsm_preprocess', 'sdsm_prepare_image_noalloc', 'sdsm_eval_counts')
 
 _lib = None
 
@@ -83,6 +83,7 @@ def load():
     lib.sdsm_launch_count.restype = i64
     lib.sdsm_solver_stats.argtypes = [vp, ctypes.POINTER(Plan), vp, vp, vp]
     lib.sdsm_finish_times.argtypes = [vp, ctypes.POINTER(Plan), vp, vp, vp]
+    if hasattr(lib, 'sdsm_eval_counts'): lib.sdsm_eval_counts.argtypes = [vp, ctypes.POINTER(Plan), vp, vp, vp]      # (absent from older builds named by SDSM_LIB)
     lib.sdsm_sweep_eval.argtypes = [vp, ctypes.POINTER(Plan), vp, i32, i32, i32, i32, vp, vp]
     if lib.sdsm_abi_version() != ABI_VERSION:
         raise ImportError('libsuperdsm_b200.so: ABI version mismatch')

@@ -96,7 +96,10 @@ struct CState {
     // speculative backtracking: the pending / last trial request holds spec_n points (x + step beta^k dx, k < spec_n), spec_k is
     // the one being examined; ls_cnt = trials examined in the current line search, ls_prev = in the previous one (the predictor)
     int32_t spec_n, spec_k, ls_cnt, ls_prev;
-    int32_t spec_h, spec_pad;              // spec_h: the pending / last trial was evaluated with its Hessian (PC_TRIALREQ)
+    int32_t spec_h, spec_pad;              // spec_h: the last point of the pending / last trial request was evaluated with its Hessian
+    // statistics (sdsm_eval_counts): trials cp evaluates F at that were decided without evaluation / trial points evaluated but
+    // never examined / accepted trials whose Hessian came with them (one pass instead of two) / Hessians evaluated in vain
+    int32_t n_skipped, n_unused, n_merged, n_hwasted;
 };
 
 // what the evaluation tasks need to know about a candidate (written by the control task that files the request)
@@ -106,7 +109,8 @@ struct EvalReq {
     int32_t want_h, use_xi;  // want_h: 0 value + gradient, 1 value + gradient + Hessian, 2 Hessian only (value and gradient at this
                              // point are already known: the accepted trial of the line search was evaluated at it)
     int32_t cpt, cpw;      // non-empty cells per CTA-wide evaluation task (chains that stay in one CTA, diagnostics) / per warp item
-    int32_t npts, ld;      // points to evaluate: x + k * ld for k < npts, results in the k-th copy of scrG / xig (npts > 1: no Hessian)
+    int32_t npts, ld;      // points to evaluate: x + k * ld for k < npts, results in the k-th copy of scrG / xig; with npts > 1,
+                           // want_h is about the last point
 };
 
 // Workspace carved out of the caller's buffer.  Per-pixel / per-cell / per-table arrays are indexed with the

@@ -271,7 +271,7 @@ __device__ __forceinline__ void hg_row(const Par& par, const sdsm_cand* __restri
             __syncwarp();
         }
     }
-    const double* x = rq.x;
+    const double* x = rq.x + (size_t)(rq.npts - 1) * rq.ld;          // the point the Hessian is evaluated at: the last of the request
     for (int t = lane; t < SP * SP; t += 32) {
         const int ka = ja + t / SP - 2 * NC, kb = jb + t % SP - 2 * NC;
         if (ka < 0 || ka >= ch || kb < 0 || kb >= cw) continue;
@@ -872,6 +872,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
                 out.d_energy[c] = 0.0;
             }
             S.status = SDSM_ST_OPTIMAL; S.bits = 0; S.it1 = S.it2 = S.it3 = -1; S.nf = S.nh = 0; S.have1 = 0; S.r_ipm = 0;
+            S.n_skipped = S.n_unused = S.n_merged = S.n_hwasted = 0;
             S.val1 = 0; S.psi_last = 0; S.energy = 0;
             if (ci.flags) { S.status = SDSM_ST_BADREGION; if (tid == 0) out.d_status[c] = S.status; S.pc = PC_DONE; yield = true; break; }
             if (ci.n_fg == 1 && par.skip_single_fg) { S.status = SDSM_ST_SKIPPED; if (tid == 0) out.d_status[c] = S.status; S.pc = PC_DONE; yield = true; break; }   // objects.py:184-191
@@ -1031,7 +1032,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
                     int bad = 0;
                     for (int i = tid; i < Nc; i += BLOCK) bad |= isnan(x[i] + step * dx[i]);
                     if (__syncthreads_or(bad) || S.nf + S.nh >= EVAL_BUDGET) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }
-                    S.nf += 1; S.ls_cnt += 1;
+                    S.nf += 1; S.ls_cnt += 1; S.n_skipped += 1;
                     const double newgap = (1.0 - (1.0 - S.sigma) * step) * S.gap + step * step * S.dsdz;
                     if (newgap <= (1.0 - CP_ALPHA * step) * S.gap) {
                         const double r = newgap / S.gap;
@@ -1052,8 +1053,11 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             // iteration in particular) tend to need the same number of trials.
             // The first request of the second pass is a confident one (its predictor is the first pass of the same iteration);
             // the others are made only for candidates allowed to waste evaluations (spec_eager).
+            // A second-pass trial made while relaxed steps are allowed is accepted whatever F returns (PC_TRIAL): one point.
+            const bool sure = S.pass == 1 && 0 <= S.relaxed && S.relaxed < MAX_RELAXED;
             int K = 1;
-            if (S.ls_cnt == 0) { if (spec_eager || S.pass == 1) K = S.ls_prev; }
+            if (sure) K = 1;
+            else if (S.ls_cnt == 0) { if (spec_eager || S.pass == 1) K = S.ls_prev; }
             else if (spec_eager) K = S.ls_cnt < spec_retry ? spec_retry : S.ls_cnt;
             K = K < 1 ? 1 : (K > spec_max ? spec_max : K);
             __syncthreads();
@@ -1067,21 +1071,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
             }
             __syncthreads();
             REQUEST(V_SPX, V_SPG, 0, PC_TRIAL, { S.r_ipm = 2; S.pc = PC_IPMDONE; });
-            if (requested && K == 1 && spec_hess && S.pass == 1 && S.ls_cnt == 0 && S.ls_prev == 1) {
-                // Speculative Hessian.  The first pass of this iteration accepted its first trial, so this pass almost certainly
-                // will too (the two passes of an iteration need the same number of trials nearly always), and the accepted point
-                // is the next iterate, whose Hessian is the next thing asked for: evaluate it with the trial (one pass over the
-                // pixels instead of two, one round trip less).  The rows the T_HG tasks write are scaled with the z of the next
-                // iterate, which only depends on the step: PC_ACCEPT's expressions.  H of the current iterate is not needed any
-                // more (it is factored, and the Newton system is solved).
-                const double ds = (1.0 + S.step * S.ds) * S.lm;
-                const double dz = (1.0 + S.step * S.dz) * S.lm;
-                const double sq_s = sqrt(ds), sq_z = sqrt(dz);
-                const double d_new = S.d * sq_s / sq_z;
-                const double lm_new = sq_s * sq_z;
-                S.z_spec = lm_new / d_new;
-                S.req_h = 1; S.spec_h = 1;
-            }
+            const bool want_spec_h = requested && spec_hess && (sure || (S.pass == 1 && S.ls_cnt == 0 && K == S.ls_prev));
             if (requested && K > 1) {
                 // a later point that holds a NaN ends the request before it (the sequential search would have stopped there)
                 int Ke = 1;
@@ -1094,13 +1084,32 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
                 }
                 S.spec_n = Ke;
             }
+            if (want_spec_h && S.spec_n == K) {
+                // The Hessian with the trial.  The trial is either sure to be accepted, or the first pass of this iteration examined
+                // K trials, so that this pass almost certainly accepts its K-th too (the two passes of an iteration need the same
+                // number of trials nearly always); the accepted point is the next iterate, whose Hessian is the next thing asked
+                // for: the last point of the request is evaluated with it (one pass over the pixels instead of two, one round
+                // trip less).  The rows the T_HG tasks write are
+                // scaled with the z of the next iterate, which only depends on the step: PC_ACCEPT's expressions.  H of the
+                // current iterate is not needed any more (it is factored, and the Newton system is solved).
+                double st = S.step;
+                for (int k = 1; k < K; ++k) st *= CP_BETA;
+                const double ds = (1.0 + st * S.ds) * S.lm;
+                const double dz = (1.0 + st * S.dz) * S.lm;
+                const double sq_s = sqrt(ds), sq_z = sqrt(dz);
+                const double d_new = S.d * sq_s / sq_z;
+                const double lm_new = sq_s * sq_z;
+                S.z_spec = lm_new / d_new;
+                S.req_h = 1; S.spec_h = 1;
+            }
+            if (requested) S.n_unused += S.spec_n;       // (every examined point takes itself off again: PC_TRIAL)
             break;
         }
         case PC_TRIAL: {                     // F and Df at x + step dx are in (f0, ng)
             const double step = S.step;
             const double* ng = P.V + (size_t)(V_SPG + S.spec_k) * ld;
             bool resumed = false;
-            S.ls_cnt += 1;
+            S.ls_cnt += 1; S.n_unused -= 1;
             S.f_trial = f0; S.psi_trial = S.psi_last;
             const double newt = S.t + step * S.dt, newz = S.z + step * S.dz2, news = S.s + step * S.ds2;
             const double newf = f0 - newt;
@@ -1158,7 +1167,8 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
                     else { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }   // cvxopt would repeat this trial until the reference's SIGALRM time-out fires
                 }
             }
-            if (backtrack) S.spec_h = 0;                 // (a Hessian evaluated with this trial is of no use)
+            // a Hessian evaluated with the request is the last point's: of no use if the search ends before or goes on after it
+            if (S.spec_h && (backtrack ? S.spec_k + 1 >= S.spec_n || resumed : S.spec_k + 1 != S.spec_n)) { S.spec_h = 0; S.n_hwasted += 1; }
             if (backtrack) {
                 if (resumed) { S.ls_cnt = 0; S.pc = PC_TRIALREQ; }                     // another point, another direction
                 else if (S.spec_k + 1 < S.spec_n) {
@@ -1193,7 +1203,7 @@ __device__ __forceinline__ bool ctrl_step(const Par& par, const Img& img, const 
                 // the Hessian at x came with the trial: what the request for it would have checked and counted, then on to PC_TOP
                 S.spec_h = 0;
                 if (S.nf + S.nh >= EVAL_BUDGET) { S.r_ipm = 2; S.pc = PC_IPMDONE; break; }
-                S.nh += 1;
+                S.nh += 1; S.n_merged += 1;
                 gather_hessian_block<BLOCK>(P, sm, S.z, Nc, S.use_xi ? P.hess_tol : 0.0);
                 f0 = S.f_trial; S.psi_last = S.psi_trial;
                 S.pc = PC_TOP;

@@ -518,6 +518,7 @@ __device__ __forceinline__ void eval_cell(const Par& par, const sdsm_cand* __res
     const int h = cd->h;
     EvalReq rq = ws.req[c];
     rq.x += (size_t)pt * rq.ld;                      // the pt-th trial point of the request (pt = 0 unless it is a speculative one)
+    if (pt != rq.npts - 1) rq.want_h = 0;            // a Hessian asked for with several trial points is the last point's
     const int32_t* cstart = ws.cell_start + cell_off;
     const int st = cstart[cell], npix = cstart[cell + 1] - st;
     const double* py = ws.pix_y + pix_off + st;

@@ -1,5 +1,6 @@
 // C ABI of the superdsm_b200 library (see include/superdsm_b200.h).  Host side: argument checks, workspace layout,
 // kernel launches on the caller's stream.  No per-batch allocation, no synchronisation.
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -36,7 +37,7 @@ struct sdsm_ctx {
     double timeout_s = 60.0;                 // SDSM_TIMEOUT_S: watchdog of k_solve
     double hi_frac = 0.02;                   // SDSM_HI_FRAC: this share of the batch (the most expensive candidates) is urgent from the start
     bool ctrl_ctas_fixed = false;            // SDSM_CTRL_CTAS given: no adaptation to the batch
-    int ctrl_ctas = 48;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
+    int ctrl_ctas = 64;                      // SDSM_CTRL_CTAS: CTAs of k_solve that run control tasks (the warps of the others evaluate)
     int hi_evals = 300;                      // SDSM_HI_EVALS: candidates that needed more evaluations than this become urgent
     int spec_max = SPEC_MAX;                 // SDSM_SPEC_MAX: trial points per line-search request (1: no speculative backtracking)
     int spec_retry = 4;                      // SDSM_SPEC_RETRY: points of the request after a first request of one point was rejected
@@ -528,6 +529,21 @@ extern "C" int sdsm_sweep_eval(sdsm_ctx* ctx, const sdsm_plan* plan, const sdsm_
         k_sweep<<<ctx->sm_count * ctx->solve_ctas_per_sm, SOLVE_BLOCK, smem, stream>>>(ctx->par, d_cands, ws, rows);
     ctx->launches += 1 + repeats;
     CUDA_TRY(ctx, cudaGetLastError());
+    return SDSM_OK;
+}
+
+extern "C" int sdsm_eval_counts(sdsm_ctx* ctx, const sdsm_plan* plan, const void* d_workspace, int32_t* h_counts, void* stream_)
+{
+    if (!ctx || !plan || !d_workspace || !h_counts) return SDSM_E_ARG;
+    const Layout L = plan_layout(plan);
+    WS ws = make_ws(const_cast<void*>(d_workspace), L);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    // the four counters are the last members of CState: one strided copy takes them out of the candidates' states
+    static_assert(offsetof(CState, n_hwasted) + sizeof(int32_t) == sizeof(CState) && offsetof(CState, n_skipped) + 4 * sizeof(int32_t) == sizeof(CState), "counters last");
+    CUDA_TRY(ctx, cudaMemcpy2DAsync(h_counts, 4 * sizeof(int32_t), reinterpret_cast<const char*>(ws.cstate) + offsetof(CState, n_skipped), sizeof(CState),
+                                    4 * sizeof(int32_t), (size_t)plan->n_cand, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(stream));
     return SDSM_OK;
 }
 

@@ -195,6 +195,15 @@ class Engine(object):
         self.control_times_us = out[n:]
         return out[:n]
 
+    def eval_counts(self, ws=None, n=None, plan=None):
+        """Per candidate of the last batch (n x 4, synchronises): trials decided without evaluating F, trial points evaluated
+        ahead and never examined, accepted trials evaluated together with their Hessian, Hessians evaluated in vain
+        (``sdsm_eval_counts``; ``info[:, 6:8]`` count the evaluations the reference makes)."""
+        if ws is None: plan, ws, n = self._last[0], self._last[2], len(self._last[3])
+        out = np.zeros((n, 4), dtype=np.int32)
+        self._check(self.lib.sdsm_eval_counts(self.ctx, ctypes.byref(plan), ws.data_ptr(), out.ctypes.data, self.stream.cuda_stream))
+        return out
+
     # -- buffers -------------------------------------------------------------------------------------------------
 
     def _buf(self, name, nbytes, pinned=False):
