@@ -48,6 +48,13 @@ RESTORE_POLICY = 'saved'
 #: diagnostics: a list here collects (iteration, pass, first step, trials, accepted step) of every line search
 LS_LOG = None
 
+#: test hook.  cp evaluates F at every trial point of the FIRST pass of an iteration, but while relaxed steps are allowed
+#: (0 <= relaxed_iters < MAX_RELAXED_ITERS) the trial is accepted or rejected on newgap alone -- a function of the step -- and
+#: nothing F returned there is used afterwards.  With POISON_UNUSED the values F returns at those trials are replaced by NaN:
+#: a solve that is unchanged by it proves the claim on that solve (tests/test_oracle_golden.py); the CUDA solver does not make
+#: those evaluations (csrc/ctrl.cuh PC_TRIALREQ).
+POISON_UNUSED = False
+
 
 class _State(object):
     __slots__ = ('x', 't', 's', 'z', 'd', 'lmbda', 'rx_x', 'rx_t', 'rznl', 'dx', 'dt', 'dz', 'ds')
@@ -278,6 +285,7 @@ def cp(F, FH, x0, trace=None, maxiters=MAXITERS, restore_policy=None, events=Non
                 nf0, ng = F(newx)
                 ls_trials += 1
                 ng = np.asarray(ng, dtype=float).reshape(-1)
+                if POISON_UNUSED and i == 0 and 0 <= relaxed_iters < MAX_RELAXED_ITERS: nf0, ng = float('nan'), np.full_like(ng, np.nan)
                 newf = nf0 - newt
                 newrx_x = newz * ng
                 newrx_t = 1.0 - newz

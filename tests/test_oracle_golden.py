@@ -109,3 +109,26 @@ def test_solver_certificate():
     def FH(x, z): return 0.0, np.zeros(3), np.zeros((3, 3))
     with pytest.raises(ValueError, match='Rank'):
         cpsolver.cp(F, FH, np.zeros(3))
+
+
+def test_first_pass_trials_do_not_use_F(case, monkeypatch):
+    """What the CUDA solver relies on when it runs first-pass line searches without evaluations (csrc/ctrl.cuh PC_TRIALREQ):
+    while relaxed steps are allowed, cp decides a first-pass trial on newgap alone and never uses what F returned there
+    (cpsolver.py: the `i == 0` branch of the line search).  Replacing those values by NaN changes no solve, bit for bit;
+    and the line searches of the two passes of an iteration examine the same number of trials (the predictor of the
+    speculative requests) in the overwhelming majority of iterations."""
+    fits = []
+    for poison in (False, True):
+        monkeypatch.setattr(cpsolver, 'POISON_UNUSED', poison)
+        monkeypatch.setattr(cpsolver, 'LS_LOG', [])
+        fits.append([orc.compute_object(case.y, case.y_mask, case.atoms, fp, case.dsm_cfg) for fp in case.footprints])
+        log = list(cpsolver.LS_LOG)
+    for a, b in zip(*fits):
+        assert a['energy'] == b['energy'] and a['fallback'] == b['fallback'] and a['is_optimal'] == b['is_optimal']
+        if a['params'] is not None: assert np.array_equal(np.asarray(a['params']), np.asarray(b['params']))
+        assert np.array_equal(a['fg_fragment'], b['fg_fragment'])
+    pairs = [(p, q) for p, q in zip(log[:-1], log[1:]) if p[1] == 0 and q[1] == 1 and p[0] == q[0]]
+    assert len(pairs) > 20
+    assert np.mean([p[3] == q[3] for p, q in pairs]) > 0.9
+    # a first pass that accepted its first trial is followed by a second pass that does, too (the trial evaluated with its Hessian)
+    assert all(q[3] == 1 for p, q in pairs if p[3] == 1)
