@@ -1,5 +1,7 @@
 # A/B of the speculative-evaluation policy on one box: whole-workload solve times (and a bitwise comparison of all results
-# with the library without speculation), then the default bench
+# with the library without speculation), then the default bench.  The baseline library is built from the commit before the
+# change: git archive 5536676 superdsm_b200 include | tar -x -C /tmp/base && (cd /tmp/base && nvcc -gencode arch=compute_100a,code=sm_100a
+# -O3 -lineinfo -std=c++17 -fmad=false -Xcompiler -fPIC -shared -o $REPO/superdsm_b200/libsuperdsm_b200_base.so superdsm_b200/csrc/sdsm.cu)
 B=$PWD/superdsm_b200/libsuperdsm_b200_base.so
 SDSM_LIB=$B python scripts/dump_results.py gpurun_out/ab_base.npz gowt1 tiled bbbc039 nih3t3 2>&1 | grep -v Warn
 python scripts/dump_results.py gpurun_out/ab_new.npz gowt1 tiled bbbc039 nih3t3 2>&1 | grep -v Warn
